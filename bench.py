@@ -1,0 +1,388 @@
+#!/usr/bin/env python
+"""bench.py — queries/sec of exact top-k over a 10M x 1024 fp32 corpus (BASELINE.json configs[1]).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--impl b200|reference]
+    torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...      (N > 1)
+
+A "step" is one pass of the hot path (index.search) over one batch of synthetic queries.
+  value     queries/s with queries AND corpus resident in HBM (CUDA events over exactly K steps)
+  e2e       the same through the C ABI with HOST buffers: pinned query rows go H2D, (D, I) come back D2H,
+            every step, inside the timed region
+  roofline  the scan kernel's algorithmic bytes (rows x row pitch, read once) / its mean launch time,
+            measured live with CUDA events on the launching stream, against MEASURED_PEAKS.json
+  cpu_baseline  the oracle's C restatement of faiss IndexFlat (OpenMP over queries only, like faiss below 20
+            queries) timed on this box's host cores on a bounded row sample, scaled linearly in rows
+N > 1: the fixed 10M-row corpus is row-sharded over the ranks (strong scaling), rank 0 broadcasts each query
+batch, every rank scans its shard, ONE all-gather exchanges the per-shard (score, id) lists, every rank merges.
+`--impl reference` times the CPU restatement alone (the reference's own implementation, faiss-cpu, is not
+installable here: BASELINE.md section 2).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "queries/sec, exact top-k (IndexFlatIP) over 10M x 1024 fp32"
+UNIT = "queries/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--rows", type=int, default=10_000_000)
+    ap.add_argument("--dim", type=int, default=1024)
+    ap.add_argument("--batch", type=int, default=1)
+    ap.add_argument("--k", type=int, default=10)
+    ap.add_argument("--dtype", default="float32", choices=["float32", "bfloat16"])
+    ap.add_argument("--cpu-sample-rows", type=int, default=1_000_000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--extra", action="store_true", help="also time batch 16 and print it under 'extra'")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return (f"IndexFlatIP over {a.rows}x{a.dim} {a.dtype} normalised synthetic embeddings, "
+            f"query batch {a.batch}, k={a.k} (BASELINE.json configs[1])")
+
+
+# ------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_id=None):
+        self.samples = []  # (wall time, sm, sm_max, power, flags dict)
+        self.proc = None
+        cmd = ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "100"]
+        if gpu_id is not None:
+            cmd += ["-i", str(gpu_id)]
+        try:
+            self.proc = subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 9:
+                continue
+            try:
+                sm, smmax = float(parts[1]), float(parts[2])
+            except ValueError:
+                continue
+            flags = {"hw_slowdown": parts[5], "hw_thermal_slowdown": parts[6], "sw_thermal_slowdown": parts[7],
+                     "sw_power_cap": parts[8]}
+            self.samples.append((time.time(), sm, smmax, parts[3], flags))
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self, t0, t1):
+        inside = [s for s in self.samples if t0 <= s[0] <= t1] or self.samples[-3:]
+        if not inside:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        reasons = sorted({name for s in inside for name, v in s[4].items() if v.lower().startswith("active")})
+        return {"sm_mhz": statistics.median(s[1] for s in inside), "sm_max_mhz": max(s[2] for s in inside),
+                "reasons": reasons, "samples": len(inside)}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic():
+    """dram bytes per scan launch from the committed ncu --set full capture, if one exists."""
+    p = os.path.join(ROOT, "profiles", "scan_traffic.json")
+    try:
+        return json.load(open(p)).get("dram_bytes_per_launch")
+    except Exception:
+        return None
+
+
+# ------------------------------------------------------------------------------------------ CPU legs
+def cpu_scan_timing(a, budget_s, max_passes, fixed_rows=None):
+    """Time oracle search_seq (faiss threading: OpenMP over queries only) on a row sample.
+    Returns dict(value=QPS scaled to a.rows, cores, sample, t_pass)."""
+    from oracle import flat
+
+    rows = fixed_rows or min(a.cpu_sample_rows, a.rows)
+    x = flat.synth(0, rows, a.dim, flat.CORPUS_SEED)
+    flat.normalize_L2(x)
+    q = flat.synth(0, a.batch, a.dim, flat.QUERY_SEED)
+    flat.normalize_L2(q)
+    flat.search_seq(x[: min(rows, 20000)], q, a.k, flat.METRIC_IP)  # warm the library
+    times, used = [], 1
+    t_begin = time.time()
+    while len(times) < max_passes and (time.time() - t_begin < budget_s or not times):
+        t0 = time.perf_counter()
+        _, _, used = flat.search_seq(x, q, a.k, flat.METRIC_IP)
+        times.append(time.perf_counter() - t0)
+    t_pass = statistics.median(times)
+    scale = a.rows / rows
+    return {"value": a.batch / (t_pass * scale), "unit": UNIT, "cores": int(used), "kind": "port",
+            "sample": f"{rows} of {a.rows} rows x {a.dim} fp32, batch {a.batch}, k={a.k}, {len(times)} passes, "
+                      f"median pass {t_pass * 1e3:.1f} ms, scaled x{scale:g} (flat scan is linear in rows); "
+                      f"OpenMP over queries only as in faiss below 20 queries; host has {os.cpu_count()} logical cores",
+            "t_pass": t_pass, "rows": rows, "host_cores": os.cpu_count()}
+
+
+def run_reference(a):
+    """--impl reference: the reference's CPU path for this workload.  faiss-cpu itself cannot be installed
+    (BASELINE.md section 2), so this is the oracle's restatement of it, timed alone on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import flat
+
+    flat.build()
+    # size the sample so that (warmup + steps) passes finish in about two minutes
+    probe = cpu_scan_timing(a, budget_s=1.0, max_passes=2, fixed_rows=min(100_000, a.rows))
+    per_row = probe["t_pass"] / probe["rows"]
+    total_passes = a.steps + a.warmup
+    rows = int(min(a.cpu_sample_rows, a.rows, max(50_000, 120.0 / max(total_passes, 1) / per_row)))
+    x = flat.synth(0, rows, a.dim, flat.CORPUS_SEED)
+    flat.normalize_L2(x)
+    qs = flat.synth(0, a.batch * total_passes, a.dim, flat.QUERY_SEED)
+    flat.normalize_L2(qs)
+    used = 1
+    for i in range(a.warmup):
+        flat.search_seq(x, qs[i * a.batch:(i + 1) * a.batch], a.k, flat.METRIC_IP)
+    t0 = time.perf_counter()
+    for i in range(a.warmup, total_passes):
+        _, _, used = flat.search_seq(x, qs[i * a.batch:(i + 1) * a.batch], a.k, flat.METRIC_IP)
+    dt = time.perf_counter() - t0
+    scale = a.rows / rows
+    t_step = dt / a.steps * scale
+    value = a.batch / t_step
+    sample = (f"each step scans {rows} of {a.rows} rows (x{scale:g} linear scaling), batch {a.batch}, k={a.k}; "
+              f"C restatement of faiss IndexFlat (oracle/flat_oracle.c), OpenMP over queries only; "
+              f"host has {os.cpu_count()} logical cores")
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": t_step * 1e3, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(a), "rows": a.rows, "dim": a.dim, "batch": a.batch, "k": a.k},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": int(used), "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------ GPU arm
+def build_shard(a, device, lo, hi):
+    """Rows [lo, hi) of the synthetic corpus, generated on the device and ingested with the fused normalise."""
+    import torch
+
+    from nv_genai_b200 import IndexFlatIP, synth_fill
+    from oracle import flat  # seeds only
+
+    idx = IndexFlatIP(a.dim, dtype=a.dtype, device=device)
+    chunk = min(1_000_000, max(hi - lo, 1))
+    buf = torch.empty((chunk, a.dim), dtype=torch.float32, device=f"cuda:{device}")
+    for r0 in range(lo, hi, chunk):
+        m = min(chunk, hi - r0)
+        synth_fill(buf[:m], r0, flat.CORPUS_SEED)
+        idx.add(buf[:m], normalize=True)
+    torch.cuda.synchronize(device)
+    del buf
+    torch.cuda.empty_cache()
+    return idx
+
+
+def make_queries(a, device, count, batch):
+    import torch
+
+    from nv_genai_b200 import normalize_L2, synth_fill
+    from oracle import flat  # seeds only
+
+    q = torch.empty((count * batch, a.dim), dtype=torch.float32, device=f"cuda:{device}")
+    synth_fill(q, 0, flat.QUERY_SEED)
+    normalize_L2(q)
+    return q.view(count, batch, a.dim)
+
+
+def run_b200(a):
+    import torch
+
+    from nv_genai_b200 import _native
+    from nv_genai_b200.sharded import ShardedFlatIndex, shard_bounds
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a GPU: nv_genai_b200 has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    assert world == a.gpus, f"--gpus {a.gpus} but WORLD_SIZE={world}: launch N>1 with torchrun"
+
+    lo, hi = shard_bounds(a.rows, world, rank)
+    idx = build_shard(a, local, lo, hi)
+    total = a.warmup + a.steps
+    sh = None
+    if world > 1:
+        sh = ShardedFlatIndex(a.dim, idx.metric_type, local_index=idx)
+        sh._refresh_bases()
+        assert sh.ntotal == a.rows
+
+    pitch = ((a.dim * (2 if a.dtype == "bfloat16" else 4) + 511) // 512) * 512
+    peak, peak_src = measured_peak()
+    props = torch.cuda.get_device_properties(local)
+    gpu_id = f"GPU-{props.uuid}" if getattr(props, "uuid", None) else local
+    sampler = ClockSampler(gpu_id) if rank == 0 else None
+
+    def one_config(batch):
+        """Returns dict with device-resident and end-to-end timings for this query batch size."""
+        q_dev = make_queries(a, local, total, batch)
+        q_host = torch.empty((total, batch, a.dim), dtype=torch.float32).pin_memory()
+        q_host.copy_(q_dev.cpu())
+        q_np = q_host.numpy()
+        stage = torch.empty((batch, a.dim), dtype=torch.float32, device=f"cuda:{local}")
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+        def step_resident(i):
+            if sh is None:
+                return idx.search(q_dev[i], a.k)
+            # rank 0 owns the batch; the others receive it by broadcast inside sh.search
+            buf = q_dev[i] if rank == 0 else stage
+            return sh.search(buf, a.k, replicated=False, src=0)
+
+        def step_e2e(i):
+            if sh is None:
+                return idx.search(q_np[i], a.k)  # host buffers in, host buffers out, through b2_index_search
+            if rank == 0:
+                stage.copy_(q_host[i], non_blocking=True)  # H2D from pinned memory
+            D, I = sh.search(stage, a.k, replicated=False, src=0)
+            if rank == 0:
+                return D.cpu(), I.cpu()  # D2H of the merged result
+            return D, I
+
+        def timed(step_fn, with_prof):
+            for i in range(a.warmup):
+                step_fn(i)
+            torch.cuda.synchronize()
+            if dist is not None:
+                dist.barrier()
+                torch.cuda.synchronize()
+            if with_prof:
+                _native.prof_read(reset=True)
+                _native.prof_enable(True)
+            _native.launch_count_reset()
+            t0 = time.time()
+            e0.record()
+            for i in range(a.warmup, total):
+                step_fn(i)
+            e1.record()
+            torch.cuda.synchronize()
+            t1 = time.time()
+            launches = _native.launch_count()
+            scan_ms, scan_n = (0.0, 0)
+            if with_prof:
+                _native.prof_enable(False)
+                scan_ms, scan_n = _native.prof_read(reset=True)
+            if dist is not None:
+                dist.barrier()
+                torch.cuda.synchronize()
+            ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=f"cuda:{local}")
+            ln = torch.tensor([launches], dtype=torch.int64, device=f"cuda:{local}")
+            if dist is not None:
+                dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+                dist.all_reduce(ln, op=dist.ReduceOp.SUM)
+            return float(ms.item()), int(ln.item()), scan_ms, scan_n, t0, t1
+
+        ms, launches, scan_ms, scan_n, t0, t1 = timed(step_resident, True)
+        ms_e, _, _, _, _, _ = timed(step_e2e, False)
+        clocks = sampler.summary(t0, t1) if sampler is not None else None
+        shard_bytes = (hi - lo) * pitch
+        scan_avg_ms = scan_ms / max(scan_n, 1)
+        achieved = shard_bytes / (scan_avg_ms * 1e-3) / 1e9 if scan_n else None
+        return {
+            "batch": batch, "ms_per_step": ms / a.steps, "value": batch * a.steps / (ms * 1e-3),
+            "e2e_value": batch * a.steps / (ms_e * 1e-3), "e2e_ms_per_step": ms_e / a.steps,
+            "launches": launches, "clocks": clocks,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": (achieved / peak) if achieved else None, "traffic": ncu_traffic() if batch == 1 else None,
+                         "kernel": "scan_topk_kernel", "algorithmic_bytes_per_launch": shard_bytes,
+                         "avg_launch_ms": scan_avg_ms, "launches_timed": scan_n, "peak_source": peak_src,
+                         "scan_share_of_step": (scan_avg_ms * scan_n / ms) if scan_n else None},
+            "h2d": batch * a.dim * 4, "d2h": batch * a.k * 12,
+        }
+
+    main = one_config(a.batch)
+    extra = None
+    if a.extra and a.batch != 16:
+        e = one_config(16)
+        extra = {"batch16": {k: e[k] for k in ("value", "ms_per_step", "e2e_value", "roofline")}}
+    if sampler is not None:
+        sampler.stop()
+
+    cpu = None
+    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        from oracle import flat
+
+        flat.build()
+        cpu = cpu_scan_timing(a, budget_s=12.0, max_passes=12)
+        for key in ("t_pass", "rows", "host_cores"):
+            cpu.pop(key, None)
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": main["value"], "unit": UNIT, "n_gpus": world, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32" if a.dtype == "float32" else "bf16 rows, f32 accumulate",
+            "data": "synthetic",
+            "config": {"workload": workload_name(a), "rows": a.rows, "dim": a.dim, "batch": a.batch, "k": a.k,
+                       "rows_per_gpu": hi - lo, "partitioning": f"row-sharded x{world}" if world > 1 else "single GPU",
+                       "l2_note": "inputs larger than L2: each step streams the whole row store "
+                                  f"({(hi - lo) * pitch / 1e9:.2f} GB per GPU) against a 126 MB L2"},
+            "e2e": {"value": main["e2e_value"], "unit": UNIT, "h2d_bytes_per_step": main["h2d"],
+                    "d2h_bytes_per_step": main["d2h"], "ms_per_step": main["e2e_ms_per_step"]},
+            "gpu_launches": main["launches"], "clocks": main["clocks"], "roofline": main["roofline"],
+        }
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        if extra is not None:
+            line["extra"] = extra
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)
+
+
+if __name__ == "__main__":
+    main()

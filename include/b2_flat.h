@@ -1,0 +1,169 @@
+/*
+ * b2_flat.h — C ABI of the B200 flat (exact) vector index.
+ *
+ * This is the drop-in boundary for the one hot path of april-yyt/NV_GenAI that
+ * this library replaces: the faiss IndexFlatL2 / IndexFlatIP object that
+ * langchain's FAISS vector store drives.  The reference reaches it at
+ *   RetrievalAugmentedGeneration/common/utils.py:85   (from faiss import IndexFlatL2)
+ *   RetrievalAugmentedGeneration/common/utils.py:217  (FAISS(embedder, IndexFlatL2(dim), InMemoryDocstore(), {}))
+ *   examples/5_mins_rag_no_gpu/main.py:90             (FAISS.from_documents -> IndexFlatL2(d) -> index.add)
+ *   examples/5_mins_rag_no_gpu/main.py:125-126        (retriever.invoke -> index.search(1 x 1024, k=4))
+ * faiss itself (faiss-cpu==1.7.4, RetrievalAugmentedGeneration/requirements.txt:25)
+ * is bound through SWIG; every entry point below names the faiss / langchain
+ * routine whose SWIG binding it replaces.
+ *
+ * Conventions
+ *   - plain C: opaque handle, pointers and sizes; no C++/torch types cross it.
+ *   - every function returns a b2_status (0 = ok); b2_last_error() gives the
+ *     thread-local message of the last failure.  No exception crosses the ABI.
+ *   - "where" arguments say whether a caller buffer lives in host or device
+ *     memory (B2_HOST / B2_DEVICE).  Host buffers are copied inside the call.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *     Work is enqueued on it; calls that return results in HOST buffers
+ *     synchronise that stream before returning, device-output calls do not.
+ *   - the caller owns x/q/D/I; the library owns the row store and any scratch
+ *     it allocates (freed by b2_index_destroy).
+ *   - many readers / one writer: searches may run concurrently from different
+ *     host threads; add / remove / merge / reset must not overlap anything.
+ *   - there is no CPU fallback: without a CUDA device every call fails.
+ */
+#ifndef B2_FLAT_H
+#define B2_FLAT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define B2_API __attribute__((visibility("default")))
+#else
+#define B2_API
+#endif
+
+typedef struct b2_index b2_index;
+
+typedef enum {
+    B2_OK = 0,
+    B2_ERR_INVALID = 1,   /* bad argument: dimension mismatch, k <= 0, null pointer ... */
+    B2_ERR_CUDA = 2,      /* a CUDA runtime / driver call failed */
+    B2_ERR_OOM = 3,       /* device or host allocation failed */
+    B2_ERR_UNSUPPORTED = 4, /* valid request outside what the kernels cover (e.g. k > B2_MAX_K) */
+    B2_ERR_NO_DEVICE = 5  /* no usable CUDA device: the library has no CPU path */
+} b2_status;
+
+/* faiss MetricType values (faiss/MetricType.h): METRIC_INNER_PRODUCT = 0, METRIC_L2 = 1 */
+#define B2_METRIC_IP 0
+#define B2_METRIC_L2 1
+
+/* row-store element type */
+#define B2_DTYPE_F32 0
+#define B2_DTYPE_BF16 1
+
+#define B2_HOST 0
+#define B2_DEVICE 1
+
+/* b2_index_add flags */
+#define B2_ADD_NORMALIZE 1u /* faiss.normalize_L2 fused into the ingest kernel */
+
+#define B2_MAX_K 2048
+
+/* Replaces the constructors faiss.IndexFlatL2(d) / faiss.IndexFlatIP(d)
+ * (common/utils.py:217; created inside FAISS.from_documents at main.py:90).
+ * `device` is the CUDA ordinal that will hold the row store. */
+B2_API int b2_index_create(int d, int metric, int dtype, int device, b2_index** out);
+
+/* Replaces the SWIG destructor of the index object. */
+B2_API int b2_index_destroy(b2_index* h);
+
+/* Replace the attributes index.ntotal, index.d, index.metric_type
+ * (langchain reads ntotal in FAISS.__add; callers at common/utils.py:342). */
+B2_API int64_t b2_index_ntotal(const b2_index* h);
+B2_API int b2_index_d(const b2_index* h);
+B2_API int b2_index_metric(const b2_index* h);
+B2_API int b2_index_dtype(const b2_index* h);
+B2_API int b2_index_device(const b2_index* h);
+
+/* Replaces index.add(x) -> IndexFlatCodes::add, plus faiss.normalize_L2(x)
+ * when B2_ADD_NORMALIZE is set (langchain FAISS.__add; reached from
+ * add_documents at examples/nvidia_api_catalog/chains.py:61, add_texts at
+ * examples/multi_turn_rag/chains.py:62, from_documents at main.py:90).
+ * x: n x d fp32, C-contiguous, host or device.  Rows get ids ntotal..ntotal+n-1. */
+B2_API int b2_index_add(b2_index* h, int64_t n, const float* x, int x_where, unsigned flags, void* stream);
+
+/* Replaces index.search(x, k) -> IndexFlat::search (knn_L2sqr / knn_inner_product);
+ * every retriever call of the reference ends here.
+ * q: nq x d fp32.  D: nq x k fp32, I: nq x k int64 (both host or both device,
+ * per out_where).  L2 = squared distance ascending, IP = dot product descending,
+ * unfilled slots I = -1 and D = +FLT_MAX (L2) / -FLT_MAX (IP); equal scores are
+ * ordered lowest id first. */
+B2_API int b2_index_search(b2_index* h, int64_t nq, const float* q, int q_where, int k, float* D, int64_t* I,
+                    int out_where, void* stream);
+
+/* Replaces index.reconstruct(i) (used by langchain's MMR search), batched:
+ * out[j] = row ids[j] as fp32 (n x d).  Negative ids give zero rows. */
+B2_API int b2_index_reconstruct_batch(b2_index* h, int64_t n, const int64_t* ids, int ids_where, float* out,
+                               int out_where, void* stream);
+
+/* Replaces index.remove_ids(np.int64 array) -> IndexFlatCodes::remove_ids
+ * (langchain FAISS.delete; called at common/utils.py:376): in-place
+ * compaction preserving order; ids shift down.  ids: host int64. */
+B2_API int b2_index_remove_ids(b2_index* h, int64_t n, const int64_t* ids, int64_t* n_removed);
+
+/* Replaces index.merge_from(other) (langchain FAISS.merge_from; called at
+ * experimental/oran-chatbot-multimodal/vectorstore/vectorstore_updater.py:216):
+ * appends other's rows, then empties other. */
+B2_API int b2_index_merge_from(b2_index* dst, b2_index* src);
+
+/* Replaces index.reset(). */
+B2_API int b2_index_reset(b2_index* h);
+
+/* Replaces the MMR step of langchain
+ * FAISS.max_marginal_relevance_search_with_score_by_vector: index.search(q, fetch_k)
+ * -> index.reconstruct for each hit -> maximal_marginal_relevance(q, rows, lambda, k)
+ * (langchain_community/vectorstores/utils.py), for a batch of queries, all on
+ * the device.  out_ids: nq x k int64 in pick order (-1 padded); out_scores:
+ * nq x k fp32 = the search score of each pick. */
+B2_API int b2_index_mmr(b2_index* h, int64_t nq, const float* q, int q_where, int k, int fetch_k, float lambda_mult,
+                 int64_t* out_ids, float* out_scores, int out_where, void* stream);
+
+/* Row-sharded search, exchange step: merges G per-shard result lists
+ * (D_parts: G x nq x k fp32, I_parts: G x nq x k int64 GLOBAL ids, device
+ * memory, shard g's rows all have lower ids than shard g+1's) into the global
+ * top-k (D, I: nq x k, device).  Has no single faiss counterpart on the CPU
+ * path of the reference; it restates what faiss IndexShards does after its
+ * per-shard searches and is what the NCCL allgather feeds. */
+B2_API int b2_merge_shard_lists(int metric, int64_t nq, int k, int nparts, const float* D_parts, const int64_t* I_parts,
+                         float* D, int64_t* I, int device, void* stream);
+
+/* faiss.normalize_L2(x) on a caller-owned device array (n x d fp32, in place). */
+B2_API int b2_normalize_l2(float* x, int64_t n, int d, int device, void* stream);
+
+/* Counter-based synthetic embeddings, written straight
+ * into device memory: rows row0..row0+nrows-1 of stream `seed`, n x d fp32.
+ * Bit-identical to oracle/flat_oracle.c b2o_synth_fill.  Bench/test support. */
+B2_API int b2_synth_fill(float* out, int64_t row0, int64_t nrows, int d, uint64_t seed, int device, void* stream);
+
+/* Kernel launches issued by this library (process-wide) since the last
+ * reset (bench.py's gpu_launches). */
+B2_API int64_t b2_launch_count(void);
+B2_API void b2_launch_count_reset(void);
+
+/* Measurement support for bench.py (no counterpart in the reference): when enabled, every
+ * launch of the dominant scan kernel is bracketed by CUDA events on its own stream;
+ * b2_prof_read synchronises those events and returns the summed kernel time and the number
+ * of launches since the last reset. */
+B2_API int b2_prof_enable(int on);
+B2_API int b2_prof_read(double* scan_ms, int64_t* scan_launches, int reset);
+
+/* Thread-local message of the most recent failure on this thread ("" if none). */
+B2_API const char* b2_last_error(void);
+
+/* Library version string. */
+B2_API const char* b2_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2_FLAT_H */

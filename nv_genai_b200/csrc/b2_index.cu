@@ -1,0 +1,777 @@
+// C ABI of the B200 flat index: handle, device row store, dispatch to the kernels.
+// Declarations and the reference interfaces they replace: include/b2_flat.h.
+#include <cuda.h>
+
+#include <algorithm>
+#include <cstring>
+#include <mutex>
+#include <shared_mutex>
+#include <string>
+#include <vector>
+
+#include "b2_common.cuh"
+#include "b2_kernels.h"
+
+namespace b2 {
+
+// ------------------------------------------------------------------ error plumbing
+static thread_local char t_err[512] = {0};
+std::atomic<long long> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(t_err, sizeof(t_err), fmt, ap);
+    va_end(ap);
+}
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) {
+            ok = false;
+            prev = -1;
+            return;
+        }
+        if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+// ------------------------------------------------------------------ driver entry points (no link-time libcuda)
+struct DriverApi {
+    bool ok = false;
+    CUresult (*MemAddressReserve)(CUdeviceptr*, size_t, size_t, CUdeviceptr, unsigned long long) = nullptr;
+    CUresult (*MemAddressFree)(CUdeviceptr, size_t) = nullptr;
+    CUresult (*MemCreate)(CUmemGenericAllocationHandle*, size_t, const CUmemAllocationProp*, unsigned long long) = nullptr;
+    CUresult (*MemRelease)(CUmemGenericAllocationHandle) = nullptr;
+    CUresult (*MemMap)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long) = nullptr;
+    CUresult (*MemUnmap)(CUdeviceptr, size_t) = nullptr;
+    CUresult (*MemSetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc*, size_t) = nullptr;
+    CUresult (*MemGetAllocationGranularity)(size_t*, const CUmemAllocationProp*, CUmemAllocationGranularity_flags) = nullptr;
+};
+
+static bool load_sym(const char* name, void** fn) {
+    cudaDriverEntryPointQueryResult qres;
+    *fn = nullptr;
+    if (cudaGetDriverEntryPoint(name, fn, cudaEnableDefault, &qres) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return qres == cudaDriverEntryPointSuccess && *fn != nullptr;
+}
+
+static const DriverApi& driver() {
+    static DriverApi api;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        bool ok = true;
+        ok &= load_sym("cuMemAddressReserve", (void**)&api.MemAddressReserve);
+        ok &= load_sym("cuMemAddressFree", (void**)&api.MemAddressFree);
+        ok &= load_sym("cuMemCreate", (void**)&api.MemCreate);
+        ok &= load_sym("cuMemRelease", (void**)&api.MemRelease);
+        ok &= load_sym("cuMemMap", (void**)&api.MemMap);
+        ok &= load_sym("cuMemUnmap", (void**)&api.MemUnmap);
+        ok &= load_sym("cuMemSetAccess", (void**)&api.MemSetAccess);
+        ok &= load_sym("cuMemGetAllocationGranularity", (void**)&api.MemGetAllocationGranularity);
+        api.ok = ok;
+    });
+    return api;
+}
+
+// ------------------------------------------------------------------ row store
+// One contiguous virtual range per index, reserved once for the whole HBM and backed by
+// physical chunks as rows arrive (cuMemCreate/cuMemMap), so a 41 GB store grows without the
+// realloc-and-copy that std::vector<uint8_t> codes does in IndexFlatCodes::add.  If the VMM
+// driver API is unavailable the store falls back to cudaMalloc with geometric growth.
+struct RowStore {
+    int device = 0;
+    bool vmm = false;
+    CUdeviceptr va = 0;
+    size_t reserved = 0, mapped = 0, gran = 0;
+    struct Chunk { CUmemGenericAllocationHandle h; size_t off, size; };
+    std::vector<Chunk> chunks;
+    void* plain = nullptr;  // fallback
+    size_t plain_cap = 0;
+
+    char* base() const { return vmm ? reinterpret_cast<char*>(va) : static_cast<char*>(plain); }
+    size_t capacity() const { return vmm ? mapped : plain_cap; }
+
+    int init(int dev) {
+        device = dev;
+        const DriverApi& d = driver();
+        if (!d.ok || getenv("B2_NO_VMM") != nullptr) return B2_OK;
+        CUmemAllocationProp prop;
+        memset(&prop, 0, sizeof(prop));
+        prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+        prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        prop.location.id = dev;
+        size_t g = 0;
+        if (d.MemGetAllocationGranularity(&g, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED) != CUDA_SUCCESS || g == 0)
+            return B2_OK;
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) {
+            cudaGetLastError();
+            return B2_OK;
+        }
+        const size_t want = ((total_b + g - 1) / g) * g;
+        CUdeviceptr p = 0;
+        if (d.MemAddressReserve(&p, want, 0, 0, 0) != CUDA_SUCCESS) return B2_OK;
+        va = p;
+        reserved = want;
+        gran = g;
+        vmm = true;
+        return B2_OK;
+    }
+
+    int ensure(size_t bytes, cudaStream_t stream) {
+        if (bytes <= capacity()) return B2_OK;
+        if (vmm) {
+            const DriverApi& d = driver();
+            size_t grow = bytes - mapped;
+            const size_t quarter = std::min<size_t>(mapped / 4, (size_t)4 << 30);
+            grow = std::max(grow, quarter);
+            grow = ((grow + gran - 1) / gran) * gran;
+            if (mapped + grow > reserved) grow = reserved - mapped;
+            if (mapped + grow < bytes) {
+                set_error("row store: %zu bytes exceed the device (%zu reserved)", bytes, reserved);
+                return B2_ERR_OOM;
+            }
+            CUmemAllocationProp prop;
+            memset(&prop, 0, sizeof(prop));
+            prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+            prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+            prop.location.id = device;
+            CUmemGenericAllocationHandle h;
+            CUresult r = d.MemCreate(&h, grow, &prop, 0);
+            if (r != CUDA_SUCCESS && grow > ((bytes - mapped + gran - 1) / gran) * gran) {
+                grow = ((bytes - mapped + gran - 1) / gran) * gran;  // retry with the bare minimum
+                r = d.MemCreate(&h, grow, &prop, 0);
+            }
+            if (r != CUDA_SUCCESS) {
+                set_error("row store: cuMemCreate(%zu) failed (%d)", grow, (int)r);
+                return B2_ERR_OOM;
+            }
+            if ((r = d.MemMap(va + mapped, grow, 0, h, 0)) != CUDA_SUCCESS) {
+                d.MemRelease(h);
+                set_error("row store: cuMemMap failed (%d)", (int)r);
+                return B2_ERR_CUDA;
+            }
+            CUmemAccessDesc acc;
+            memset(&acc, 0, sizeof(acc));
+            acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+            acc.location.id = device;
+            acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+            if ((r = d.MemSetAccess(va + mapped, grow, &acc, 1)) != CUDA_SUCCESS) {
+                d.MemUnmap(va + mapped, grow);
+                d.MemRelease(h);
+                set_error("row store: cuMemSetAccess failed (%d)", (int)r);
+                return B2_ERR_CUDA;
+            }
+            chunks.push_back({h, mapped, grow});
+            mapped += grow;
+            return B2_OK;
+        }
+        // fallback: geometric growth with a copy
+        size_t ncap = std::max(bytes, plain_cap + plain_cap / 2);
+        ncap = std::max<size_t>(ncap, (size_t)1 << 20);
+        void* np = nullptr;
+        cudaError_t e = cudaMalloc(&np, ncap);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            e = cudaMalloc(&np, bytes);
+            ncap = bytes;
+        }
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            set_error("row store: cudaMalloc(%zu) failed: %s", ncap, cudaGetErrorString(e));
+            return B2_ERR_OOM;
+        }
+        if (plain != nullptr) {
+            // the old contents may still be in use by work on `stream`: copy in stream order, then free
+            if (plain_cap) B2_CUDA_TRY(cudaMemcpyAsync(np, plain, plain_cap, cudaMemcpyDeviceToDevice, stream));
+            B2_CUDA_TRY(cudaStreamSynchronize(stream));
+            cudaFree(plain);
+        }
+        plain = np;
+        plain_cap = ncap;
+        return B2_OK;
+    }
+
+    void release() {
+        if (vmm) {
+            const DriverApi& d = driver();
+            for (auto& c : chunks) {
+                d.MemUnmap(va + c.off, c.size);
+                d.MemRelease(c.h);
+            }
+            chunks.clear();
+            if (va) d.MemAddressFree(va, reserved);
+            va = 0;
+            mapped = reserved = 0;
+            vmm = false;
+        }
+        if (plain) cudaFree(plain);
+        plain = nullptr;
+        plain_cap = 0;
+    }
+};
+
+}  // namespace b2
+
+using namespace b2;
+
+struct b2_index {
+    int d = 0, metric = 0, dtype = 0, device = 0, num_sms = 148;
+    size_t pitch = 0;  // bytes per row, multiple of 512
+    int64_t ntotal = 0;
+    RowStore store;
+    float* norms = nullptr;  // squared norm of each stored row
+    int64_t norms_cap = 0;
+    std::shared_mutex mu;
+};
+
+static size_t row_pitch_bytes(int d, int dtype) {
+    const size_t raw = (size_t)d * (dtype == B2_DTYPE_BF16 ? 2 : 4);
+    return ((raw + 511) / 512) * 512;
+}
+
+static int ensure_norms(b2_index* h, int64_t n, cudaStream_t stream) {
+    if (n <= h->norms_cap) return B2_OK;
+    int64_t ncap = std::max<int64_t>(n, h->norms_cap + h->norms_cap / 2);
+    ncap = std::max<int64_t>(ncap, 1024);
+    float* np = nullptr;
+    B2_CUDA_TRY(cudaMalloc(&np, (size_t)ncap * sizeof(float)));
+    if (h->norms != nullptr) {
+        if (h->ntotal > 0)
+            B2_CUDA_TRY(cudaMemcpyAsync(np, h->norms, (size_t)h->ntotal * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+        B2_CUDA_TRY(cudaStreamSynchronize(stream));
+        cudaFree(h->norms);
+    }
+    h->norms = np;
+    h->norms_cap = ncap;
+    return B2_OK;
+}
+
+static int check_handle(const b2_index* h) {
+    if (h == nullptr) {
+        set_error("null index handle");
+        return B2_ERR_INVALID;
+    }
+    return B2_OK;
+}
+
+extern "C" {
+
+const char* b2_last_error(void) { return t_err; }
+const char* b2_version(void) { return "b2flat 0.1 (sm_100a)"; }
+int64_t b2_launch_count(void) { return (int64_t)g_launches.load(); }
+void b2_launch_count_reset(void) { g_launches.store(0); }
+
+int b2_prof_enable(int on) {
+    prof_enable(on);
+    return B2_OK;
+}
+int b2_prof_read(double* scan_ms, int64_t* scan_launches, int reset) { return prof_read(scan_ms, scan_launches, reset); }
+
+int b2_index_create(int d, int metric, int dtype, int device, b2_index** out) {
+    if (out == nullptr) {
+        set_error("b2_index_create: out is null");
+        return B2_ERR_INVALID;
+    }
+    *out = nullptr;
+    if (d <= 0 || d > 32768) {
+        set_error("b2_index_create: dimension %d out of range [1, 32768]", d);
+        return B2_ERR_INVALID;
+    }
+    if (metric != B2_METRIC_IP && metric != B2_METRIC_L2) {
+        set_error("b2_index_create: unknown metric %d", metric);
+        return B2_ERR_INVALID;
+    }
+    if (dtype != B2_DTYPE_F32 && dtype != B2_DTYPE_BF16) {
+        set_error("b2_index_create: unknown dtype %d", dtype);
+        return B2_ERR_INVALID;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        set_error("no CUDA device available: this library has no CPU path");
+        return B2_ERR_NO_DEVICE;
+    }
+    if (device < 0 || device >= ndev) {
+        set_error("b2_index_create: device %d out of range (have %d)", device, ndev);
+        return B2_ERR_INVALID;
+    }
+    DeviceGuard g(device);
+    if (!g.ok) {
+        set_error("cannot select device %d", device);
+        return B2_ERR_CUDA;
+    }
+    int major = 0, sms = 0;
+    B2_CUDA_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+    B2_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    if (major != 10) {
+        set_error("device %d is sm_%d0: this build targets sm_100a (B200) only", device, major);
+        return B2_ERR_NO_DEVICE;
+    }
+    // keep stream-ordered scratch cached in the pool instead of returning it to the OS
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+        unsigned long long thr = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+    cudaGetLastError();
+    b2_index* h = new (std::nothrow) b2_index();
+    if (h == nullptr) {
+        set_error("out of host memory");
+        return B2_ERR_OOM;
+    }
+    h->d = d;
+    h->metric = metric;
+    h->dtype = dtype;
+    h->device = device;
+    h->num_sms = sms;
+    h->pitch = row_pitch_bytes(d, dtype);
+    h->store.init(device);
+    *out = h;
+    return B2_OK;
+}
+
+int b2_index_destroy(b2_index* h) {
+    if (h == nullptr) return B2_OK;
+    {
+        DeviceGuard g(h->device);
+        cudaDeviceSynchronize();
+        h->store.release();
+        if (h->norms) cudaFree(h->norms);
+        cudaGetLastError();
+    }
+    delete h;
+    return B2_OK;
+}
+
+int64_t b2_index_ntotal(const b2_index* h) { return h ? h->ntotal : -1; }
+int b2_index_d(const b2_index* h) { return h ? h->d : -1; }
+int b2_index_metric(const b2_index* h) { return h ? h->metric : -1; }
+int b2_index_dtype(const b2_index* h) { return h ? h->dtype : -1; }
+int b2_index_device(const b2_index* h) { return h ? h->device : -1; }
+
+int b2_index_add(b2_index* h, int64_t n, const float* x, int x_where, unsigned flags, void* stream_) {
+    B2_TRY(check_handle(h));
+    if (n < 0 || (n > 0 && x == nullptr)) {
+        set_error("b2_index_add: bad arguments (n=%lld)", (long long)n);
+        return B2_ERR_INVALID;
+    }
+    if (n == 0) return B2_OK;
+    if (h->ntotal + n >= (int64_t)0xfffffff0ll) {
+        set_error("b2_index_add: more than 2^32-16 rows per index are not supported");
+        return B2_ERR_UNSUPPORTED;
+    }
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    std::unique_lock<std::shared_mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    if (!g.ok) {
+        set_error("cannot select device %d", h->device);
+        return B2_ERR_CUDA;
+    }
+    B2_TRY(h->store.ensure((size_t)(h->ntotal + n) * h->pitch, stream));
+    B2_TRY(ensure_norms(h, h->ntotal + n, stream));
+    const bool normalize = (flags & B2_ADD_NORMALIZE) != 0;
+    char* dst = h->store.base() + (size_t)h->ntotal * h->pitch;
+    float* nrm = h->norms + h->ntotal;
+    if (x_where == B2_DEVICE) {
+        B2_TRY(ingest_rows(x, n, h->d, dst, h->pitch, h->dtype, normalize, nrm, stream));
+    } else {
+        // host rows: staged through two device buffers so the copy of chunk i+1 can be queued
+        // while chunk i is converted (pinned sources make the copies truly asynchronous)
+        const size_t row_bytes = (size_t)h->d * sizeof(float);
+        int64_t chunk = std::max<int64_t>(1, (int64_t)(((size_t)64 << 20) / row_bytes));
+        chunk = std::min(chunk, n);
+        float* stage[2] = {nullptr, nullptr};
+        B2_CUDA_TRY(cudaMallocAsync(&stage[0], (size_t)chunk * row_bytes, stream));
+        if (n > chunk) {
+            cudaError_t e = cudaMallocAsync(&stage[1], (size_t)chunk * row_bytes, stream);
+            if (e != cudaSuccess) {
+                cudaFreeAsync(stage[0], stream);
+                set_error("b2_index_add: staging allocation failed: %s", cudaGetErrorString(e));
+                return B2_ERR_OOM;
+            }
+        }
+        int rc = B2_OK;
+        int which = 0;
+        for (int64_t off = 0; off < n && rc == B2_OK; off += chunk) {
+            const int64_t m = std::min(chunk, n - off);
+            float* sb = stage[which];
+            cudaError_t e = cudaMemcpyAsync(sb, x + (size_t)off * h->d, (size_t)m * row_bytes, cudaMemcpyHostToDevice, stream);
+            if (e != cudaSuccess) {
+                set_error("b2_index_add: H2D copy failed: %s", cudaGetErrorString(e));
+                rc = B2_ERR_CUDA;
+                break;
+            }
+            rc = ingest_rows(sb, m, h->d, dst + (size_t)off * h->pitch, h->pitch, h->dtype, normalize, nrm + off, stream);
+            if (stage[1] != nullptr) which ^= 1;
+        }
+        cudaFreeAsync(stage[0], stream);
+        if (stage[1]) cudaFreeAsync(stage[1], stream);
+        if (rc != B2_OK) return rc;
+        // the caller may reuse its host buffer as soon as we return
+        B2_CUDA_TRY(cudaStreamSynchronize(stream));
+    }
+    h->ntotal += n;
+    return B2_OK;
+}
+
+// largest query tile (power of two <= 16) whose shared memory fits for this k
+static int max_query_tile(const b2_index* h, int kpad) {
+    const int nchunks = (int)(h->pitch / 512);
+    for (int t = 16; t >= 1; t >>= 1)
+        if (scan_smem_bytes(t, nchunks, h->dtype == B2_DTYPE_BF16, kpad) <= 200 * 1024) return t;
+    return 0;
+}
+
+__global__ void fill_empty_kernel(float* D, int64_t* I, int64_t n, float dval) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        D[i] = dval;
+        I[i] = -1;
+    }
+}
+
+// Device-side search: q_dev [nq][d], D_dev/I_dev [nq][k]; caller holds the shared lock and the device.
+static int search_device(b2_index* h, int64_t nq, const float* q_dev, int k, float* D_dev, int64_t* I_dev,
+                         cudaStream_t stream) {
+    if (h->ntotal == 0) {
+        const int64_t tot = nq * k;
+        fill_empty_kernel<<<(unsigned)std::min<int64_t>((tot + 255) / 256, 1024), 256, 0, stream>>>(
+            D_dev, I_dev, tot, h->metric == B2_METRIC_IP ? -FLT_MAX : FLT_MAX);
+        B2_AFTER_LAUNCH();
+        return B2_OK;
+    }
+    const int kpad = next_pow2(k < 32 ? 32 : k);
+    const int tmax = max_query_tile(h, kpad);
+    if (tmax == 0) {
+        set_error("search: d=%d with k=%d does not fit the scan kernel's shared memory", h->d, k);
+        return B2_ERR_UNSUPPORTED;
+    }
+    for (int64_t off = 0; off < nq;) {
+        const int64_t rem = nq - off;
+        int tile = (int)std::min<int64_t>(next_pow2((int)std::min<int64_t>(rem, 16)), tmax);
+        const int valid = (int)std::min<int64_t>(rem, tile);
+        uint64_t* partial = nullptr;
+        int grid = 0;
+        B2_TRY(scan_pass(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, h->metric, q_dev + (size_t)off * h->d,
+                         valid, tile, k, h->num_sms, stream, &partial, &grid));
+        int rc = merge_partials(partial, valid, grid, k, h->metric, 0, D_dev + (size_t)off * k, I_dev + (size_t)off * k,
+                                (size_t)k, stream);
+        cudaFreeAsync(partial, stream);
+        B2_TRY(rc);
+        off += valid;
+    }
+    return B2_OK;
+}
+
+int b2_index_search(b2_index* h, int64_t nq, const float* q, int q_where, int k, float* D, int64_t* I, int out_where,
+                    void* stream_) {
+    B2_TRY(check_handle(h));
+    if (nq < 0 || k <= 0 || (nq > 0 && (q == nullptr || D == nullptr || I == nullptr))) {
+        set_error("b2_index_search: bad arguments (nq=%lld, k=%d)", (long long)nq, k);
+        return B2_ERR_INVALID;
+    }
+    if (k > B2_MAX_K) {
+        set_error("b2_index_search: k=%d exceeds B2_MAX_K=%d", k, B2_MAX_K);
+        return B2_ERR_UNSUPPORTED;
+    }
+    if (nq == 0) return B2_OK;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    std::shared_lock<std::shared_mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    if (!g.ok) {
+        set_error("cannot select device %d", h->device);
+        return B2_ERR_CUDA;
+    }
+    const float* q_dev = q;
+    float* q_tmp = nullptr;
+    float* D_dev = D;
+    int64_t* I_dev = I;
+    void* out_tmp = nullptr;
+    const size_t nres = (size_t)nq * k;
+    int rc = B2_OK;
+    if (q_where == B2_HOST) {
+        B2_CUDA_TRY(cudaMallocAsync(&q_tmp, (size_t)nq * h->d * sizeof(float), stream));
+        cudaError_t e = cudaMemcpyAsync(q_tmp, q, (size_t)nq * h->d * sizeof(float), cudaMemcpyHostToDevice, stream);
+        if (e != cudaSuccess) {
+            set_error("b2_index_search: query copy failed: %s", cudaGetErrorString(e));
+            rc = B2_ERR_CUDA;
+        }
+        q_dev = q_tmp;
+    }
+    if (rc == B2_OK && out_where == B2_HOST) {
+        cudaError_t e = cudaMallocAsync(&out_tmp, nres * 12, stream);
+        if (e != cudaSuccess) {
+            set_error("b2_index_search: result allocation failed: %s", cudaGetErrorString(e));
+            rc = B2_ERR_OOM;
+        } else {
+            I_dev = static_cast<int64_t*>(out_tmp);
+            D_dev = reinterpret_cast<float*>(I_dev + nres);
+        }
+    }
+    if (rc == B2_OK) rc = search_device(h, nq, q_dev, k, D_dev, I_dev, stream);
+    if (rc == B2_OK && out_where == B2_HOST) {
+        cudaError_t e = cudaMemcpyAsync(I, I_dev, nres * 8, cudaMemcpyDeviceToHost, stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(D, D_dev, nres * 4, cudaMemcpyDeviceToHost, stream);
+        if (e != cudaSuccess) {
+            set_error("b2_index_search: result copy failed: %s", cudaGetErrorString(e));
+            rc = B2_ERR_CUDA;
+        }
+    }
+    if (q_tmp) cudaFreeAsync(q_tmp, stream);
+    if (out_tmp) cudaFreeAsync(out_tmp, stream);
+    if (rc == B2_OK && out_where == B2_HOST) {
+        cudaError_t e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess) {
+            set_error("b2_index_search: %s", cudaGetErrorString(e));
+            rc = B2_ERR_CUDA;
+        }
+    }
+    return rc;
+}
+
+int b2_index_reconstruct_batch(b2_index* h, int64_t n, const int64_t* ids, int ids_where, float* out, int out_where,
+                               void* stream_) {
+    B2_TRY(check_handle(h));
+    if (n < 0 || (n > 0 && (ids == nullptr || out == nullptr))) {
+        set_error("b2_index_reconstruct_batch: bad arguments");
+        return B2_ERR_INVALID;
+    }
+    if (n == 0) return B2_OK;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    std::shared_lock<std::shared_mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    const int64_t* ids_dev = ids;
+    int64_t* ids_tmp = nullptr;
+    float* out_dev = out;
+    float* out_tmp = nullptr;
+    if (ids_where == B2_HOST) {
+        B2_CUDA_TRY(cudaMallocAsync(&ids_tmp, (size_t)n * 8, stream));
+        B2_CUDA_TRY(cudaMemcpyAsync(ids_tmp, ids, (size_t)n * 8, cudaMemcpyHostToDevice, stream));
+        ids_dev = ids_tmp;
+    }
+    if (out_where == B2_HOST) {
+        B2_CUDA_TRY(cudaMallocAsync(&out_tmp, (size_t)n * h->d * 4, stream));
+        out_dev = out_tmp;
+    }
+    int rc = gather_rows(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, ids_dev, n, out_dev, stream);
+    if (rc == B2_OK && out_where == B2_HOST) {
+        cudaError_t e = cudaMemcpyAsync(out, out_dev, (size_t)n * h->d * 4, cudaMemcpyDeviceToHost, stream);
+        if (e != cudaSuccess) {
+            set_error("reconstruct: %s", cudaGetErrorString(e));
+            rc = B2_ERR_CUDA;
+        }
+    }
+    if (ids_tmp) cudaFreeAsync(ids_tmp, stream);
+    if (out_tmp) cudaFreeAsync(out_tmp, stream);
+    if (rc == B2_OK && out_where == B2_HOST) B2_CUDA_TRY(cudaStreamSynchronize(stream));
+    return rc;
+}
+
+int b2_index_remove_ids(b2_index* h, int64_t n, const int64_t* ids, int64_t* n_removed) {
+    B2_TRY(check_handle(h));
+    if (n_removed) *n_removed = 0;
+    if (n < 0 || (n > 0 && ids == nullptr)) {
+        set_error("b2_index_remove_ids: bad arguments");
+        return B2_ERR_INVALID;
+    }
+    if (n == 0 || h->ntotal == 0) return B2_OK;
+    std::unique_lock<std::shared_mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    const int64_t nt = h->ntotal;
+    std::vector<uint8_t> drop((size_t)nt, 0);
+    int64_t removed = 0, first = nt;
+    for (int64_t i = 0; i < n; ++i) {
+        const int64_t id = ids[i];
+        if (id >= 0 && id < nt && !drop[(size_t)id]) {
+            drop[(size_t)id] = 1;
+            ++removed;
+            first = std::min(first, id);
+        }
+    }
+    if (removed == 0) return B2_OK;
+    std::vector<int64_t> src;
+    src.reserve((size_t)(nt - first - removed));
+    for (int64_t i = first; i < nt; ++i)
+        if (!drop[(size_t)i]) src.push_back(i);
+    cudaStream_t stream = nullptr;
+    int rc = B2_OK;
+    if (!src.empty()) {
+        int64_t* src_dev = nullptr;
+        B2_CUDA_TRY(cudaMallocAsync(&src_dev, src.size() * 8, stream));
+        cudaError_t e = cudaMemcpyAsync(src_dev, src.data(), src.size() * 8, cudaMemcpyHostToDevice, stream);
+        if (e != cudaSuccess) {
+            set_error("remove_ids: %s", cudaGetErrorString(e));
+            rc = B2_ERR_CUDA;
+        } else {
+            rc = compact_rows(h->store.base(), h->pitch, h->norms, src_dev, (int64_t)src.size(), first, stream);
+        }
+        cudaFreeAsync(src_dev, stream);
+    }
+    B2_CUDA_TRY(cudaStreamSynchronize(stream));
+    if (rc != B2_OK) return rc;
+    h->ntotal = nt - removed;
+    if (n_removed) *n_removed = removed;
+    return B2_OK;
+}
+
+int b2_index_merge_from(b2_index* dst, b2_index* src) {
+    B2_TRY(check_handle(dst));
+    B2_TRY(check_handle(src));
+    if (dst == src) {
+        set_error("b2_index_merge_from: cannot merge an index into itself");
+        return B2_ERR_INVALID;
+    }
+    if (dst->d != src->d || dst->dtype != src->dtype || dst->metric != src->metric) {
+        set_error("b2_index_merge_from: indexes are not compatible (d %d vs %d, dtype %d vs %d, metric %d vs %d)", dst->d,
+                  src->d, dst->dtype, src->dtype, dst->metric, src->metric);
+        return B2_ERR_INVALID;
+    }
+    std::unique_lock<std::shared_mutex> l1(dst->mu);
+    std::unique_lock<std::shared_mutex> l2(src->mu);
+    const int64_t n = src->ntotal;
+    if (n == 0) return B2_OK;
+    if (dst->ntotal + n >= (int64_t)0xfffffff0ll) {
+        set_error("b2_index_merge_from: more than 2^32-16 rows per index are not supported");
+        return B2_ERR_UNSUPPORTED;
+    }
+    DeviceGuard g(dst->device);
+    cudaStream_t stream = nullptr;
+    B2_TRY(dst->store.ensure((size_t)(dst->ntotal + n) * dst->pitch, stream));
+    B2_TRY(ensure_norms(dst, dst->ntotal + n, stream));
+    char* to = dst->store.base() + (size_t)dst->ntotal * dst->pitch;
+    if (dst->device == src->device) {
+        B2_CUDA_TRY(cudaMemcpyAsync(to, src->store.base(), (size_t)n * dst->pitch, cudaMemcpyDeviceToDevice, stream));
+        B2_CUDA_TRY(cudaMemcpyAsync(dst->norms + dst->ntotal, src->norms, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream));
+    } else {
+        B2_CUDA_TRY(cudaMemcpyPeerAsync(to, dst->device, src->store.base(), src->device, (size_t)n * dst->pitch, stream));
+        B2_CUDA_TRY(cudaMemcpyPeerAsync(dst->norms + dst->ntotal, dst->device, src->norms, src->device, (size_t)n * 4, stream));
+    }
+    B2_CUDA_TRY(cudaStreamSynchronize(stream));
+    dst->ntotal += n;
+    src->ntotal = 0;  // faiss: other.reset()
+    return B2_OK;
+}
+
+int b2_index_reset(b2_index* h) {
+    B2_TRY(check_handle(h));
+    std::unique_lock<std::shared_mutex> lk(h->mu);
+    h->ntotal = 0;
+    return B2_OK;
+}
+
+int b2_index_mmr(b2_index* h, int64_t nq, const float* q, int q_where, int k, int fetch_k, float lambda_mult,
+                 int64_t* out_ids, float* out_scores, int out_where, void* stream_) {
+    B2_TRY(check_handle(h));
+    if (nq < 0 || k <= 0 || fetch_k <= 0 || (nq > 0 && (q == nullptr || out_ids == nullptr || out_scores == nullptr))) {
+        set_error("b2_index_mmr: bad arguments (nq=%lld k=%d fetch_k=%d)", (long long)nq, k, fetch_k);
+        return B2_ERR_INVALID;
+    }
+    if (fetch_k > B2_MAX_K) {
+        set_error("b2_index_mmr: fetch_k=%d exceeds B2_MAX_K=%d", fetch_k, B2_MAX_K);
+        return B2_ERR_UNSUPPORTED;
+    }
+    if (nq == 0) return B2_OK;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    std::shared_lock<std::shared_mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    const size_t nf = (size_t)nq * fetch_k, nk = (size_t)nq * k;
+    // one stream-ordered scratch block: [q?][I fetch][D fetch][rows][out ids][out scores]
+    const size_t q_bytes = (q_where == B2_HOST) ? (size_t)nq * h->d * 4 : 0;
+    const size_t rows_bytes = nf * h->d * 4;
+    const size_t out_bytes = (out_where == B2_HOST) ? nk * 12 : 0;
+    auto al = [](size_t v) { return (v + 255) / 256 * 256; };
+    const size_t total = al(q_bytes) + al(nf * 8) + al(nf * 4) + al(rows_bytes) + al(out_bytes) + 256;
+    char* blk = nullptr;
+    B2_CUDA_TRY(cudaMallocAsync(&blk, total, stream));
+    char* p = blk;
+    float* q_dev = const_cast<float*>(q);
+    if (q_where == B2_HOST) {
+        q_dev = reinterpret_cast<float*>(p);
+        p += al(q_bytes);
+    }
+    int64_t* If = reinterpret_cast<int64_t*>(p);
+    p += al(nf * 8);
+    float* Df = reinterpret_cast<float*>(p);
+    p += al(nf * 4);
+    float* rows = reinterpret_cast<float*>(p);
+    p += al(rows_bytes);
+    int64_t* oi = out_ids;
+    float* os = out_scores;
+    if (out_where == B2_HOST) {
+        oi = reinterpret_cast<int64_t*>(p);
+        os = reinterpret_cast<float*>(oi + nk);
+    }
+    int rc = B2_OK;
+    cudaError_t e = cudaSuccess;
+    if (q_where == B2_HOST) e = cudaMemcpyAsync(q_dev, q, q_bytes, cudaMemcpyHostToDevice, stream);
+    if (e != cudaSuccess) {
+        set_error("b2_index_mmr: %s", cudaGetErrorString(e));
+        rc = B2_ERR_CUDA;
+    }
+    if (rc == B2_OK) rc = search_device(h, nq, q_dev, fetch_k, Df, If, stream);
+    if (rc == B2_OK) rc = gather_rows(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, If, (int64_t)nf, rows, stream);
+    if (rc == B2_OK) rc = mmr_select(q_dev, h->d, (int)nq, rows, If, Df, fetch_k, k, lambda_mult, oi, os, stream);
+    if (rc == B2_OK && out_where == B2_HOST) {
+        e = cudaMemcpyAsync(out_ids, oi, nk * 8, cudaMemcpyDeviceToHost, stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(out_scores, os, nk * 4, cudaMemcpyDeviceToHost, stream);
+        if (e != cudaSuccess) {
+            set_error("b2_index_mmr: %s", cudaGetErrorString(e));
+            rc = B2_ERR_CUDA;
+        }
+    }
+    cudaFreeAsync(blk, stream);
+    if (rc == B2_OK && out_where == B2_HOST) B2_CUDA_TRY(cudaStreamSynchronize(stream));
+    return rc;
+}
+
+int b2_merge_shard_lists(int metric, int64_t nq, int k, int nparts, const float* D_parts, const int64_t* I_parts,
+                         float* D, int64_t* I, int device, void* stream_) {
+    if (nq < 0 || k <= 0 || nparts <= 0 || (nq > 0 && (!D_parts || !I_parts || !D || !I))) {
+        set_error("b2_merge_shard_lists: bad arguments");
+        return B2_ERR_INVALID;
+    }
+    if (nq == 0) return B2_OK;
+    DeviceGuard g(device);
+    if (!g.ok) {
+        set_error("cannot select device %d", device);
+        return B2_ERR_CUDA;
+    }
+    return merge_shards(metric, (int)nq, k, nparts, D_parts, I_parts, D, I, static_cast<cudaStream_t>(stream_));
+}
+
+int b2_normalize_l2(float* x, int64_t n, int d, int device, void* stream_) {
+    if (n < 0 || d <= 0 || (n > 0 && x == nullptr)) {
+        set_error("b2_normalize_l2: bad arguments");
+        return B2_ERR_INVALID;
+    }
+    DeviceGuard g(device);
+    if (!g.ok) {
+        set_error("cannot select device %d", device);
+        return B2_ERR_CUDA;
+    }
+    return normalize_rows_inplace(x, n, d, static_cast<cudaStream_t>(stream_));
+}
+
+int b2_synth_fill(float* out, int64_t row0, int64_t nrows, int d, uint64_t seed, int device, void* stream_) {
+    if (nrows < 0 || d <= 0 || (nrows > 0 && out == nullptr)) {
+        set_error("b2_synth_fill: bad arguments");
+        return B2_ERR_INVALID;
+    }
+    DeviceGuard g(device);
+    if (!g.ok) {
+        set_error("cannot select device %d", device);
+        return B2_ERR_CUDA;
+    }
+    return synth_fill(out, row0, nrows, d, seed, static_cast<cudaStream_t>(stream_));
+}
+
+}  // extern "C"

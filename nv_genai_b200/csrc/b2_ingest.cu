@@ -1,0 +1,262 @@
+// Row-store ingest and row movement kernels.
+//
+// ingest_rows replaces index.add -> IndexFlatCodes::add (a host memcpy in faiss) fused with
+// faiss.normalize_L2 -> fvec_renorm_L2 (faiss/utils/distances.cpp): per row nr = sum x^2; if
+// nr > 0 the row is scaled by 1/sqrtf(nr), zero rows stay zero.  Reached from langchain
+// FAISS.__add (add_documents at
+// /root/reference/RetrievalAugmentedGeneration/examples/nvidia_api_catalog/chains.py:61,
+// from_documents at /root/reference/examples/5_mins_rag_no_gpu/main.py:90).
+// One warp per row: 128-bit loads, shuffle-reduced sum of squares, scale, store as fp32 or
+// bf16 into the 512-byte-pitched row store together with the squared norm of the stored row.
+// Algorithmic bytes per row: 4 d read + (4 | 2) d written.
+//
+// gather_rows replaces index.reconstruct (IndexFlatCodes::reconstruct); copy_rows_indexed is
+// the mover behind index.remove_ids (IndexFlatCodes::remove_ids compaction).
+#include "b2_common.cuh"
+#include "b2_kernels.h"
+
+namespace b2 {
+
+constexpr int kIngestWarps = 8;
+constexpr int kIngestThreads = kIngestWarps * kWarp;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) v += __shfl_xor_sync(kFull, v, s);
+    return v;
+}
+
+// VEC: rows are 16-byte aligned and d % 4 == 0.  REGS: the row fits 8 float4 per lane (d <= 1024).
+template <bool VEC, bool REGS, bool BF16>
+__global__ void __launch_bounds__(kIngestThreads) ingest_kernel(const float* src, int64_t n, int d,
+                                                               size_t src_pitch_elems, char* dst,
+                                                               size_t pitch_bytes, int pitch_elems, bool normalize,
+                                                               float* __restrict__ norms) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp0 = (int64_t)blockIdx.x * kIngestWarps + (threadIdx.x >> 5);
+    const int64_t wstride = (int64_t)gridDim.x * kIngestWarps;
+    for (int64_t row = warp0; row < n; row += wstride) {
+        const float* s = src + row * src_pitch_elems;
+        char* o = dst + row * pitch_bytes;
+        float ss = 0.f;
+        float4 keep[REGS ? 8 : 1];
+        if (VEC) {
+            const float4* s4 = reinterpret_cast<const float4*>(s);
+            const int nv = d >> 2;
+            if (REGS) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int c = j * 32 + lane;
+                    keep[j] = (c < nv) ? s4[c] : make_float4(0.f, 0.f, 0.f, 0.f);
+                    ss = fmaf(keep[j].x, keep[j].x, ss);
+                    ss = fmaf(keep[j].y, keep[j].y, ss);
+                    ss = fmaf(keep[j].z, keep[j].z, ss);
+                    ss = fmaf(keep[j].w, keep[j].w, ss);
+                }
+            } else {
+                for (int c = lane; c < nv; c += 32) {
+                    const float4 v = s4[c];
+                    ss = fmaf(v.x, v.x, ss);
+                    ss = fmaf(v.y, v.y, ss);
+                    ss = fmaf(v.z, v.z, ss);
+                    ss = fmaf(v.w, v.w, ss);
+                }
+            }
+        } else {
+            for (int c = lane; c < d; c += 32) ss = fmaf(s[c], s[c], ss);
+        }
+        const float nr = warp_sum(ss);
+        const float scale = (normalize && nr > 0.f) ? (1.0f / sqrtf(nr)) : 1.0f;
+
+        float ss2 = 0.f;
+        if (VEC) {
+            const float4* s4 = reinterpret_cast<const float4*>(s);
+            const int nv = d >> 2;
+            const int nvp = pitch_elems >> 2;
+            auto put = [&](int c, float4 v) {
+                v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale;
+                if (BF16) {
+                    __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+                    const float2 fa = __bfloat1622float2(a), fb = __bfloat1622float2(b);
+                    ss2 = fmaf(fa.x, fa.x, ss2); ss2 = fmaf(fa.y, fa.y, ss2);
+                    ss2 = fmaf(fb.x, fb.x, ss2); ss2 = fmaf(fb.y, fb.y, ss2);
+                    uint2 w;
+                    w.x = *reinterpret_cast<uint32_t*>(&a);
+                    w.y = *reinterpret_cast<uint32_t*>(&b);
+                    reinterpret_cast<uint2*>(o)[c] = w;
+                } else {
+                    ss2 = fmaf(v.x, v.x, ss2); ss2 = fmaf(v.y, v.y, ss2);
+                    ss2 = fmaf(v.z, v.z, ss2); ss2 = fmaf(v.w, v.w, ss2);
+                    reinterpret_cast<float4*>(o)[c] = v;
+                }
+            };
+            if (REGS) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int c = j * 32 + lane;
+                    if (c < nvp) put(c, keep[j]);  // keep[j] is already zero past d
+                }
+            } else {
+                for (int c = lane; c < nvp; c += 32) put(c, (c < nv) ? s4[c] : make_float4(0.f, 0.f, 0.f, 0.f));
+            }
+        } else {
+            for (int c = lane; c < pitch_elems; c += 32) {
+                float v = (c < d) ? s[c] * scale : 0.f;
+                if (BF16) {
+                    const __nv_bfloat16 b = __float2bfloat16_rn(v);
+                    v = __bfloat162float(b);
+                    reinterpret_cast<__nv_bfloat16*>(o)[c] = b;
+                } else {
+                    reinterpret_cast<float*>(o)[c] = v;
+                }
+                ss2 = fmaf(v, v, ss2);
+            }
+        }
+        ss2 = warp_sum(ss2);
+        if (norms != nullptr && lane == 0) norms[row] = ss2;
+    }
+}
+
+template <bool BF16>
+static int launch_ingest(const float* src, int64_t n, int d, size_t src_pitch_elems, void* dst, size_t pitch_bytes,
+                         bool normalize, float* norms, cudaStream_t stream) {
+    if (n <= 0) return B2_OK;
+    const int pitch_elems = (int)(pitch_bytes / (BF16 ? 2 : 4));
+    const bool vec = (d % 4 == 0) && (src_pitch_elems % 4 == 0) && ((reinterpret_cast<uintptr_t>(src) & 15) == 0) &&
+                     ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) && (pitch_bytes % 16 == 0) &&
+                     (pitch_elems % 4 == 0);
+    const bool regs = vec && pitch_elems <= 1024;
+    long long blocks = (n + kIngestWarps - 1) / kIngestWarps;
+    if (blocks > 148LL * 32) blocks = 148LL * 32;
+    char* o = static_cast<char*>(dst);
+    if (vec && regs)
+        ingest_kernel<true, true, BF16><<<(int)blocks, kIngestThreads, 0, stream>>>(src, n, d, src_pitch_elems, o,
+                                                                                  pitch_bytes, pitch_elems, normalize, norms);
+    else if (vec)
+        ingest_kernel<true, false, BF16><<<(int)blocks, kIngestThreads, 0, stream>>>(src, n, d, src_pitch_elems, o,
+                                                                                   pitch_bytes, pitch_elems, normalize, norms);
+    else
+        ingest_kernel<false, false, BF16><<<(int)blocks, kIngestThreads, 0, stream>>>(src, n, d, src_pitch_elems, o,
+                                                                                    pitch_bytes, pitch_elems, normalize, norms);
+    B2_AFTER_LAUNCH();
+    return B2_OK;
+}
+
+int ingest_rows(const float* src, int64_t n, int d, void* dst, size_t pitch_bytes, int dtype, bool normalize,
+                float* norms, cudaStream_t stream) {
+    if (dtype == B2_DTYPE_BF16) return launch_ingest<true>(src, n, d, (size_t)d, dst, pitch_bytes, normalize, norms, stream);
+    return launch_ingest<false>(src, n, d, (size_t)d, dst, pitch_bytes, normalize, norms, stream);
+}
+
+int normalize_rows_inplace(float* x, int64_t n, int d, cudaStream_t stream) {
+    // dense in place: destination pitch == source pitch == d floats, no padding columns
+    if (n <= 0) return B2_OK;
+    const bool vec = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
+    long long blocks = (n + kIngestWarps - 1) / kIngestWarps;
+    if (blocks > 148LL * 32) blocks = 148LL * 32;
+    char* o = reinterpret_cast<char*>(x);
+    if (vec && d <= 1024)
+        ingest_kernel<true, true, false><<<(int)blocks, kIngestThreads, 0, stream>>>(x, n, d, (size_t)d, o, (size_t)d * 4, d, true, nullptr);
+    else if (vec)
+        ingest_kernel<true, false, false><<<(int)blocks, kIngestThreads, 0, stream>>>(x, n, d, (size_t)d, o, (size_t)d * 4, d, true, nullptr);
+    else
+        ingest_kernel<false, false, false><<<(int)blocks, kIngestThreads, 0, stream>>>(x, n, d, (size_t)d, o, (size_t)d * 4, d, true, nullptr);
+    B2_AFTER_LAUNCH();
+    return B2_OK;
+}
+
+// ------------------------------------------------------------------ gather (reconstruct)
+__global__ void __launch_bounds__(256) gather_rows_kernel(const char* __restrict__ rows, int64_t ntotal,
+                                                          size_t pitch_bytes, int d, bool bf16,
+                                                          const int64_t* __restrict__ ids, int64_t n,
+                                                          float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (w >= n) return;
+    const int64_t id = ids[w];
+    float* o = out + w * (int64_t)d;
+    if (id < 0 || id >= ntotal) {
+        for (int c = lane; c < d; c += 32) o[c] = 0.f;
+        return;
+    }
+    const char* r = rows + (size_t)id * pitch_bytes;
+    if (bf16) {
+        const __nv_bfloat16* rb = reinterpret_cast<const __nv_bfloat16*>(r);
+        for (int c = lane; c < d; c += 32) o[c] = __bfloat162float(rb[c]);
+    } else {
+        const float* rf = reinterpret_cast<const float*>(r);
+        for (int c = lane; c < d; c += 32) o[c] = rf[c];
+    }
+}
+
+int gather_rows(const void* rows, int64_t ntotal, size_t pitch_bytes, int d, int dtype, const int64_t* ids, int64_t n,
+                float* out, cudaStream_t stream) {
+    if (n <= 0) return B2_OK;
+    const long long blocks = (n + 7) / 8;
+    gather_rows_kernel<<<(unsigned)blocks, 256, 0, stream>>>(static_cast<const char*>(rows), ntotal, pitch_bytes, d,
+                                                            dtype == B2_DTYPE_BF16, ids, n, out);
+    B2_AFTER_LAUNCH();
+    return B2_OK;
+}
+
+// ------------------------------------------------------------------ compaction mover
+// tmp row j  <-  row src_of_dst[j]  (raw 16-byte copies), and the same for norms.
+__global__ void __launch_bounds__(256) copy_rows_indexed_kernel(const char* __restrict__ rows, size_t pitch_bytes,
+                                                                const float* __restrict__ norms,
+                                                                const int64_t* __restrict__ src_idx, int64_t n,
+                                                                char* __restrict__ tmp_rows,
+                                                                float* __restrict__ tmp_norms) {
+    const int lane = threadIdx.x & 31;
+    const int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (w >= n) return;
+    const int64_t s = src_idx[w];
+    const uint4* a = reinterpret_cast<const uint4*>(rows + (size_t)s * pitch_bytes);
+    uint4* b = reinterpret_cast<uint4*>(tmp_rows + (size_t)w * pitch_bytes);
+    const int nv = (int)(pitch_bytes >> 4);
+    for (int c = lane; c < nv; c += 32) b[c] = a[c];
+    if (lane == 0) tmp_norms[w] = norms[s];
+}
+
+// Moves rows so that dst row (first_moved + j) = old row src_of_dst[j], j < n_dst, where
+// src_of_dst is increasing and src_of_dst[j] >= first_moved + j.  Chunked through a
+// temporary so that no row is overwritten before it has been read.
+int compact_rows(void* rows, size_t pitch_bytes, float* norms, const int64_t* src_of_dst, int64_t n_dst,
+                 int64_t first_moved, cudaStream_t stream) {
+    if (n_dst <= 0) return B2_OK;
+    int64_t chunk = (int64_t)((64ull << 20) / pitch_bytes);
+    if (chunk < 1) chunk = 1;
+    if (chunk > n_dst) chunk = n_dst;
+    char* tmp = nullptr;
+    float* tmpn = nullptr;
+    B2_CUDA_TRY(cudaMallocAsync(&tmp, (size_t)chunk * pitch_bytes, stream));
+    cudaError_t e = cudaMallocAsync(&tmpn, (size_t)chunk * sizeof(float), stream);
+    if (e != cudaSuccess) {
+        cudaFreeAsync(tmp, stream);
+        set_error("compact_rows: %s", cudaGetErrorString(e));
+        return B2_ERR_OOM;
+    }
+    char* base = static_cast<char*>(rows);
+    int rc = B2_OK;
+    for (int64_t c0 = 0; c0 < n_dst && rc == B2_OK; c0 += chunk) {
+        const int64_t m = (n_dst - c0 < chunk) ? (n_dst - c0) : chunk;
+        copy_rows_indexed_kernel<<<(unsigned)((m + 7) / 8), 256, 0, stream>>>(base, pitch_bytes, norms,
+                                                                            src_of_dst + c0, m, tmp, tmpn);
+        B2_COUNT_LAUNCH();
+        e = cudaGetLastError();
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(base + (size_t)(first_moved + c0) * pitch_bytes, tmp, (size_t)m * pitch_bytes,
+                                cudaMemcpyDeviceToDevice, stream);
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(norms + first_moved + c0, tmpn, (size_t)m * sizeof(float), cudaMemcpyDeviceToDevice,
+                                stream);
+        if (e != cudaSuccess) {
+            set_error("compact_rows: %s", cudaGetErrorString(e));
+            rc = B2_ERR_CUDA;
+        }
+    }
+    cudaFreeAsync(tmp, stream);
+    cudaFreeAsync(tmpn, stream);
+    return rc;
+}
+
+}  // namespace b2

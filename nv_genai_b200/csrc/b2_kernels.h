@@ -1,0 +1,45 @@
+// Internal launch interfaces between the translation units of libb2flat.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b2 {
+
+// b2_scan.cu ---------------------------------------------------------------
+size_t scan_smem_bytes(int nq_tile, int nchunks, bool bf16, int kpad);
+int scan_pass(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* q_dev,
+              int nq_valid, int nq_tile, int k, int num_sms, cudaStream_t stream, uint64_t** partial, int* grid);
+
+void prof_enable(int on);
+int prof_read(double* ms, int64_t* n, int reset);
+
+// b2_merge.cu --------------------------------------------------------------
+// partial: [nq][nlists][k] candidates (pos = local row id) -> D/I [nq][k] with I = id_base + pos.
+int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metric, int64_t id_base, float* D,
+                   int64_t* I, size_t out_stride, cudaStream_t stream);
+// (D_parts, I_parts): [nparts][nq][k] -> [nq][k]
+int merge_shards(int metric, int nq, int k, int nparts, const float* D_parts, const int64_t* I_parts, float* D,
+                 int64_t* I, cudaStream_t stream);
+
+// b2_ingest.cu -------------------------------------------------------------
+// src: n x d fp32 dense (device) -> dst rows at `pitch_bytes`, fp32 or bf16, padding zeroed;
+// optional L2 normalisation; norms[i] = sum of squares of the STORED row.
+int ingest_rows(const float* src, int64_t n, int d, void* dst, size_t pitch_bytes, int dtype, bool normalize,
+                float* norms, cudaStream_t stream);
+int normalize_rows_inplace(float* x, int64_t n, int d, cudaStream_t stream);
+// out[j] = row ids[j] as fp32 (n x d dense); negative / out-of-range ids give zero rows
+int gather_rows(const void* rows, int64_t ntotal, size_t pitch_bytes, int d, int dtype, const int64_t* ids, int64_t n,
+                float* out, cudaStream_t stream);
+// keep[i] != 0 rows are compacted to the front preserving order; dst_index = exclusive prefix of keep
+int compact_rows(void* rows, size_t pitch_bytes, float* norms, const int64_t* src_of_dst, int64_t n_dst,
+                 int64_t first_moved, cudaStream_t stream);
+
+// b2_mmr.cu ----------------------------------------------------------------
+int mmr_select(const float* q, int d, int nq, const float* cand_rows /*[nq][fetch_k][d]*/, const int64_t* cand_ids,
+               const float* cand_scores, int fetch_k, int k, float lambda_mult, int64_t* out_ids, float* out_scores,
+               cudaStream_t stream);
+
+// b2_synth.cu --------------------------------------------------------------
+int synth_fill(float* out, int64_t row0, int64_t nrows, int d, uint64_t seed, cudaStream_t stream);
+
+}  // namespace b2

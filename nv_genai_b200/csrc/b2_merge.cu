@@ -1,0 +1,121 @@
+// Block merge of partial top-k lists -> final (D, I).
+//
+// Replaces the tail of faiss's result handlers (HeapResultHandler::end -> heap_reorder,
+// faiss/impl/ResultHandler.h, faiss/utils/Heap.h): the final sort of the k survivors and the
+// -1 / +-FLT_MAX padding, reached from index.search.  The same kernel does
+// the exchange step of the row-sharded search (per-shard lists after the NCCL allgather).
+//
+// One CTA per query.  The running best `kpad` candidates sit at the front of a shared-memory
+// buffer of SORT_N u64; the rest of the buffer is refilled with the next chunk of candidates
+// and the whole buffer is bitonic-sorted, until the input is consumed.
+#include "b2_common.cuh"
+#include "b2_kernels.h"
+
+namespace b2 {
+
+constexpr int kMergeThreads = 512;
+
+__device__ __forceinline__ void emit_result(uint64_t c, int metric, int64_t id_base, float* D, int64_t* I) {
+    const uint32_t pos = cand_pos(c);
+    if (pos == kNoPos) {
+        *I = -1;
+        *D = (metric == B2_METRIC_IP) ? -FLT_MAX : FLT_MAX;
+    } else {
+        *I = id_base + (int64_t)pos;
+        const float key = cand_key(c);
+        *D = (metric == B2_METRIC_IP) ? key : -key;
+    }
+}
+
+__global__ void __launch_bounds__(kMergeThreads) merge_partials_kernel(const uint64_t* __restrict__ partial,
+                                                                      int total, int k, int kpad, int sort_n,
+                                                                      int metric, int64_t id_base, float* D,
+                                                                      int64_t* I, size_t out_stride) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw);
+    const int q = blockIdx.x, tid = threadIdx.x;
+    const uint64_t* in = partial + (size_t)q * total;
+    const int cap = sort_n - kpad;
+    for (int i = tid; i < kpad; i += kMergeThreads) buf[i] = B2_SENTINEL;
+    for (int off = 0; off < total; off += cap) {
+        for (int i = tid; i < cap; i += kMergeThreads) buf[kpad + i] = (off + i < total) ? in[off + i] : B2_SENTINEL;
+        block_bitonic_desc(buf, sort_n, tid, kMergeThreads);
+    }
+    __syncthreads();
+    for (int i = tid; i < k; i += kMergeThreads)
+        emit_result(buf[i], metric, id_base, D + (size_t)q * out_stride + i, I + (size_t)q * out_stride + i);
+}
+
+int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metric, int64_t id_base, float* D,
+                   int64_t* I, size_t out_stride, cudaStream_t stream) {
+    const int kpad = next_pow2(k < 32 ? 32 : k);
+    const int total = nlists * k;
+    int sort_n = 2 * kpad;
+    const int want = next_pow2(total + kpad);
+    while (sort_n < want && sort_n < 4096) sort_n <<= 1;
+    const size_t smem = (size_t)sort_n * sizeof(uint64_t);
+    merge_partials_kernel<<<nq, kMergeThreads, smem, stream>>>(partial, total, k, kpad, sort_n, metric, id_base, D, I,
+                                                               out_stride);
+    B2_AFTER_LAUNCH();
+    return B2_OK;
+}
+
+// ---------------------------------------------------------------- shard lists
+// Candidate position = part * k + rank: parts are in global id order and each part's list
+// is already ordered lowest-id-first among equal keys, so "lower position first" is exactly
+// "lower global id first".
+__global__ void __launch_bounds__(kMergeThreads) merge_shards_kernel(int metric, int k, int nparts, int nq,
+                                                                    const float* __restrict__ Dp,
+                                                                    const int64_t* __restrict__ Ip, int sort_n,
+                                                                    float* D, int64_t* I) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw);
+    const int q = blockIdx.x, tid = threadIdx.x;
+    const int total = nparts * k;
+    for (int i = tid; i < sort_n; i += kMergeThreads) {
+        uint64_t c = B2_SENTINEL;
+        if (i < total) {
+            const int part = i / k, r = i - part * k;
+            const size_t src = ((size_t)part * nq + q) * k + r;
+            const int64_t id = Ip[src];
+            if (id >= 0) {
+                const float d = Dp[src];
+                c = pack_cand(metric == B2_METRIC_IP ? d : -d, (uint32_t)i);
+            }
+        }
+        buf[i] = c;
+    }
+    block_bitonic_desc(buf, sort_n, tid, kMergeThreads);
+    for (int i = tid; i < k; i += kMergeThreads) {
+        const uint64_t c = buf[i];
+        const uint32_t pos = cand_pos(c);
+        float* Dq = D + (size_t)q * k + i;
+        int64_t* Iq = I + (size_t)q * k + i;
+        if (pos == kNoPos) {
+            *Iq = -1;
+            *Dq = (metric == B2_METRIC_IP) ? -FLT_MAX : FLT_MAX;
+        } else {
+            const int part = pos / k, r = pos - part * k;
+            const size_t src = ((size_t)part * nq + q) * k + r;
+            *Iq = Ip[src];
+            *Dq = Dp[src];
+        }
+    }
+}
+
+int merge_shards(int metric, int nq, int k, int nparts, const float* D_parts, const int64_t* I_parts, float* D,
+                 int64_t* I, cudaStream_t stream) {
+    const long long total = (long long)nparts * k;
+    const int sort_n = next_pow2((int)(total < 32 ? 32 : total));
+    const size_t smem = (size_t)sort_n * sizeof(uint64_t);
+    if (smem > 200 * 1024) {
+        set_error("merge_shards: nparts*k = %lld too large", total);
+        return B2_ERR_UNSUPPORTED;
+    }
+    B2_CUDA_TRY(cudaFuncSetAttribute(merge_shards_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    merge_shards_kernel<<<nq, kMergeThreads, smem, stream>>>(metric, k, nparts, nq, D_parts, I_parts, sort_n, D, I);
+    B2_AFTER_LAUNCH();
+    return B2_OK;
+}
+
+}  // namespace b2

@@ -1,0 +1,114 @@
+"""Row-sharded exact search across GPUs: one process per GPU, torch.distributed for plumbing.
+
+The reference has no multi-GPU code; this is the partitioning the path
+admits: rank g of G holds one contiguous block of rows, queries are made
+visible on every rank, each rank runs the single-GPU scan, the per-shard sorted
+`(score, id)` lists are exchanged with ONE all-gather (NCCL over NVLink on GPUs) and merged
+on the device by `b2_merge_shard_lists`.  Top-k is a decomposable reduction, so the result
+equals the single-GPU result bit for bit: the same kernels score each row, and the merge
+orders equal scores lowest-global-id first because shards are in id order.
+
+The local index and the merge are injectable so that the host logic (bounds, bases,
+exchange layout) is testable with the gloo backend on CPU; the defaults are the CUDA ones
+and there is no CPU fallback in the product path.
+"""
+from __future__ import annotations
+
+from typing import Any, Callable, Optional, Tuple
+
+
+def shard_bounds(n: int, world: int, rank: int) -> Tuple[int, int]:
+    """Contiguous block partition: rank r holds rows [lo, hi); blocks differ by at most one row."""
+    base, rem = divmod(int(n), int(world))
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+class ShardedFlatIndex:
+    """IndexFlat sharded by rows over the ranks of a torch.distributed process group."""
+
+    def __init__(self, d: int, metric: int, dtype: str = "float32", group: Any = None, device: Any = None,
+                 local_index: Any = None, merge_fn: Optional[Callable] = None):
+        import torch
+        import torch.distributed as dist
+
+        self._torch, self._dist = torch, dist
+        if not dist.is_initialized():
+            raise RuntimeError("ShardedFlatIndex needs an initialised torch.distributed process group")
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.d, self.metric = int(d), int(metric)
+        if local_index is None:
+            from .index import IndexFlat
+
+            local_index = IndexFlat(d, metric, dtype, device)
+        self.local = local_index
+        if merge_fn is None:
+            from .index import merge_shard_lists
+
+            merge_fn = merge_shard_lists
+        self._merge = merge_fn
+        self.bases = [0] * (self.world + 1)  # bases[g] = global id of shard g's first row
+
+    # ------------------------------------------------------------------ build
+    def _comm_device(self):
+        t = self._torch
+        if self._dist.get_backend(self.group) == "nccl":
+            return t.device("cuda", getattr(self.local, "device", t.cuda.current_device()))
+        return t.device("cpu")
+
+    def _refresh_bases(self) -> None:
+        t, dist = self._torch, self._dist
+        mine = t.tensor([int(self.local.ntotal)], dtype=t.int64, device=self._comm_device())
+        counts = [t.zeros_like(mine) for _ in range(self.world)]
+        dist.all_gather(counts, mine, group=self.group)
+        acc = 0
+        self.bases = [0]
+        for c in counts:
+            acc += int(c.item())
+            self.bases.append(acc)
+
+    def add_local(self, x, normalize: bool = False) -> None:
+        """Append this rank's own rows to its shard; global ids follow rank order.  Collective."""
+        self.local.add(x, normalize=normalize)
+        self._refresh_bases()
+
+    def add_global(self, x, normalize: bool = False) -> None:
+        """Every rank passes the SAME [n, d] block; each keeps its contiguous slice.  Collective.
+
+        Only valid while the shards are still empty or when called in the same order on all ranks for a store
+        that is rebuilt; rows of one call are spread over all ranks, so ids of a later call do not continue the
+        earlier ones contiguously (use add_local for incremental growth)."""
+        if any(b != 0 for b in self.bases):
+            raise RuntimeError("add_global on a non-empty sharded index would break the id order; use add_local")
+        lo, hi = shard_bounds(x.shape[0], self.world, self.rank)
+        self.local.add(x[lo:hi], normalize=normalize)
+        self._refresh_bases()
+
+    @property
+    def ntotal(self) -> int:
+        return self.bases[-1]
+
+    # ------------------------------------------------------------------ search
+    def search(self, q, k: int, replicated: bool = True, src: int = 0):
+        """Global top-k on every rank.  q: [nq, d] tensor on the communication device; if not
+        `replicated`, rank `src` broadcasts it first.  Returns (D [nq, k] fp32, I [nq, k] int64 global ids)."""
+        t, dist = self._torch, self._dist
+        if not replicated:
+            dist.broadcast(q, src=src, group=self.group)
+        D_loc, I_loc = self.local.search(q, k)
+        if not isinstance(D_loc, t.Tensor):
+            D_loc, I_loc = t.from_numpy(D_loc), t.from_numpy(I_loc)
+        base = self.bases[self.rank]
+        I_glob = t.where(I_loc >= 0, I_loc + base, I_loc)
+        nq = D_loc.shape[0]
+        # one exchange: [ I (int64) | D (fp32) ] packed as bytes, 12 B per result
+        packed = t.cat([I_glob.contiguous().view(t.uint8).reshape(-1), D_loc.contiguous().view(t.uint8).reshape(-1)])
+        flat_out = t.empty(self.world * packed.numel(), dtype=t.uint8, device=packed.device)
+        dist.all_gather_into_tensor(flat_out, packed, group=self.group)
+        gathered = flat_out.view(self.world, packed.numel())
+        nb_i = nq * k * 8
+        I_parts = gathered[:, :nb_i].contiguous().view(t.int64).reshape(self.world, nq, k)
+        D_parts = gathered[:, nb_i:].contiguous().view(t.float32).reshape(self.world, nq, k)
+        return self._merge(self.metric, D_parts, I_parts)

@@ -1,0 +1,71 @@
+"""CPU: the C-ABI library loads without a GPU and exports every symbol include/b2_flat.h declares."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "b2_flat.h")
+
+
+def declared_symbols():
+    src = open(HEADER).read()
+    return sorted(set(re.findall(r"B2_API\s+[\w\s\*]+?\b(b2_\w+)\s*\(", src)))
+
+
+def test_header_declares_the_expected_entry_points():
+    syms = declared_symbols()
+    for must in ("b2_index_create", "b2_index_add", "b2_index_search", "b2_index_mmr", "b2_merge_shard_lists",
+                 "b2_index_remove_ids", "b2_index_merge_from", "b2_index_reconstruct_batch", "b2_last_error"):
+        assert must in syms
+    text = open(HEADER).read()
+    assert "common/utils.py:217" in text and "main.py:90" in text  # every entry cites the interface it replaces
+
+
+def test_library_exports_every_declared_symbol():
+    from nv_genai_b200 import _native
+
+    lib = ctypes.CDLL(_native.SO_PATH)
+    for name in declared_symbols():
+        assert hasattr(lib, name), f"{name} declared in b2_flat.h but not exported"
+    assert sorted(_native.SYMBOLS) == declared_symbols()
+    assert "sm_100a" in _native.version()
+
+
+def test_no_cpu_fallback_without_a_gpu():
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from nv_genai_b200 import _native as N
+    from nv_genai_b200 import IndexFlatL2
+
+    h = ctypes.c_void_p()
+    st = N.lib.b2_index_create(8, N.METRIC_L2, N.DTYPE_F32, 0, ctypes.byref(h))
+    assert st == N.B2_ERR_NO_DEVICE and not h.value
+    assert b"no CPU path" in N.lib.b2_last_error()
+    with pytest.raises(N.B2Error):
+        IndexFlatL2(8)
+
+
+def test_argument_validation_happens_before_any_device_work():
+    from nv_genai_b200 import _native as N
+
+    h = ctypes.c_void_p()
+    assert N.lib.b2_index_create(0, N.METRIC_L2, N.DTYPE_F32, 0, ctypes.byref(h)) == N.B2_ERR_INVALID
+    assert N.lib.b2_index_create(8, 7, N.DTYPE_F32, 0, ctypes.byref(h)) == N.B2_ERR_INVALID
+    assert N.lib.b2_index_create(8, N.METRIC_L2, 9, 0, ctypes.byref(h)) == N.B2_ERR_INVALID
+    assert N.lib.b2_index_search(None, 1, None, 0, 1, None, None, 0, None) == N.B2_ERR_INVALID
+    assert N.lib.b2_index_ntotal(None) == -1
+    assert N.lib.b2_index_destroy(None) == N.B2_OK
+
+
+def test_product_package_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "nv_genai_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", text, re.M), f
+                assert "flat_oracle" not in text.replace("oracle/flat_oracle.c b2o_synth_fill", ""), f
