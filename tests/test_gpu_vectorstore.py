@@ -99,8 +99,12 @@ def test_normalize_l2_store_and_mmr_and_async():
     assert s[0][0].page_content == TEXTS[3] and abs(float(s[0][1])) < 1e-6 and float(s[1][1]) <= 4.0
     docs = vs.max_marginal_relevance_search(TEXTS[11], k=4, fetch_k=20)
     assert len(docs) == 4 and docs[0].page_content == TEXTS[11]
+    # a query that is NOT a stored row: with a self-query lambda*cos(q,e) - (1-lambda)*cos(e,e_self) is
+    # identically zero for lambda = 0.5 and rounding noise alone would pick the order
+    probe = "a question that was never ingested"
+    docs = vs.max_marginal_relevance_search(probe, k=4, fetch_k=20)
     x = vs.index.reconstruct_n(0, 300)
-    want, _ = flat.mmr_search(x, np.array(emb.embed_query(TEXTS[11]), np.float32), 4, 20, 0.5, flat.METRIC_L2)
+    want, _ = flat.mmr_search(x, np.array(emb.embed_query(probe), np.float32), 4, 20, 0.5, flat.METRIC_L2)
     assert [d.page_content for d in docs] == [TEXTS[i] for i in want]
     filt = vs.max_marginal_relevance_search(TEXTS[11], k=3, fetch_k=20, filter=lambda m: True)
     assert len(filt) == 3 and filt[0].page_content == TEXTS[11]
