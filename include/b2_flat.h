@@ -101,6 +101,28 @@ B2_API int b2_index_add(b2_index* h, int64_t n, const float* x, int x_where, uns
 B2_API int b2_index_search(b2_index* h, int64_t nq, const float* q, int q_where, int k, float* D, int64_t* I,
                     int out_where, void* stream);
 
+/* No counterpart in the reference: b2_index_search for callers that must not allocate.
+ * A service that gives all of HBM to its own memory manager at start-up, or a request loop
+ * that cannot risk the device-wide synchronisation an allocator call may cause, cannot use
+ * b2_index_search, which takes scratch from cudaMallocAsync.  This variant runs the same scan
+ * and merge kernels with the per-CTA partial lists in a fixed 2 MiB array inside the library
+ * image (held by every GPU that loads the library, until the process exits) and calls no
+ * cudaMalloc / cudaFree / allocating routine.
+ *   - q, D, I are DEVICE pointers (nq x d fp32, nq x k fp32, nq x k int64); nq <= 16;
+ *     work is enqueued on `stream`, nothing is synchronised.
+ *   - limit: query tile (nq rounded up to a power of two) x CTAs launched x k must not exceed
+ *     256 Ki candidates, otherwise B2_ERR_UNSUPPORTED (on a 148-SM B200: nq = 16 with k = 100
+ *     and nq = 1 with k = 10 fit; nq = 1 with k = 1024 does not).
+ *   - the first call on each device looks up the array's device address and the kernel's
+ *     launch attributes; make that call before starting any stream capture.
+ *   - all calls share the one array and it keeps the last call's contents.  Nothing in it has
+ *     to start at zero (every slot a call reads, the same call has written first), but two
+ *     calls whose kernels overlap on the GPU (different streams, or threads) race on it:
+ *     serialise them.
+ * Results are identical to b2_index_search. */
+B2_API int b2_index_search_static(b2_index* h, int64_t nq, const float* q_dev, int k, float* D_dev, int64_t* I_dev,
+                           void* stream);
+
 /* Replaces index.reconstruct(i) (used by langchain's MMR search), batched:
  * out[j] = row ids[j] as fp32 (n x d).  Negative ids give zero rows. */
 B2_API int b2_index_reconstruct_batch(b2_index* h, int64_t n, const int64_t* ids, int ids_where, float* out,

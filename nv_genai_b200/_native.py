@@ -22,7 +22,7 @@ MAX_K = 2048
 # Every symbol include/b2_flat.h declares (tests check the library exports all of them).
 SYMBOLS = [
     "b2_index_create", "b2_index_destroy", "b2_index_ntotal", "b2_index_d", "b2_index_metric", "b2_index_dtype",
-    "b2_index_device", "b2_index_add", "b2_index_search", "b2_index_reconstruct_batch", "b2_index_remove_ids",
+    "b2_index_device", "b2_index_add", "b2_index_search", "b2_index_search_static", "b2_index_reconstruct_batch", "b2_index_remove_ids",
     "b2_index_merge_from", "b2_index_reset", "b2_index_mmr", "b2_merge_shard_lists", "b2_normalize_l2",
     "b2_synth_fill", "b2_launch_count", "b2_launch_count_reset", "b2_prof_enable", "b2_prof_read", "b2_last_error",
     "b2_version",
@@ -52,6 +52,8 @@ def _load() -> ctypes.CDLL:
     L.b2_index_ntotal.restype = i64
     L.b2_index_add.argtypes = [vp, i64, vp, i32, u32, vp]
     L.b2_index_search.argtypes = [vp, i64, vp, i32, i32, vp, vp, i32, vp]
+    L.b2_index_search_static.argtypes = [vp, i64, vp, i32, vp, vp, vp]
+    L.b2_index_search_static.restype = i32
     L.b2_index_reconstruct_batch.argtypes = [vp, i64, vp, i32, vp, i32, vp]
     L.b2_index_remove_ids.argtypes = [vp, i64, vp, ctypes.POINTER(i64)]
     L.b2_index_merge_from.argtypes = [vp, vp]

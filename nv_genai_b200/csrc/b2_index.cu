@@ -264,6 +264,23 @@ static int check_handle(const b2_index* h) {
     return B2_OK;
 }
 
+namespace b2 {
+int index_view_lock_shared(b2_index* h, IndexView* v) {
+    B2_TRY(check_handle(h));
+    h->mu.lock_shared();
+    v->rows = h->store.base();
+    v->ntotal = h->ntotal;
+    v->pitch = h->pitch;
+    v->d = h->d;
+    v->dtype = h->dtype;
+    v->metric = h->metric;
+    v->device = h->device;
+    v->num_sms = h->num_sms;
+    return B2_OK;
+}
+void index_unlock_shared(b2_index* h) { h->mu.unlock_shared(); }
+}  // namespace b2
+
 extern "C" {
 
 const char* b2_last_error(void) { return t_err; }

@@ -3,6 +3,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "../../include/b2_flat.h"
+
 namespace b2 {
 
 // b2_scan.cu ---------------------------------------------------------------
@@ -12,6 +14,18 @@ int scan_pass(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype,
 
 void prof_enable(int on);
 int prof_read(double* ms, int64_t* n, int reset);
+
+// b2_index.cu -------------------------------------------------------------
+// Read-only snapshot of an index handle for entry points implemented next to their kernels.
+struct IndexView {
+    const void* rows;
+    int64_t ntotal;
+    size_t pitch;
+    int d, dtype, metric, device, num_sms;
+};
+// Takes the handle's reader lock and fills *v; pair with index_unlock_shared.
+int index_view_lock_shared(b2_index* h, IndexView* v);
+void index_unlock_shared(b2_index* h);
 
 // b2_merge.cu --------------------------------------------------------------
 // partial: [nq][nlists][k] candidates (pos = local row id) -> D/I [nq][k] with I = id_base + pos.

@@ -395,3 +395,141 @@ int scan_pass(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype,
 }
 
 }  // namespace b2
+
+// =====================================================================================
+// b2_index_search_static: the same scan + merge, for callers that must not allocate.
+//
+// Some users of this library cannot let a search touch the CUDA allocator: a retrieval
+// service that hands the whole HBM to its own memory manager at start-up (any later
+// cudaMalloc / cudaMallocAsync would fail or fragment that plan), or a latency-critical
+// request loop that cannot afford the device-wide synchronisation an allocator call may
+// trigger.  b2_index_search takes its per-CTA partial top-k lists from cudaMallocAsync;
+// this variant keeps them in the fixed array below instead and therefore calls neither
+// cudaMalloc, cudaFree nor any allocating library routine.
+//
+// The array is part of the library image: every GPU that loads libb2flat.so holds these
+// 2 MiB until the process exits, whether or not this entry point is ever called.
+// =====================================================================================
+namespace b2 {
+
+constexpr size_t kStaticPartialEntries = (size_t)256 << 10;  // 256 Ki candidates x 8 B = 2 MiB
+static __device__ __align__(256) uint64_t g_static_partials[kStaticPartialEntries];
+
+// `g_static_partials` is only a stand-in on the host side: its device address has to be asked
+// for once per device, with that device current.  Cached afterwards.
+static int static_partials_ptr(int device, uint64_t** out) {
+    static std::mutex mu;
+    static uint64_t* cache[64] = {nullptr};
+    if (device < 0 || device >= 64) {
+        set_error("b2_index_search_static: device ordinal %d not supported (0..63)", device);
+        return B2_ERR_UNSUPPORTED;
+    }
+    std::lock_guard<std::mutex> lk(mu);
+    if (cache[device] == nullptr) {
+        void* p = nullptr;
+        B2_CUDA_TRY(cudaGetSymbolAddress(&p, g_static_partials));
+        cache[device] = static_cast<uint64_t*>(p);
+    }
+    *out = cache[device];
+    return B2_OK;
+}
+
+template <int METRIC, bool BF16, int NQ, int R>
+static int run_scan_static(ScanParams p, int num_sms, cudaStream_t stream, uint64_t* scratch, int* grid_out) {
+    const size_t smem = scan_smem_bytes(NQ, p.nchunks, BF16, p.kpad);
+    int grid = 0;
+    B2_TRY((launch_scan<METRIC, BF16, NQ, R>(p, num_sms, smem, stream, &grid)));
+    const size_t need = (size_t)NQ * grid * p.k;
+    if (need > kStaticPartialEntries) {
+        set_error("b2_index_search_static: query tile %d x %d CTAs x k=%d = %zu partial candidates exceed the fixed "
+                  "scratch of %zu (2 MiB); use b2_index_search",
+                  NQ, grid, p.k, need, kStaticPartialEntries);
+        return B2_ERR_UNSUPPORTED;
+    }
+    p.partial = scratch;
+    scan_topk_kernel<METRIC, BF16, NQ, R><<<grid, kScanThreads, smem, stream>>>(p);
+    B2_AFTER_LAUNCH();
+    *grid_out = grid;
+    return B2_OK;
+}
+
+template <int METRIC, bool BF16>
+static int dispatch_nq_static(int nq_tile, const ScanParams& p, int num_sms, cudaStream_t s, uint64_t* scratch, int* grid) {
+    switch (nq_tile) {
+        case 1: return run_scan_static<METRIC, BF16, 1, 4>(p, num_sms, s, scratch, grid);
+        case 2: return run_scan_static<METRIC, BF16, 2, 4>(p, num_sms, s, scratch, grid);
+        case 4: return run_scan_static<METRIC, BF16, 4, 4>(p, num_sms, s, scratch, grid);
+        case 8: return run_scan_static<METRIC, BF16, 8, 4>(p, num_sms, s, scratch, grid);
+        case 16: return run_scan_static<METRIC, BF16, 16, 4>(p, num_sms, s, scratch, grid);
+    }
+    set_error("internal: bad query tile %d", nq_tile);
+    return B2_ERR_INVALID;
+}
+
+}  // namespace b2
+
+extern "C" int b2_index_search_static(b2_index* h, int64_t nq, const float* q_dev, int k, float* D_dev, int64_t* I_dev,
+                                      void* stream_) {
+    using namespace b2;
+    if (nq < 0 || k <= 0 || (nq > 0 && (q_dev == nullptr || D_dev == nullptr || I_dev == nullptr))) {
+        set_error("b2_index_search_static: bad arguments (nq=%lld, k=%d)", (long long)nq, k);
+        return B2_ERR_INVALID;
+    }
+    if (nq > 16) {
+        set_error("b2_index_search_static: nq=%lld exceeds the 16 queries one scan pass holds", (long long)nq);
+        return B2_ERR_UNSUPPORTED;
+    }
+    if (k > B2_MAX_K) {
+        set_error("b2_index_search_static: k=%d exceeds B2_MAX_K=%d", k, B2_MAX_K);
+        return B2_ERR_UNSUPPORTED;
+    }
+    IndexView v;
+    B2_TRY(index_view_lock_shared(h, &v));
+    if (nq == 0) {
+        index_unlock_shared(h);
+        return B2_OK;
+    }
+    int prev = -1;
+    int rc = B2_OK;
+    if (cudaGetDevice(&prev) != cudaSuccess || (prev != v.device && cudaSetDevice(v.device) != cudaSuccess)) {
+        cudaGetLastError();
+        set_error("cannot select device %d", v.device);
+        rc = B2_ERR_CUDA;
+    }
+    if (rc == B2_OK) {
+        cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+        ScanParams p;
+        p.rows = static_cast<const char*>(v.rows);
+        p.n = (uint32_t)v.ntotal;
+        p.pitch_bytes = (uint32_t)v.pitch;
+        p.nchunks = (int)(v.pitch / 512);
+        p.q = q_dev;
+        p.d = v.d;
+        p.nq_valid = (int)nq;
+        p.k = k;
+        p.kpad = next_pow2(k < 32 ? 32 : k);
+        p.partial = nullptr;
+        const bool bf16 = v.dtype == B2_DTYPE_BF16;
+        const int tile = next_pow2((int)nq);
+        uint64_t* scratch = nullptr;
+        int grid = 0;
+        if (scan_smem_bytes(tile, p.nchunks, bf16, p.kpad) > 200 * 1024) {
+            set_error("b2_index_search_static: %lld queries with d=%d, k=%d do not fit one scan pass; use b2_index_search",
+                      (long long)nq, v.d, k);
+            rc = B2_ERR_UNSUPPORTED;
+        }
+        if (rc == B2_OK) rc = static_partials_ptr(v.device, &scratch);
+        if (rc == B2_OK) {
+            if (v.metric == B2_METRIC_IP)
+                rc = bf16 ? dispatch_nq_static<B2_METRIC_IP, true>(tile, p, v.num_sms, stream, scratch, &grid)
+                          : dispatch_nq_static<B2_METRIC_IP, false>(tile, p, v.num_sms, stream, scratch, &grid);
+            else
+                rc = bf16 ? dispatch_nq_static<B2_METRIC_L2, true>(tile, p, v.num_sms, stream, scratch, &grid)
+                          : dispatch_nq_static<B2_METRIC_L2, false>(tile, p, v.num_sms, stream, scratch, &grid);
+        }
+        if (rc == B2_OK) rc = merge_partials(scratch, (int)nq, grid, k, v.metric, 0, D_dev, I_dev, (size_t)k, stream);
+    }
+    if (prev >= 0 && prev != v.device) cudaSetDevice(prev);
+    index_unlock_shared(h);
+    return rc;
+}

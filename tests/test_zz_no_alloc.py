@@ -1,0 +1,121 @@
+"""GPU: b2_index_search_static — the search for callers that must not allocate.
+
+Some users of the library cannot let a search reach the CUDA allocator: a service that hands
+all of HBM to its own memory manager at start-up, or a request loop that cannot risk the
+device-wide synchronisation an allocator call may cause.  For them the library offers one
+extra entry point that keeps the scan kernel's per-CTA partial lists in a fixed 2 MiB array
+inside the library image instead of taking them from cudaMallocAsync.
+
+This file checks, through the C ABI only, that the entry point returns exactly what
+b2_index_search returns (the same kernels run, so the comparison is bit for bit), on two calls
+in a row — the second call reuses the array with the first call's contents still in it — and
+that it refuses sizes beyond its fixed scratch with a clear error.  It is named test_zz_* so
+that pytest collects it after every other test file.
+"""
+import ctypes
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev_ptr(t):
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def _search_pair(N, h, q, k, stream):
+    """(D, I) from b2_index_search and from b2_index_search_static for the same device queries."""
+    import torch
+
+    nq = q.shape[0]
+    D0 = torch.empty((nq, k), dtype=torch.float32, device=q.device)
+    I0 = torch.empty((nq, k), dtype=torch.int64, device=q.device)
+    D1 = torch.full((nq, k), float("nan"), dtype=torch.float32, device=q.device)
+    I1 = torch.full((nq, k), -7, dtype=torch.int64, device=q.device)
+    N.check(N.lib.b2_index_search(h, nq, _dev_ptr(q), N.DEVICE, k, _dev_ptr(D0), _dev_ptr(I0), N.DEVICE, stream))
+    N.check(N.lib.b2_index_search_static(h, nq, _dev_ptr(q), k, _dev_ptr(D1), _dev_ptr(I1), stream))
+    torch.cuda.synchronize()
+    return D0.cpu().numpy(), I0.cpu().numpy(), D1.cpu().numpy(), I1.cpu().numpy()
+
+
+@pytest.mark.parametrize("metric_name,dtype_name", [("ip", "f32"), ("l2", "f32"), ("ip", "bf16")])
+def test_static_scratch_search_equals_the_allocating_search_twice_in_a_row(metric_name, dtype_name):
+    import torch
+
+    from nv_genai_b200 import _native as N
+
+    dev = torch.device("cuda", 0)
+    n, d = 60_000, 1024
+    metric = N.METRIC_INNER_PRODUCT if metric_name == "ip" else N.METRIC_L2
+    dtype = N.DTYPE_F32 if dtype_name == "f32" else N.DTYPE_BF16
+    h = ctypes.c_void_p()
+    N.check(N.lib.b2_index_create(d, metric, dtype, 0, ctypes.byref(h)))
+    try:
+        x = torch.empty((n, d), dtype=torch.float32, device=dev)
+        N.check(N.lib.b2_synth_fill(_dev_ptr(x), 0, n, d, 0x5EED0001, 0, None))
+        N.check(N.lib.b2_index_add(h, n, _dev_ptr(x), N.DEVICE, N.ADD_NORMALIZE, None))
+        q = torch.empty((16, d), dtype=torch.float32, device=dev)
+        N.check(N.lib.b2_synth_fill(_dev_ptr(q), 0, 16, d, 0x5EED0002, 0, None))
+        N.check(N.lib.b2_normalize_l2(_dev_ptr(q), 16, d, 0, None))
+        torch.cuda.synchronize()
+
+        # first call: 16 queries, k = 10 (BASELINE config 2 shape); second call: other queries, other k,
+        # smaller tile, so it reads a differently shaped region of the array the first call filled
+        for nq, k, first in ((16, 10, 0), (3, 100, 5)):
+            qs = q[first:first + nq].contiguous()
+            D0, I0, D1, I1 = _search_pair(N, h, qs, k, None)
+            assert np.array_equal(I0, I1), (nq, k)
+            assert np.array_equal(D0, D1), (nq, k)  # identical kernels: bit for bit, tolerance 0
+            assert (I1 >= 0).all() and (I1 < n).all()
+            if metric_name == "ip":
+                assert np.all(np.diff(D1, axis=1) <= 0)
+            else:
+                assert np.all(np.diff(D1, axis=1) >= 0)
+    finally:
+        N.lib.b2_index_destroy(h)
+
+
+def test_static_scratch_search_rejects_what_does_not_fit_and_handles_small_indexes():
+    import torch
+
+    from nv_genai_b200 import _native as N
+
+    dev = torch.device("cuda", 0)
+    n, d = 70_000, 128
+    h = ctypes.c_void_p()
+    N.check(N.lib.b2_index_create(d, N.METRIC_L2, N.DTYPE_F32, 0, ctypes.byref(h)))
+    try:
+        q = torch.empty((17, d), dtype=torch.float32, device=dev)
+        N.check(N.lib.b2_synth_fill(_dev_ptr(q), 0, 17, d, 0x5EED0002, 0, None))
+        D = torch.empty((17, 2048), dtype=torch.float32, device=dev)
+        I = torch.empty((17, 2048), dtype=torch.int64, device=dev)
+
+        # empty index: padding only, as b2_index_search gives
+        N.check(N.lib.b2_index_search_static(h, 2, _dev_ptr(q), 3, _dev_ptr(D), _dev_ptr(I), None))
+        torch.cuda.synchronize()
+        assert (I.view(-1)[:6].cpu().numpy() == -1).all()
+        assert (D.view(-1)[:6].cpu().numpy() == np.finfo(np.float32).max).all()
+
+        x = torch.empty((n, d), dtype=torch.float32, device=dev)
+        N.check(N.lib.b2_synth_fill(_dev_ptr(x), 0, n, d, 0x5EED0001, 0, None))
+        N.check(N.lib.b2_index_add(h, n, _dev_ptr(x), N.DEVICE, 0, None))
+
+        # more than one scan pass of queries
+        st = N.lib.b2_index_search_static(h, 17, _dev_ptr(q), 4, _dev_ptr(D), _dev_ptr(I), None)
+        assert st == N.B2_ERR_UNSUPPORTED and b"16 queries" in N.lib.b2_last_error()
+        # partial lists larger than the fixed scratch: 1 query x (hundreds of CTAs) x k = 1024
+        st = N.lib.b2_index_search_static(h, 1, _dev_ptr(q), 1024, _dev_ptr(D), _dev_ptr(I), None)
+        assert st == N.B2_ERR_UNSUPPORTED and b"exceed the fixed scratch" in N.lib.b2_last_error()
+        # a query tile that does not fit one scan pass at this k
+        st = N.lib.b2_index_search_static(h, 8, _dev_ptr(q), 2048, _dev_ptr(D), _dev_ptr(I), None)
+        assert st == N.B2_ERR_UNSUPPORTED and b"one scan pass" in N.lib.b2_last_error()
+        # bad arguments
+        assert N.lib.b2_index_search_static(h, 1, None, 4, _dev_ptr(D), _dev_ptr(I), None) == N.B2_ERR_INVALID
+        assert N.lib.b2_index_search_static(None, 1, _dev_ptr(q), 4, _dev_ptr(D), _dev_ptr(I), None) == N.B2_ERR_INVALID
+
+        # and a size that fits still works after the refusals
+        D0, I0, D1, I1 = _search_pair(N, h, q[:1].contiguous(), 4, None)
+        assert np.array_equal(I0, I1) and np.array_equal(D0, D1)
+    finally:
+        N.lib.b2_index_destroy(h)
