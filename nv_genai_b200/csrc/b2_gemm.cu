@@ -1,0 +1,775 @@
+// Large-batch exact search on the 5th-generation tensor cores (tcgen05 + TMEM), top-k fused
+// into the accumulator read-out so the nq x ntotal score matrix never reaches HBM.
+//
+// Replaces faiss exhaustive_inner_product_blas / exhaustive_L2sqr_blas + the heap / reservoir
+// result handlers (faiss/utils/distances.cpp, the nq >= distance_compute_blas_threshold = 20
+// path of IndexFlat::search; reached from every batched index.search of the reference, e.g.
+// /root/reference/RetrievalAugmentedGeneration/examples/nvidia_api_catalog/chains.py:122-123
+// when requests are batched, and the hard-negative mining matmul at
+// /root/reference/experimental/synthetic-data-retriever-customization/retriever_customization.ipynb cell 21).
+// Like faiss's BLAS path, L2 is |q|^2 + |x|^2 - 2 q.x clamped at 0 (the |x|^2 come from the
+// ingest kernel's side array), IP is the plain dot product.
+//
+// Mapping (one persistent CTA per SM, warp-specialised):
+//   M = 128 queries (TMEM lanes), N = 256 corpus rows (TMEM columns), K = the row, streamed
+//   in 64-byte slices.  Both operands are K-major, 64-byte swizzled, brought in by TMA:
+//     A = the query tile, pre-split by prep_queries_kernel into hi + lo parts
+//         (bf16 store: bf16 hi/lo, so q is carried to ~16 mantissa bits;
+//          fp32 store: tf32 hi/lo for the 3xTF32 scheme),
+//     B = corpus rows straight from the row store (bf16), or fp32 rows that four transform
+//         warps split in shared memory into tf32 hi (in place) + lo (second buffer).
+//   MMAs per K slice: bf16  D += A_hi.B + A_lo.B            (kind::f16,  2 products)
+//                     fp32  D += A_hi.B_hi + A_lo.B_hi + A_hi.B_lo   (kind::tf32, 3xTF32)
+//   The tensor core adds each product into the fp32 accumulator with truncation, a bias that
+//   grows with the number of accumulation steps (measured: -1e-5 relative at d = 1536 with all
+//   three 3xTF32 products in one accumulator).  The fp32 path therefore keeps TWO accumulators
+//   per tile in TMEM: columns [0,256) take A_hi.B_hi, columns [256,512) take the two small
+//   correction products (2^-11 of the main term, so their truncation is negligible); the
+//   epilogue adds them in fp32 registers.  That uses all 512 TMEM columns, so the fp32 path is
+//   single-buffered (tile time ~49k cycles vs ~2k for the read-out); the bf16 path (2 x 256
+//   columns) is double-buffered: while the MMA warp fills one accumulator, the four epilogue
+//   warps read the other with tcgen05.ld (one thread = one query = one TMEM lane).
+//   The epilogue compares every score with the thread's running threshold and pushes the few survivors
+//   into (a) the query's sorted list of its k best keys in shared memory (warp-cooperative
+//   insertion; slot k-1 is the exact running k-th best = the threshold), and (b) a candidate
+//   log in global memory.
+//   Work item = (query tile, corpus segment); items are dealt round-robin to the CTAs with the
+//   query tile varying fastest, so the CTAs that run at the same time read the same corpus
+//   segment and the corpus is streamed from HBM about once.  A finished item publishes its
+//   k-th best key per query (atomicMax); later items of the same query tile start from that
+//   bound.  Every item emits k candidates per query; merge_partials_kernel finishes.
+//
+// Tie rule: equal keys keep the lower row id (a key has to be strictly better than the running
+// k-th to enter, rows arrive in id order, and bounds imported from other segments admit ties).
+//
+// Algorithmic work per launch: 2 * nq_pad * ntotal * K flop per product (x2 bf16, x3 fp32);
+// corpus bytes ntotal * pitch read ~once from HBM, query tile re-read from L2 per corpus tile.
+#include <cuda.h>
+
+#include <mutex>
+
+#include "b2_common.cuh"
+#include "b2_kernels.h"
+
+namespace b2 {
+
+namespace {
+
+constexpr int kTileM = 128;                        // queries per tile
+constexpr int kTileN = 256;                        // corpus rows per tile
+constexpr int kMaxStages = 8;
+constexpr int kCandCap = 1024;                     // candidate log entries per query per CTA
+constexpr int kGemmMaxK = 128;                     // heap slots per query (k <= 128 on this path)
+constexpr int kEpiThreads = 128;
+constexpr unsigned long long kWatchdogCycles = 20000000000ull;  // ~10 s: a broken pipeline traps instead of hanging
+
+struct GemmParams {
+    int nq, nq_pad;
+    uint32_t n;
+    int k;
+    int kstages;        // K slices per tile
+    int metric;
+    int n_qt, n_seg, tiles_per_seg, n_tiles, n_items;
+    int num_stages;
+    const float* norms; // |x|^2 per stored row
+    uint64_t* cand;     // [grid][kCandCap][128]
+    uint64_t* partial;  // [nq_pad][n_seg][k]
+    uint32_t* tau;      // [nq_pad] ordered image of an exclusive lower bound of the final k-th key
+};
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok = 0;
+    unsigned long long t0 = 0;
+    while (true) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (ok) break;
+        const unsigned long long now = clock64();
+        if (t0 == 0) t0 = now;
+        if (now - t0 > kWatchdogCycles) __trap();
+    }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int x, int y, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(x), "r"(y)
+        : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+template <int KIND>
+__device__ __forceinline__ void umma(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    if (KIND == 0) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+            ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+            : "memory");
+    } else {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+            ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+            : "memory");
+    }
+}
+// K-major operand tile, SWB-byte swizzle (64 or 128): rows of SWB bytes, 8-row groups 8*SWB bytes apart.
+template <int SWB>
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((addr >> 4) & 0x3fff);        // start address
+    d |= (uint64_t)1 << 16;                       // leading byte offset (unused for swizzled K-major)
+    d |= (uint64_t)((8 * SWB) >> 4) << 32;        // stride byte offset: 8 rows x SWB bytes
+    d |= (uint64_t)1 << 46;                       // descriptor version (Blackwell)
+    d |= (uint64_t)(SWB == 128 ? 2 : 4) << 61;    // SWIZZLE_128B / SWIZZLE_64B
+    return d;
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// Register-only v[c] for a run-time c (a dynamically indexed array would live in local memory).
+__device__ __forceinline__ float select32(const float (&v)[32], int c) {
+    float a[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) a[i] = (c & 16) ? v[16 + i] : v[i];
+    float b[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) b[i] = (c & 8) ? a[8 + i] : a[i];
+    float e[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) e[i] = (c & 4) ? b[4 + i] : b[i];
+    const float f0 = (c & 2) ? e[2] : e[0], f1 = (c & 2) ? e[3] : e[1];
+    return (c & 1) ? f1 : f0;
+}
+
+// ------------------------------------------------------------------ per-query running top-k
+// Every epilogue warp owns 32 queries.  For each query, shared memory holds the k best KEYS seen so far,
+// sorted best-first (unfilled slots = -inf); slot k-1 is the exact running k-th best, i.e. the admission
+// threshold.  A survivor is inserted by the whole warp at once: lane l holds slots l, l+32, ..., the insertion
+// point is a ballot count, and every slot behind it takes its left neighbour's value (shuffle) - about a
+// hundred cycles per insertion with no dependent chain of shared-memory loads.  The (key, row) pair itself is
+// appended to the query's candidate log in global memory (arrival order = row order).
+__device__ __forceinline__ float coop_insert(float* __restrict__ A, int k, float x, int lane) {
+    constexpr float kNegInf = -__builtin_huge_valf();
+    float v[kGemmMaxK / 32];
+    int p = 0;
+#pragma unroll
+    for (int i = 0; i < kGemmMaxK / 32; ++i) {
+        const int idx = lane + 32 * i;
+        v[i] = (idx < k) ? A[idx] : kNegInf;
+        p += __popc(__ballot_sync(kFull, v[i] >= x));
+    }
+    float last = x;
+#pragma unroll
+    for (int i = 0; i < kGemmMaxK / 32; ++i) {
+        const int idx = lane + 32 * i;
+        float left = __shfl_up_sync(kFull, v[i], 1);
+        const float carry = __shfl_sync(kFull, v[i > 0 ? i - 1 : 0], 31);
+        if (lane == 0) left = carry;
+        const float nv = (idx < p) ? v[i] : (idx == p ? x : left);
+        if (idx >= p && idx < k) A[idx] = nv;
+        if (i == ((k - 1) >> 5)) last = nv;
+    }
+    last = __shfl_sync(kFull, last, (k - 1) & 31);
+    __syncwarp();
+    return last;  // the new k-th best key of this query
+}
+
+// Keep exactly the current top-k of this thread's log, in arrival order: keys above tau, plus the earliest
+// entries equal to tau.  Called by all lanes of a warp together (the log is [entry][128 queries], so lanes
+// read neighbouring words); lanes with !active only keep the loops uniform.
+__device__ __forceinline__ void compact_log(uint64_t* __restrict__ log, int& cnt, float tau, int k, bool active) {
+    int cmax = active ? cnt : 0;
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) cmax = max(cmax, __shfl_xor_sync(kFull, cmax, s));
+    const uint32_t to = f2ord(tau);
+    const int n = active ? cnt : 0;
+    int n_gt = 0;
+    for (int j0 = 0; j0 < cmax; j0 += 8) {
+        uint64_t e[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) e[u] = (j0 + u < n) ? log[(size_t)(j0 + u) * kEpiThreads] : 0ull;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) n_gt += (j0 + u < n && (uint32_t)(e[u] >> 32) > to) ? 1 : 0;
+    }
+    int eq_left = k - n_gt;
+    int w = 0;
+    for (int j0 = 0; j0 < cmax; j0 += 8) {
+        uint64_t e[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) e[u] = (j0 + u < n) ? log[(size_t)(j0 + u) * kEpiThreads] : 0ull;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            if (j0 + u < n) {
+                const uint32_t ko = (uint32_t)(e[u] >> 32);
+                bool keep = ko > to;
+                if (ko == to && eq_left > 0) {
+                    keep = true;
+                    --eq_left;
+                }
+                if (keep) {
+                    log[(size_t)w * kEpiThreads] = e[u];  // w <= j0 + u: never overtakes the reads
+                    ++w;
+                }
+            }
+        }
+    }
+    if (active) cnt = w;
+}
+
+// ------------------------------------------------------------------ the kernel
+// KIND 0: bf16 rows, kind::f16.  KIND 1: fp32 rows, kind::tf32 (3xTF32).  NA: query parts (1 = hi only, 2 = hi + lo).
+// SWB: bytes of K per pipeline stage = the shared-memory swizzle width (64 or 128).
+template <int KIND, int NA, int SWB>
+__global__ void __launch_bounds__(KIND == 1 ? 320 : 192, 1)
+gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+    constexpr int ELEM = (KIND == 0) ? 2 : 4;
+    constexpr int kSwizzleBytes = SWB;
+    constexpr int kAPartBytes = kTileM * SWB;
+    constexpr int kBTileBytes = kTileN * SWB;
+    constexpr int KSLICE = kSwizzleBytes / ELEM;          // elements per stage along K
+    constexpr int STAGE_BYTES = NA * kAPartBytes + kBTileBytes + (KIND == 1 ? kBTileBytes : 0);
+    constexpr uint32_t STAGE_TX = NA * kAPartBytes + kBTileBytes;
+    constexpr int B_OFF = NA * kAPartBytes;
+    constexpr int BLO_OFF = B_OFF + kBTileBytes;
+    constexpr uint32_t NBUF = (KIND == 0) ? 2u : 1u;  // accumulator buffers (fp32 rows: main + correction, see above)
+    // instruction descriptor: D fp32, A/B bf16 or tf32, both K-major, N = 256, M = 128
+    constexpr uint32_t FMT = (KIND == 0) ? 1u : 2u;
+    constexpr uint32_t IDESC = (1u << 4) | (FMT << 7) | (FMT << 10) | ((uint32_t)(kTileN >> 3) << 17) |
+                               ((uint32_t)(kTileM >> 4) << 24);
+
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t pad = ((raw + 1023u) & ~1023u) - raw;
+    uint8_t* smem = smem_raw + pad;
+    const int S = p.num_stages;
+    uint8_t* stages = smem;
+    float* heap_s = reinterpret_cast<float*>(stages + (size_t)S * STAGE_BYTES);          // [128 queries][k] sorted keys
+    float* nrm_s = heap_s + (size_t)p.k * kEpiThreads;                                    // [2][256]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(nrm_s + 2 * kTileN);
+    uint64_t* full_bar = bars;                    // [S] TMA -> MMA / transform
+    uint64_t* empty_bar = bars + kMaxStages;      // [S] MMA -> TMA
+    uint64_t* xf_bar = bars + 2 * kMaxStages;     // [S] transform -> MMA (fp32 rows)
+    uint64_t* tfull_bar = bars + 3 * kMaxStages;  // [2] MMA -> epilogue
+    uint64_t* tempty_bar = tfull_bar + 2;         // [2] epilogue -> MMA
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    if (tid == 0) {
+        for (int s = 0; s < S; ++s) {
+            mbar_init(smem_u32(full_bar + s), 1);
+            mbar_init(smem_u32(empty_bar + s), 1);
+            mbar_init(smem_u32(xf_bar + s), 4);
+        }
+        for (int b = 0; b < 2; ++b) {  // fp32 rows use only buffer 0
+            mbar_init(smem_u32(tfull_bar + b), 1);
+            mbar_init(smem_u32(tempty_bar + b), 4);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 5) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 4) {
+        // ================= TMA producer
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+                const int qt = item % p.n_qt, seg = item / p.n_qt;
+                const int t0 = seg * p.tiles_per_seg;
+                const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
+                for (int t = t0; t < t1; ++t) {
+                    for (int ks = 0; ks < p.kstages; ++ks) {
+                        mbar_wait(smem_u32(empty_bar + stage), phase ^ 1u);
+                        const uint32_t fb = smem_u32(full_bar + stage);
+                        mbar_expect_tx(fb, STAGE_TX);
+                        const uint32_t sb = smem_u32(stages + (size_t)stage * STAGE_BYTES);
+                        const int x = ks * KSLICE;
+                        tma_load_2d(sb, &tmA, x, qt * kTileM, fb);
+                        if (NA == 2) tma_load_2d(sb + kAPartBytes, &tmA, x, p.nq_pad + qt * kTileM, fb);
+                        tma_load_2d(sb + B_OFF, &tmB, x, t * kTileN, fb);
+                        if (++stage == S) {
+                            stage = 0;
+                            phase ^= 1u;
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 5) {
+        // ================= MMA issuer (one thread)
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            uint32_t tc = 0;
+            for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+                const int seg = item / p.n_qt;
+                const int t0 = seg * p.tiles_per_seg;
+                const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
+                for (int t = t0; t < t1; ++t, ++tc) {
+                    const uint32_t buf = tc % NBUF, par = (tc / NBUF) & 1u;
+                    mbar_wait(smem_u32(tempty_bar + buf), par ^ 1u);
+                    tcgen05_fence_after();
+                    const uint32_t d_tmem = tmem_base + buf * kTileN;
+                    const uint32_t c_tmem = tmem_base + kTileN;  // fp32 rows: correction accumulator
+                    for (int ks = 0; ks < p.kstages; ++ks) {
+                        mbar_wait(smem_u32((KIND == 1 ? xf_bar : full_bar) + stage), phase);
+                        tcgen05_fence_after();
+                        const uint32_t sb = smem_u32(stages + (size_t)stage * STAGE_BYTES);
+#pragma unroll
+                        for (int j = 0; j < kSwizzleBytes / 32; ++j) {
+                            const uint32_t acc = (ks | j) ? 1u : 0u;
+                            const uint64_t a_hi = smem_desc<SWB>(sb + j * 32);
+                            const uint64_t b_hi = smem_desc<SWB>(sb + B_OFF + j * 32);
+                            umma<KIND>(d_tmem, a_hi, b_hi, IDESC, acc);
+                            if (KIND == 0) {
+                                if (NA == 2) {
+                                    const uint64_t a_lo = smem_desc<SWB>(sb + kAPartBytes + j * 32);
+                                    umma<KIND>(d_tmem, a_lo, b_hi, IDESC, 1u);
+                                }
+                            } else {
+                                const uint64_t b_lo = smem_desc<SWB>(sb + BLO_OFF + j * 32);
+                                umma<KIND>(c_tmem, a_hi, b_lo, IDESC, acc);
+                                if (NA == 2) {
+                                    const uint64_t a_lo = smem_desc<SWB>(sb + kAPartBytes + j * 32);
+                                    umma<KIND>(c_tmem, a_lo, b_hi, IDESC, 1u);
+                                }
+                            }
+                        }
+                        tcgen05_commit(smem_u32(empty_bar + stage));
+                        if (++stage == S) {
+                            stage = 0;
+                            phase ^= 1u;
+                        }
+                    }
+                    tcgen05_commit(smem_u32(tfull_bar + buf));
+                }
+            }
+        }
+    } else if (warp >= 6) {
+        // ================= fp32 rows: split the landed B slice into tf32 hi (in place) + lo
+        if (KIND == 1) {
+            const int xt = tid - 192;  // 0..127
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+                const int seg = item / p.n_qt;
+                const int t0 = seg * p.tiles_per_seg;
+                const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
+                for (int t = t0; t < t1; ++t) {
+                    for (int ks = 0; ks < p.kstages; ++ks) {
+                        mbar_wait(smem_u32(full_bar + stage), phase);
+                        float4* b_hi = reinterpret_cast<float4*>(stages + (size_t)stage * STAGE_BYTES + B_OFF);
+                        float4* b_lo = reinterpret_cast<float4*>(stages + (size_t)stage * STAGE_BYTES + BLO_OFF);
+#pragma unroll
+                        for (int i = 0; i < kBTileBytes / 16 / 128; ++i) {
+                            const int idx = i * 128 + xt;
+                            const float4 x = b_hi[idx];
+                            float4 h, l;
+                            uint32_t u;
+                            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x.x)); h.x = __uint_as_float(u);
+                            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x.y)); h.y = __uint_as_float(u);
+                            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x.z)); h.z = __uint_as_float(u);
+                            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x.w)); h.w = __uint_as_float(u);
+                            l.x = x.x - h.x; l.y = x.y - h.y; l.z = x.z - h.z; l.w = x.w - h.w;
+                            b_hi[idx] = h;
+                            b_lo[idx] = l;
+                        }
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(smem_u32(xf_bar + stage));
+                        if (++stage == S) {
+                            stage = 0;
+                            phase ^= 1u;
+                        }
+                    }
+                }
+            }
+        }
+    } else {
+        // ================= epilogue: warps 0..3, thread = query = TMEM lane
+        constexpr float kNegInf = -__builtin_huge_valf();
+        const int ql = tid;  // 0..127
+        const int k = p.k;
+        float* keys_w = heap_s + (size_t)(warp * 32) * k;  // this warp's 32 sorted key lists, k slots each
+        uint64_t* log = p.cand + (size_t)blockIdx.x * kCandCap * kEpiThreads + ql;
+        const bool l2 = p.metric == B2_METRIC_L2;
+        uint32_t tc = 0;
+        for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+            const int qt = item % p.n_qt, seg = item / p.n_qt;
+            const int t0 = seg * p.tiles_per_seg;
+            const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
+            const int q = qt * kTileM + ql;
+            const bool active = q < p.nq;
+            // bound imported from finished items of this query (exclusive); +inf parks padding lanes
+            const float thr0 = active ? ord2f(__ldcg(p.tau + q)) : -kNegInf;
+            float thr = thr0;
+            int cnt = 0;
+            for (int i = lane; i < 32 * k; i += 32) keys_w[i] = kNegInf;
+            __syncwarp();
+            for (int t = t0; t < t1; ++t, ++tc) {
+                const uint32_t buf = tc % NBUF, par = (tc / NBUF) & 1u;
+                const uint32_t row0 = (uint32_t)t * kTileN;
+                if (l2) {
+                    float* ns = nrm_s + (tc & 1u) * kTileN;  // always double-buffered: a faster warp may already be one tile ahead
+                    for (int c = ql; c < kTileN; c += kEpiThreads) {
+                        const uint32_t r = row0 + c;
+                        ns[c] = (r < p.n) ? p.norms[r] : 0.f;
+                    }
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                }
+                // a whole tile of survivors must fit behind cnt: compact first if any lane is close (warp-uniform)
+                if (__any_sync(kFull, cnt > kCandCap - kTileN))
+                    compact_log(log, cnt, keys_w[(size_t)lane * k + (k - 1)], k, cnt > k);
+                mbar_wait(smem_u32(tfull_bar + buf), par);
+                tcgen05_fence_after();
+                const int limit = (int)min((uint32_t)kTileN, p.n - row0);
+                const uint32_t taddr0 = tmem_base + buf * kTileN + ((uint32_t)(warp * 32) << 16);
+#pragma unroll 1
+                for (int ch = 0; ch < kTileN / 32; ++ch) {
+                    uint32_t raw32[32];
+                    tmem_ld32(taddr0 + ch * 32, raw32);
+                    if (KIND == 1) {
+                        uint32_t cor32[32];
+                        tmem_ld32(taddr0 + kTileN + ch * 32, cor32);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int c = 0; c < 32; ++c)
+                            raw32[c] = __float_as_uint(__uint_as_float(raw32[c]) + __uint_as_float(cor32[c]));
+                    } else {
+                        tmem_ld_wait();
+                    }
+                    float key[32];
+                    if (l2) {
+                        const float4* n4 = reinterpret_cast<const float4*>(nrm_s + (tc & 1u) * kTileN + ch * 32);
+#pragma unroll
+                        for (int c4 = 0; c4 < 8; ++c4) {
+                            const float4 nn = n4[c4];
+                            key[4 * c4 + 0] = fmaf(2.f, __uint_as_float(raw32[4 * c4 + 0]), -nn.x);
+                            key[4 * c4 + 1] = fmaf(2.f, __uint_as_float(raw32[4 * c4 + 1]), -nn.y);
+                            key[4 * c4 + 2] = fmaf(2.f, __uint_as_float(raw32[4 * c4 + 2]), -nn.z);
+                            key[4 * c4 + 3] = fmaf(2.f, __uint_as_float(raw32[4 * c4 + 3]), -nn.w);
+                        }
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) key[c] = __uint_as_float(raw32[c]) + 0.0f;
+                    }
+                    uint32_t m = 0;
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) m |= (key[c] > thr) ? (1u << c) : 0u;
+                    const int left = limit - ch * 32;
+                    if (left < 32) m &= (left <= 0) ? 0u : ((1u << left) - 1u);
+                    // survivors, one (query, column) at a time, each inserted by the whole warp
+                    unsigned pending = __ballot_sync(kFull, m != 0u);
+                    while (pending) {
+                        const int src = __ffs(pending) - 1;
+                        const int c = m ? (__ffs(m) - 1) : 0;
+                        const float kv = select32(key, c);
+                        const float xs = __shfl_sync(kFull, kv, src);
+                        const float ts = __shfl_sync(kFull, thr, src);
+                        if (xs > ts) {  // the threshold may have risen since the mask was built
+                            const float kth = coop_insert(keys_w + (size_t)src * k, k, xs, lane);
+                            if (lane == src) {
+                                log[(size_t)cnt * kEpiThreads] = pack_cand(kv, row0 + ch * 32 + c);
+                                ++cnt;
+                                thr = fmaxf(thr0, kth);
+                            }
+                        }
+                        if (lane == src) m &= m - 1u;
+                        pending = __ballot_sync(kFull, m != 0u);
+                    }
+                }
+                tcgen05_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(tempty_bar + buf));
+            }
+            // ---- item done: emit this query's k best of the segment, publish the bound
+            const float tau = keys_w[(size_t)lane * k + (k - 1)];
+            const bool full = active && tau > kNegInf;
+            compact_log(log, cnt, tau, k, full);
+            if (full) atomicMax(p.tau + q, f2ord(tau) - 1u);
+            if (active) {
+                uint64_t* out = p.partial + ((size_t)q * p.n_seg + seg) * k;
+                for (int i0 = 0; i0 < k; i0 += 8) {
+                    uint64_t e[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        e[u] = (i0 + u < cnt) ? log[(size_t)(i0 + u) * kEpiThreads] : B2_SENTINEL;
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (i0 + u < k) out[i0 + u] = e[u];
+                }
+            }
+            __syncwarp();
+        }
+    }
+
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 5) {
+        tcgen05_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
+// ------------------------------------------------------------------ query preparation
+// q [nq][d] fp32 -> A [NA][nq_pad][kp] (bf16 or fp32-holding-tf32), zero padded; qn[q] = |q|^2.
+template <int KIND>
+__global__ void prep_queries_kernel(const float* __restrict__ q, int nq, int d, int nq_pad, int kp, int na, void* A,
+                                    float* __restrict__ qn, uint32_t* __restrict__ tau) {
+    const int lane = threadIdx.x & 31;
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= nq_pad) return;
+    float ss = 0.f;
+    for (int c = lane; c < kp; c += 32) {
+        const float x = (row < nq && c < d) ? q[(size_t)row * d + c] : 0.f;
+        ss = fmaf(x, x, ss);
+        if (KIND == 0) {
+            __nv_bfloat16* a = static_cast<__nv_bfloat16*>(A);
+            const __nv_bfloat16 h = __float2bfloat16_rn(x);
+            a[(size_t)row * kp + c] = h;
+            if (na == 2) a[((size_t)nq_pad + row) * kp + c] = __float2bfloat16_rn(x - __bfloat162float(h));
+        } else {
+            float* a = static_cast<float*>(A);
+            uint32_t u;
+            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+            const float h = __uint_as_float(u);
+            a[(size_t)row * kp + c] = h;
+            if (na == 2) a[((size_t)nq_pad + row) * kp + c] = x - h;
+        }
+    }
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) ss += __shfl_xor_sync(kFull, ss, s);
+    if (lane == 0) {
+        qn[row] = ss;
+        tau[row] = 0x00800000u;  // image of -FLT_MAX as the exclusive bound: admits every key > -FLT_MAX
+    }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+        else
+            cudaGetLastError();
+    });
+    return fn;
+}
+
+int make_map(CUtensorMap* m, bool bf16, int swb, const void* base, uint64_t inner_elems, uint64_t rows,
+             uint64_t pitch_bytes, uint32_t box_rows) {
+    EncodeTiledFn fn = encode_tiled();
+    if (fn == nullptr) {
+        set_error("cuTensorMapEncodeTiled is not available from this driver");
+        return B2_ERR_UNSUPPORTED;
+    }
+    const cuuint64_t dims[2] = {inner_elems, rows};
+    const cuuint64_t strides[1] = {pitch_bytes};
+    const cuuint32_t box[2] = {(cuuint32_t)(swb / (bf16 ? 2 : 4)), box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = fn(m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                          const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          swb == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed (%d) for %llu x %llu, pitch %llu", (int)r,
+                  (unsigned long long)inner_elems, (unsigned long long)rows, (unsigned long long)pitch_bytes);
+        return B2_ERR_CUDA;
+    }
+    return B2_OK;
+}
+
+size_t gemm_smem_bytes(bool fp32_rows, int na, int swb, int stages, int k) {
+    const size_t stage = (size_t)na * kTileM * swb + (size_t)kTileN * swb * (fp32_rows ? 2 : 1);
+    return 1024 + stages * stage + (size_t)k * kEpiThreads * 4 + 2 * kTileN * 4 + (3 * kMaxStages + 4) * 8 + 16;
+}
+
+template <int KIND, int NA, int SWB>
+int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int grid, size_t smem,
+                cudaStream_t stream) {
+    auto kern = gemm_topk_kernel<KIND, NA, SWB>;
+    static std::mutex mu;
+    static size_t attr[64] = {0};
+    int dev = 0;
+    B2_CUDA_TRY(cudaGetDevice(&dev));
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (smem > attr[dev & 63]) {
+            B2_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            attr[dev & 63] = smem;
+        }
+    }
+    kern<<<grid, KIND == 1 ? 320 : 192, smem, stream>>>(tmA, tmB, p);
+    B2_AFTER_LAUNCH();
+    return B2_OK;
+}
+
+}  // namespace
+
+bool gemm_path_supported(int64_t n, int d, int dtype, int k, int64_t nq) {
+    if (getenv("B2_NO_TENSOR") != nullptr) return false;
+    const int elem = dtype == B2_DTYPE_BF16 ? 2 : 4;
+    return nq >= 20 && k <= kGemmMaxK && n >= 4096 && n < ((int64_t)1 << 31) && (int64_t)d * elem >= 64;
+}
+
+int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* norms,
+                const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream) {
+    const bool bf16 = dtype == B2_DTYPE_BF16;
+    const int elem = bf16 ? 2 : 4;
+    int na = 2;
+    if (const char* e = getenv("B2_GEMM_QUERY_PARTS")) na = (atoi(e) == 1) ? 1 : 2;
+    // stage width: 128-byte swizzle when at least three stages of it fit beside the k-slot heaps, else 64
+    int swb = (gemm_smem_bytes(!bf16, na, 128, 3, k) <= 227 * 1024) ? 128 : 64;
+    if (const char* e = getenv("B2_GEMM_SWIZZLE")) swb = (atoi(e) == 128) ? 128 : 64;  // tuning override
+    if (swb == 128 && gemm_smem_bytes(!bf16, na, 128, 2, k) > 227 * 1024) swb = 64;
+    const size_t kbytes = (((size_t)d * elem + swb - 1) / swb) * swb;
+    const int kp = (int)(kbytes / elem);
+
+    GemmParams p;
+    p.nq = (int)nq;
+    p.nq_pad = (int)((nq + kTileM - 1) / kTileM) * kTileM;
+    p.n = (uint32_t)n;
+    p.k = k;
+    p.kstages = (int)(kbytes / swb);
+    p.metric = metric;
+    p.n_qt = p.nq_pad / kTileM;
+    p.n_tiles = (int)((n + kTileN - 1) / kTileN);
+    p.norms = norms;
+
+    // segments: make (query tiles x segments) a near multiple of the CTA count, segments >= 8 tiles
+    const int grid_max = num_sms;
+    int best_s = 1;
+    double best_cost = 1e30;
+    const int max_s = std::max(1, std::min(p.n_tiles / 8, 4 * grid_max));
+    for (int s = 1; s <= max_s; ++s) {
+        const int tps = (p.n_tiles + s - 1) / s;
+        const int s_eff = (p.n_tiles + tps - 1) / tps;
+        const long long items = (long long)p.n_qt * s_eff;
+        const long long waves = (items + grid_max - 1) / grid_max;
+        // time ~ waves x tiles per segment (+ a per-item warm-up cost of about 6 tiles)
+        const double cost = (double)waves * (tps + 6.0);
+        if (cost < best_cost * 0.995) {
+            best_cost = cost;
+            best_s = s_eff;
+        }
+    }
+    p.tiles_per_seg = (p.n_tiles + best_s - 1) / best_s;
+    p.n_seg = (p.n_tiles + p.tiles_per_seg - 1) / p.tiles_per_seg;
+    p.n_items = p.n_qt * p.n_seg;
+    const int grid = (int)std::min<long long>(grid_max, p.n_items);
+
+    // pipeline depth from the shared-memory budget
+    int stages = kMaxStages;
+    while (stages > 2 && gemm_smem_bytes(!bf16, na, swb, stages, k) > 227 * 1024) --stages;
+    const size_t smem = gemm_smem_bytes(!bf16, na, swb, stages, k);
+    if (smem > 227 * 1024) {
+        set_error("tensor-core search: k=%d does not fit shared memory", k);
+        return B2_ERR_UNSUPPORTED;
+    }
+    p.num_stages = stages;
+
+    // scratch: [A parts][qn][tau][partial][candidate logs]
+    auto al = [](size_t v) { return (v + 1023) / 1024 * 1024; };
+    const size_t a_bytes = al((size_t)na * p.nq_pad * kbytes);
+    const size_t qn_bytes = al((size_t)p.nq_pad * 4);
+    const size_t tau_bytes = al((size_t)p.nq_pad * 4);
+    const size_t part_bytes = al((size_t)p.nq_pad * p.n_seg * k * 8);
+    const size_t cand_bytes = al((size_t)grid * kCandCap * kEpiThreads * 8);
+    char* blk = nullptr;
+    B2_CUDA_TRY(cudaMallocAsync(&blk, a_bytes + qn_bytes + tau_bytes + part_bytes + cand_bytes, stream));
+    void* A = blk;
+    float* qn = reinterpret_cast<float*>(blk + a_bytes);
+    p.tau = reinterpret_cast<uint32_t*>(blk + a_bytes + qn_bytes);
+    p.partial = reinterpret_cast<uint64_t*>(blk + a_bytes + qn_bytes + tau_bytes);
+    p.cand = reinterpret_cast<uint64_t*>(blk + a_bytes + qn_bytes + tau_bytes + part_bytes);
+
+    int rc = B2_OK;
+    CUtensorMap tmA, tmB;
+    rc = make_map(&tmA, bf16, swb, A, (uint64_t)kp, (uint64_t)na * p.nq_pad, kbytes, kTileM);
+    if (rc == B2_OK) rc = make_map(&tmB, bf16, swb, rows, (uint64_t)(pitch_bytes / elem), (uint64_t)n, pitch_bytes, kTileN);
+    if (rc == B2_OK) {
+        const int wpb = 8;
+        const int blocks = (p.nq_pad + wpb - 1) / wpb;
+        if (bf16)
+            prep_queries_kernel<0><<<blocks, wpb * 32, 0, stream>>>(q_dev, (int)nq, d, p.nq_pad, kp, na, A, qn, p.tau);
+        else
+            prep_queries_kernel<1><<<blocks, wpb * 32, 0, stream>>>(q_dev, (int)nq, d, p.nq_pad, kp, na, A, qn, p.tau);
+        B2_COUNT_LAUNCH();
+        if (cudaGetLastError() != cudaSuccess) {
+            set_error("prep_queries launch failed");
+            rc = B2_ERR_CUDA;
+        }
+    }
+    if (rc == B2_OK) {
+        const int variant = (bf16 ? 0 : 4) + (na == 2 ? 2 : 0) + (swb == 128 ? 1 : 0);
+        switch (variant) {
+            case 0: rc = launch_gemm<0, 1, 64>(tmA, tmB, p, grid, smem, stream); break;
+            case 1: rc = launch_gemm<0, 1, 128>(tmA, tmB, p, grid, smem, stream); break;
+            case 2: rc = launch_gemm<0, 2, 64>(tmA, tmB, p, grid, smem, stream); break;
+            case 3: rc = launch_gemm<0, 2, 128>(tmA, tmB, p, grid, smem, stream); break;
+            case 4: rc = launch_gemm<1, 1, 64>(tmA, tmB, p, grid, smem, stream); break;
+            case 5: rc = launch_gemm<1, 1, 128>(tmA, tmB, p, grid, smem, stream); break;
+            case 6: rc = launch_gemm<1, 2, 64>(tmA, tmB, p, grid, smem, stream); break;
+            default: rc = launch_gemm<1, 2, 128>(tmA, tmB, p, grid, smem, stream); break;
+        }
+    }
+    if (rc == B2_OK)
+        rc = merge_partials(p.partial, (int)nq, p.n_seg, k, metric, 0, D, I, (size_t)k, stream,
+                            metric == B2_METRIC_L2 ? qn : nullptr);
+    cudaFreeAsync(blk, stream);
+    return rc;
+}
+
+}  // namespace b2

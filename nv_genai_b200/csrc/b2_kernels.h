@@ -29,8 +29,15 @@ void index_unlock_shared(b2_index* h);
 
 // b2_merge.cu --------------------------------------------------------------
 // partial: [nq][nlists][k] candidates (pos = local row id) -> D/I [nq][k] with I = id_base + pos.
+// qnorm (optional, L2 only): keys are 2 q.x - |x|^2 and D = max(0, qnorm[q] - key) (the BLAS-path form).
 int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metric, int64_t id_base, float* D,
-                   int64_t* I, size_t out_stride, cudaStream_t stream);
+                   int64_t* I, size_t out_stride, cudaStream_t stream, const float* qnorm = nullptr);
+
+// b2_gemm.cu ---------------------------------------------------------------
+// Tensor-core search for batches of >= 20 queries (faiss's BLAS threshold), k <= 128.
+bool gemm_path_supported(int64_t n, int d, int dtype, int k, int64_t nq);
+int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* norms,
+                const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream);
 // (D_parts, I_parts): [nparts][nq][k] -> [nq][k]
 int merge_shards(int metric, int nq, int k, int nparts, const float* D_parts, const int64_t* I_parts, float* D,
                  int64_t* I, cudaStream_t stream);

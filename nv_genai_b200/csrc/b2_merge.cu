@@ -15,7 +15,8 @@ namespace b2 {
 
 constexpr int kMergeThreads = 512;
 
-__device__ __forceinline__ void emit_result(uint64_t c, int metric, int64_t id_base, float* D, int64_t* I) {
+__device__ __forceinline__ void emit_result(uint64_t c, int metric, int64_t id_base, float* D, int64_t* I,
+                                            const float* qn = nullptr) {
     const uint32_t pos = cand_pos(c);
     if (pos == kNoPos) {
         *I = -1;
@@ -23,14 +24,18 @@ __device__ __forceinline__ void emit_result(uint64_t c, int metric, int64_t id_b
     } else {
         *I = id_base + (int64_t)pos;
         const float key = cand_key(c);
-        *D = (metric == B2_METRIC_IP) ? key : -key;
+        if (qn != nullptr)
+            *D = fmaxf(*qn - key, 0.f);  // faiss exhaustive_L2sqr_blas: |q|^2 + |x|^2 - 2 q.x, negatives clamped
+        else
+            *D = (metric == B2_METRIC_IP) ? key : -key;
     }
 }
 
 __global__ void __launch_bounds__(kMergeThreads) merge_partials_kernel(const uint64_t* __restrict__ partial,
                                                                       int total, int k, int kpad, int sort_n,
                                                                       int metric, int64_t id_base, float* D,
-                                                                      int64_t* I, size_t out_stride) {
+                                                                      int64_t* I, size_t out_stride,
+                                                                      const float* __restrict__ qnorm) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw);
     const int q = blockIdx.x, tid = threadIdx.x;
@@ -43,11 +48,12 @@ __global__ void __launch_bounds__(kMergeThreads) merge_partials_kernel(const uin
     }
     __syncthreads();
     for (int i = tid; i < k; i += kMergeThreads)
-        emit_result(buf[i], metric, id_base, D + (size_t)q * out_stride + i, I + (size_t)q * out_stride + i);
+        emit_result(buf[i], metric, id_base, D + (size_t)q * out_stride + i, I + (size_t)q * out_stride + i,
+                    qnorm ? qnorm + q : nullptr);
 }
 
 int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metric, int64_t id_base, float* D,
-                   int64_t* I, size_t out_stride, cudaStream_t stream) {
+                   int64_t* I, size_t out_stride, cudaStream_t stream, const float* qnorm) {
     const int kpad = next_pow2(k < 32 ? 32 : k);
     const int total = nlists * k;
     int sort_n = 2 * kpad;
@@ -55,7 +61,7 @@ int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metri
     while (sort_n < want && sort_n < 4096) sort_n <<= 1;
     const size_t smem = (size_t)sort_n * sizeof(uint64_t);
     merge_partials_kernel<<<nq, kMergeThreads, smem, stream>>>(partial, total, k, kpad, sort_n, metric, id_base, D, I,
-                                                               out_stride);
+                                                               out_stride, qnorm);
     B2_AFTER_LAUNCH();
     return B2_OK;
 }
