@@ -47,7 +47,8 @@ def parse_args():
     ap.add_argument("--dtype", default="float32", choices=["float32", "bfloat16"])
     ap.add_argument("--cpu-sample-rows", type=int, default=1_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--extra", action="store_true", help="also time batch 16 and print it under 'extra'")
+    ap.add_argument("--extra", action="store_true",
+                    help="also time batch 16 and BASELINE configs[2] (batch 4096, k=100, fp32 and bf16 rows) under 'extra'")
     return ap.parse_args()
 
 
@@ -113,6 +114,25 @@ def measured_peak():
         except Exception:
             pass
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def measured_tensor_peak(fp32_rows):
+    """Dense tensor peak for a kernel timed inside a long step: the measured sustained bf16 cuBLAS figure; the
+    tf32 pipe runs at half the bf16 rate (no measured tf32 number exists, so it is derived and labelled)."""
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    peak, src = 1400.0, "fallback (B200_PROFILING.md ~1.4 PFLOP/s sustained bf16)"
+    if os.path.exists(p):
+        try:
+            peak, src = float(json.load(open(p))["bf16_tflops_sustained"]), "measured (MEASURED_PEAKS.json bf16_tflops_sustained)"
+        except Exception:
+            pass
+    if fp32_rows:
+        return peak / 2.0, src + " / 2: tf32 issues at half the bf16 rate"
+    return peak, src
+
+
+def uses_tensor_path(batch, k, rows):
+    return batch >= 20 and k <= 128 and rows >= 4096
 
 
 def ncu_traffic():
@@ -193,14 +213,14 @@ def run_reference(a):
 
 
 # ------------------------------------------------------------------------------------------ GPU arm
-def build_shard(a, device, lo, hi):
+def build_shard(a, device, lo, hi, dtype=None):
     """Rows [lo, hi) of the synthetic corpus, generated on the device and ingested with the fused normalise."""
     import torch
 
     from nv_genai_b200 import IndexFlatIP, synth_fill
     from oracle import flat  # seeds only
 
-    idx = IndexFlatIP(a.dim, dtype=a.dtype, device=device)
+    idx = IndexFlatIP(a.dim, dtype=dtype or a.dtype, device=device)
     chunk = min(1_000_000, max(hi - lo, 1))
     buf = torch.empty((chunk, a.dim), dtype=torch.float32, device=f"cuda:{device}")
     for r0 in range(lo, hi, chunk):
@@ -255,59 +275,73 @@ def run_b200(a):
 
     pitch = ((a.dim * (2 if a.dtype == "bfloat16" else 4) + 511) // 512) * 512
     peak, peak_src = measured_peak()
+    total = a.warmup + a.steps
     props = torch.cuda.get_device_properties(local)
     gpu_id = f"GPU-{props.uuid}" if getattr(props, "uuid", None) else local
     sampler = ClockSampler(gpu_id) if rank == 0 else None
 
-    def one_config(batch):
+    def one_config(batch, index=None, k=None, dtype=None, steps=None):
         """Returns dict with device-resident and end-to-end timings for this query batch size."""
-        q_dev = make_queries(a, local, total, batch)
-        q_host = torch.empty((total, batch, a.dim), dtype=torch.float32).pin_memory()
+        index = idx if index is None else index
+        k = a.k if k is None else k
+        dtype = a.dtype if dtype is None else dtype
+        steps = a.steps if steps is None else steps
+        warm = min(a.warmup, 3) if steps < a.steps else a.warmup
+        tot = warm + steps
+        shx = None
+        if world > 1:
+            shx = sh if index is idx else ShardedFlatIndex(a.dim, index.metric_type, local_index=index)
+            if shx is not sh:
+                shx._refresh_bases()
+        q_dev = make_queries(a, local, tot, batch)
+        q_host = torch.empty((tot, batch, a.dim), dtype=torch.float32).pin_memory()
         q_host.copy_(q_dev.cpu())
         q_np = q_host.numpy()
         stage = torch.empty((batch, a.dim), dtype=torch.float32, device=f"cuda:{local}")
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        tensor = uses_tensor_path(batch, k, hi - lo)
+        kern = _native.PROF_GEMM if tensor else _native.PROF_SCAN
 
         def step_resident(i):
-            if sh is None:
-                return idx.search(q_dev[i], a.k)
+            if shx is None:
+                return index.search(q_dev[i], k)
             # rank 0 owns the batch; the others receive it by broadcast inside sh.search
             buf = q_dev[i] if rank == 0 else stage
-            return sh.search(buf, a.k, replicated=False, src=0)
+            return shx.search(buf, k, replicated=False, src=0)
 
         def step_e2e(i):
-            if sh is None:
-                return idx.search(q_np[i], a.k)  # host buffers in, host buffers out, through b2_index_search
+            if shx is None:
+                return index.search(q_np[i], k)  # host buffers in, host buffers out, through b2_index_search
             if rank == 0:
                 stage.copy_(q_host[i], non_blocking=True)  # H2D from pinned memory
-            D, I = sh.search(stage, a.k, replicated=False, src=0)
+            D, I = shx.search(stage, k, replicated=False, src=0)
             if rank == 0:
                 return D.cpu(), I.cpu()  # D2H of the merged result
             return D, I
 
         def timed(step_fn, with_prof):
-            for i in range(a.warmup):
+            for i in range(warm):
                 step_fn(i)
             torch.cuda.synchronize()
             if dist is not None:
                 dist.barrier()
                 torch.cuda.synchronize()
             if with_prof:
-                _native.prof_read(reset=True)
+                _native.prof_read(reset=True, kernel=kern)
                 _native.prof_enable(True)
             _native.launch_count_reset()
             t0 = time.time()
             e0.record()
-            for i in range(a.warmup, total):
+            for i in range(warm, tot):
                 step_fn(i)
             e1.record()
             torch.cuda.synchronize()
             t1 = time.time()
             launches = _native.launch_count()
-            scan_ms, scan_n = (0.0, 0)
+            k_ms, k_n = (0.0, 0)
             if with_prof:
                 _native.prof_enable(False)
-                scan_ms, scan_n = _native.prof_read(reset=True)
+                k_ms, k_n = _native.prof_read(reset=True, kernel=kern)
             if dist is not None:
                 dist.barrier()
                 torch.cuda.synchronize()
@@ -316,31 +350,63 @@ def run_b200(a):
             if dist is not None:
                 dist.all_reduce(ms, op=dist.ReduceOp.MAX)
                 dist.all_reduce(ln, op=dist.ReduceOp.SUM)
-            return float(ms.item()), int(ln.item()), scan_ms, scan_n, t0, t1
+            return float(ms.item()), int(ln.item()), k_ms, k_n, t0, t1
 
-        ms, launches, scan_ms, scan_n, t0, t1 = timed(step_resident, True)
+        ms, launches, k_ms, k_n, t0, t1 = timed(step_resident, True)
         ms_e, _, _, _, _, _ = timed(step_e2e, False)
         clocks = sampler.summary(t0, t1) if sampler is not None else None
-        shard_bytes = (hi - lo) * pitch
-        scan_avg_ms = scan_ms / max(scan_n, 1)
-        achieved = shard_bytes / (scan_avg_ms * 1e-3) / 1e9 if scan_n else None
+        pitch_c = ((a.dim * (2 if dtype == "bfloat16" else 4) + 511) // 512) * 512
+        k_avg_ms = k_ms / max(k_n, 1)
+        if tensor:
+            fp32_rows = dtype != "bfloat16"
+            tpeak, tsrc = measured_tensor_peak(fp32_rows)
+            flops = 2.0 * batch * (hi - lo) * a.dim  # algorithmic: one product per (query, row, dim)
+            products = 3 if fp32_rows else 2
+            achieved = flops / (k_avg_ms * 1e-3) / 1e12 if k_n else None
+            roof = {"bound": "tensor", "achieved": achieved, "peak": tpeak, "unit": "TFLOP/s",
+                    "frac": (achieved / tpeak) if achieved else None, "traffic": None,
+                    "kernel": "gemm_topk_kernel", "algorithmic_flops_per_launch": flops,
+                    "mma_products_per_score": products,
+                    "issued_mma_tflops": (achieved * products * (-(-batch // 128) * 128) / batch) if achieved else None,
+                    "avg_launch_ms": k_avg_ms, "launches_timed": k_n, "peak_source": tsrc,
+                    "kernel_share_of_step": (k_avg_ms * k_n / ms) if k_n else None}
+        else:
+            shard_bytes = (hi - lo) * pitch_c
+            achieved = shard_bytes / (k_avg_ms * 1e-3) / 1e9 if k_n else None
+            per_step = -(-batch // 16)  # scan passes per step
+            roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                    "frac": (achieved / peak) if achieved else None,
+                    "traffic": ncu_traffic() if (batch == 1 and dtype == "float32" and world == 1) else None,
+                    "kernel": "scan_topk_kernel", "algorithmic_bytes_per_launch": shard_bytes,
+                    "avg_launch_ms": k_avg_ms, "launches_timed": k_n, "peak_source": peak_src,
+                    "scan_share_of_step": (k_avg_ms * k_n / ms) if k_n else None, "scan_passes_per_step": per_step}
         return {
-            "batch": batch, "ms_per_step": ms / a.steps, "value": batch * a.steps / (ms * 1e-3),
-            "e2e_value": batch * a.steps / (ms_e * 1e-3), "e2e_ms_per_step": ms_e / a.steps,
-            "launches": launches, "clocks": clocks,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": (achieved / peak) if achieved else None, "traffic": ncu_traffic() if batch == 1 else None,
-                         "kernel": "scan_topk_kernel", "algorithmic_bytes_per_launch": shard_bytes,
-                         "avg_launch_ms": scan_avg_ms, "launches_timed": scan_n, "peak_source": peak_src,
-                         "scan_share_of_step": (scan_avg_ms * scan_n / ms) if scan_n else None},
-            "h2d": batch * a.dim * 4, "d2h": batch * a.k * 12,
+            "batch": batch, "k": k, "dtype": dtype, "steps": steps, "ms_per_step": ms / steps,
+            "value": batch * steps / (ms * 1e-3),
+            "e2e_value": batch * steps / (ms_e * 1e-3), "e2e_ms_per_step": ms_e / steps,
+            "launches": launches, "clocks": clocks, "roofline": roof,
+            "h2d": batch * a.dim * 4, "d2h": batch * k * 12,
         }
 
     main = one_config(a.batch)
     extra = None
-    if a.extra and a.batch != 16:
-        e = one_config(16)
-        extra = {"batch16": {k: e[k] for k in ("value", "ms_per_step", "e2e_value", "roofline")}}
+    if a.extra:
+        extra = {}
+        keep = ("batch", "k", "dtype", "steps", "value", "ms_per_step", "e2e_value", "roofline")
+        if a.batch != 16:
+            e = one_config(16)  # the other half of BASELINE configs[1]
+            extra["batch16"] = {kk: e[kk] for kk in keep}
+        if a.dtype == "float32" and a.batch != 4096:
+            # BASELINE configs[2]: batch 4096, k = 100, fp32 rows (3xTF32) and bf16 rows, tensor-core path
+            e = one_config(4096, k=100, steps=max(3, min(a.steps, 5)))
+            extra["cfg3_fp32_batch4096_k100"] = {kk: e[kk] for kk in keep}
+            idx16 = build_shard(a, local, lo, hi, dtype="bfloat16")
+            e = one_config(4096, index=idx16, k=100, dtype="bfloat16", steps=max(3, min(a.steps, 5)))
+            extra["cfg3_bf16_batch4096_k100"] = {kk: e[kk] for kk in keep}
+            e = one_config(1, index=idx16, dtype="bfloat16", steps=max(3, min(a.steps, 20)))
+            extra["bf16_batch1_k10"] = {kk: e[kk] for kk in keep}
+            del idx16
+            torch.cuda.empty_cache()
     if sampler is not None:
         sampler.stop()
 

@@ -178,6 +178,10 @@ B2_API void b2_launch_count_reset(void);
  * of launches since the last reset. */
 B2_API int b2_prof_enable(int on);
 B2_API int b2_prof_read(double* scan_ms, int64_t* scan_launches, int reset);
+/* The same per kernel: B2_PROF_SCAN = the small-batch scan kernel, B2_PROF_GEMM = the tensor-core kernel. */
+#define B2_PROF_SCAN 0
+#define B2_PROF_GEMM 1
+B2_API int b2_prof_read_kernel(int kernel, double* ms, int64_t* launches, int reset);
 
 /* Thread-local message of the most recent failure on this thread ("" if none). */
 B2_API const char* b2_last_error(void);

@@ -24,7 +24,7 @@ SYMBOLS = [
     "b2_index_create", "b2_index_destroy", "b2_index_ntotal", "b2_index_d", "b2_index_metric", "b2_index_dtype",
     "b2_index_device", "b2_index_add", "b2_index_search", "b2_index_search_static", "b2_index_reconstruct_batch", "b2_index_remove_ids",
     "b2_index_merge_from", "b2_index_reset", "b2_index_mmr", "b2_merge_shard_lists", "b2_normalize_l2",
-    "b2_synth_fill", "b2_launch_count", "b2_launch_count_reset", "b2_prof_enable", "b2_prof_read", "b2_last_error",
+    "b2_synth_fill", "b2_launch_count", "b2_launch_count_reset", "b2_prof_enable", "b2_prof_read", "b2_prof_read_kernel", "b2_last_error",
     "b2_version",
 ]
 
@@ -70,6 +70,8 @@ def _load() -> ctypes.CDLL:
     L.b2_prof_enable.restype = i32
     L.b2_prof_read.argtypes = [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(i64), i32]
     L.b2_prof_read.restype = i32
+    L.b2_prof_read_kernel.argtypes = [i32, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(i64), i32]
+    L.b2_prof_read_kernel.restype = i32
     L.b2_last_error.argtypes = []
     L.b2_last_error.restype = ctypes.c_char_p
     L.b2_version.argtypes = []
@@ -110,10 +112,13 @@ def prof_enable(on: bool) -> None:
     lib.b2_prof_enable(1 if on else 0)
 
 
-def prof_read(reset: bool = True):
-    """(summed scan-kernel milliseconds, scan-kernel launches) since the last reset."""
+PROF_SCAN, PROF_GEMM = 0, 1
+
+
+def prof_read(reset: bool = True, kernel: int = PROF_SCAN):
+    """(summed kernel milliseconds, launches) of the scan or the tensor-core kernel since the last reset."""
     ms, n = ctypes.c_double(0.0), ctypes.c_int64(0)
-    lib.b2_prof_read(ctypes.byref(ms), ctypes.byref(n), 1 if reset else 0)
+    lib.b2_prof_read_kernel(kernel, ctypes.byref(ms), ctypes.byref(n), 1 if reset else 0)
     return float(ms.value), int(n.value)
 
 

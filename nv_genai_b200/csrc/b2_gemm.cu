@@ -71,6 +71,7 @@ struct GemmParams {
     int metric;
     int n_qt, n_seg, tiles_per_seg, n_tiles, n_items;
     int num_stages;
+    int trunc_hi;       // fp32 rows: 1 = leave the raw tile as the hi operand (hardware truncation), 0 = round it in place
     const float* norms; // |x|^2 per stored row
     uint64_t* cand;     // [grid][kCandCap][128]
     uint64_t* partial;  // [nq_pad][n_seg][k]
@@ -407,13 +408,22 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             const int idx = i * 128 + xt;
                             const float4 x = b_hi[idx];
                             float4 h, l;
-                            uint32_t u;
-                            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x.x)); h.x = __uint_as_float(u);
-                            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x.y)); h.y = __uint_as_float(u);
-                            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x.z)); h.z = __uint_as_float(u);
-                            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x.w)); h.w = __uint_as_float(u);
+                            if (p.trunc_hi) {
+                                // the tensor core ignores the low 13 mantissa bits of a tf32 operand, so the raw
+                                // fp32 tile already IS the hi part; only lo = x - trunc(x) has to be written
+                                h.x = __uint_as_float(__float_as_uint(x.x) & 0xffffe000u);
+                                h.y = __uint_as_float(__float_as_uint(x.y) & 0xffffe000u);
+                                h.z = __uint_as_float(__float_as_uint(x.z) & 0xffffe000u);
+                                h.w = __uint_as_float(__float_as_uint(x.w) & 0xffffe000u);
+                            } else {
+                                uint32_t u;
+                                asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x.x)); h.x = __uint_as_float(u);
+                                asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x.y)); h.y = __uint_as_float(u);
+                                asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x.z)); h.z = __uint_as_float(u);
+                                asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x.w)); h.w = __uint_as_float(u);
+                                b_hi[idx] = h;
+                            }
                             l.x = x.x - h.x; l.y = x.y - h.y; l.z = x.z - h.z; l.w = x.w - h.w;
-                            b_hi[idx] = h;
                             b_lo[idx] = l;
                         }
                         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -651,7 +661,9 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
             attr[dev & 63] = smem;
         }
     }
+    void* tok = prof_begin(stream);
     kern<<<grid, KIND == 1 ? 320 : 192, smem, stream>>>(tmA, tmB, p);
+    prof_end(tok, 1, stream);
     B2_AFTER_LAUNCH();
     return B2_OK;
 }
@@ -719,6 +731,8 @@ int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtyp
         return B2_ERR_UNSUPPORTED;
     }
     p.num_stages = stages;
+    p.trunc_hi = 0;
+    if (const char* e = getenv("B2_GEMM_TRUNC")) p.trunc_hi = atoi(e) ? 1 : 0;
 
     // scratch: [A parts][qn][tau][partial][candidate logs]
     auto al = [](size_t v) { return (v + 1023) / 1024 * 1024; };

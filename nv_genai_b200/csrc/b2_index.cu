@@ -292,7 +292,14 @@ int b2_prof_enable(int on) {
     prof_enable(on);
     return B2_OK;
 }
-int b2_prof_read(double* scan_ms, int64_t* scan_launches, int reset) { return prof_read(scan_ms, scan_launches, reset); }
+int b2_prof_read(double* scan_ms, int64_t* scan_launches, int reset) { return prof_read(0, scan_ms, scan_launches, reset); }
+int b2_prof_read_kernel(int kernel, double* ms, int64_t* launches, int reset) {
+    if (kernel != B2_PROF_SCAN && kernel != B2_PROF_GEMM) {
+        set_error("b2_prof_read_kernel: unknown kernel %d", kernel);
+        return B2_ERR_INVALID;
+    }
+    return prof_read(kernel, ms, launches, reset);
+}
 
 int b2_index_create(int d, int metric, int dtype, int device, b2_index** out) {
     if (out == nullptr) {

@@ -13,7 +13,9 @@ int scan_pass(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype,
               int nq_valid, int nq_tile, int k, int num_sms, cudaStream_t stream, uint64_t** partial, int* grid);
 
 void prof_enable(int on);
-int prof_read(double* ms, int64_t* n, int reset);
+void* prof_begin(cudaStream_t stream);                       // nullptr when profiling is off
+void prof_end(void* token, int kind, cudaStream_t stream);   // kind 0 = scan kernel, 1 = tensor-core kernel
+int prof_read(int kind, double* ms, int64_t* n, int reset);
 
 // b2_index.cu -------------------------------------------------------------
 // Read-only snapshot of an index handle for entry points implemented next to their kernels.

@@ -23,33 +23,59 @@
 
 namespace b2 {
 
-// ---- optional per-launch timing of the scan kernel (bench.py's roofline figure)
+// ---- optional per-launch timing of the dominant kernels (bench.py's roofline figures)
+// kind 0 = scan_topk_kernel, kind 1 = gemm_topk_kernel.  Events are recorded on the launching stream.
 static std::atomic<int> g_prof_on{0};
 static std::mutex g_prof_mu;
-static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_prof_events;
-static double g_prof_ms = 0.0;
-static long long g_prof_n = 0;
+struct ProfEvents { cudaEvent_t a, b; int kind; };
+static std::vector<ProfEvents> g_prof_events;
+static double g_prof_ms[2] = {0.0, 0.0};
+static long long g_prof_n[2] = {0, 0};
 
 void prof_enable(int on) { g_prof_on.store(on ? 1 : 0); }
 
-int prof_read(double* ms, int64_t* n, int reset) {
+void* prof_begin(cudaStream_t stream) {
+    if (g_prof_on.load() == 0) return nullptr;
+    cudaEvent_t* ev = new cudaEvent_t[2];
+    if (cudaEventCreate(&ev[0]) != cudaSuccess || cudaEventCreate(&ev[1]) != cudaSuccess) {
+        cudaGetLastError();
+        delete[] ev;
+        return nullptr;
+    }
+    cudaEventRecord(ev[0], stream);
+    return ev;
+}
+
+void prof_end(void* token, int kind, cudaStream_t stream) {
+    if (token == nullptr) return;
+    cudaEvent_t* ev = static_cast<cudaEvent_t*>(token);
+    cudaEventRecord(ev[1], stream);
+    {
+        std::lock_guard<std::mutex> lk(g_prof_mu);
+        g_prof_events.push_back({ev[0], ev[1], kind});
+    }
+    delete[] ev;
+}
+
+int prof_read(int kind, double* ms, int64_t* n, int reset) {
+    if (kind < 0 || kind > 1) kind = 0;
     std::lock_guard<std::mutex> lk(g_prof_mu);
     for (auto& ev : g_prof_events) {
         float t = 0.f;
-        if (cudaEventSynchronize(ev.second) == cudaSuccess && cudaEventElapsedTime(&t, ev.first, ev.second) == cudaSuccess) {
-            g_prof_ms += t;
-            ++g_prof_n;
+        if (cudaEventSynchronize(ev.b) == cudaSuccess && cudaEventElapsedTime(&t, ev.a, ev.b) == cudaSuccess) {
+            g_prof_ms[ev.kind] += t;
+            ++g_prof_n[ev.kind];
         }
-        cudaEventDestroy(ev.first);
-        cudaEventDestroy(ev.second);
+        cudaEventDestroy(ev.a);
+        cudaEventDestroy(ev.b);
     }
     cudaGetLastError();
     g_prof_events.clear();
-    if (ms) *ms = g_prof_ms;
-    if (n) *n = g_prof_n;
+    if (ms) *ms = g_prof_ms[kind];
+    if (n) *n = g_prof_n[kind];
     if (reset) {
-        g_prof_ms = 0.0;
-        g_prof_n = 0;
+        g_prof_ms[kind] = 0.0;
+        g_prof_n[kind] = 0;
     }
     return B2_OK;
 }
@@ -188,12 +214,30 @@ __global__ void __launch_bounds__(kScanThreads) scan_topk_kernel(const ScanParam
 #pragma unroll
         for (int i = 0; i < V; ++i) acc[i] = 0.f;
 
+        // Many queries per pass make the loop FMA-heavy (NQ x R x 4 FFMA per 128-bit load) with few warps
+        // resident, so the next chunk's loads are issued before this chunk's arithmetic (register double
+        // buffer); with few queries the loop is load-bound and plain unrolling keeps more loads in flight.
+        constexpr bool PREFETCH = (!BF16) && (NQ >= 8);
+        float4 xnext[PREFETCH ? R : 1];
+        if (PREFETCH) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) xnext[PREFETCH ? r : 0] = ld_stream_f4(rp[r]);
+        }
 #pragma unroll 2
         for (int j = 0; j < nchunks; ++j) {
             if (!BF16) {
                 float4 x[R];
+                if (PREFETCH) {
 #pragma unroll
-                for (int r = 0; r < R; ++r) x[r] = ld_stream_f4(rp[r] + (size_t)j * 512);
+                    for (int r = 0; r < R; ++r) x[r] = xnext[PREFETCH ? r : 0];
+                    if (j + 1 < nchunks) {
+#pragma unroll
+                        for (int r = 0; r < R; ++r) xnext[PREFETCH ? r : 0] = ld_stream_f4(rp[r] + (size_t)(j + 1) * 512);
+                    }
+                } else {
+#pragma unroll
+                    for (int r = 0; r < R; ++r) x[r] = ld_stream_f4(rp[r] + (size_t)j * 512);
+                }
 #pragma unroll
                 for (int qi = 0; qi < NQ; ++qi) {
                     const float4 qv = q4[(qi * nchunks + j) * 32 + lane];
@@ -337,17 +381,11 @@ static int run_scan(ScanParams p, int num_sms, cudaStream_t stream, uint64_t** p
     uint64_t* buf = nullptr;
     B2_CUDA_TRY(cudaMallocAsync(&buf, (size_t)NQ * grid * p.k * sizeof(uint64_t), stream));
     p.partial = buf;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    const bool prof = g_prof_on.load() != 0;
-    if (prof && cudaEventCreate(&ev0) == cudaSuccess && cudaEventCreate(&ev1) == cudaSuccess) cudaEventRecord(ev0, stream);
+    void* tok = prof_begin(stream);
     scan_topk_kernel<METRIC, BF16, NQ, R><<<grid, kScanThreads, smem, stream>>>(p);
     B2_COUNT_LAUNCH();
     cudaError_t e = cudaGetLastError();
-    if (prof && ev0 && ev1) {
-        cudaEventRecord(ev1, stream);
-        std::lock_guard<std::mutex> lk(g_prof_mu);
-        g_prof_events.emplace_back(ev0, ev1);
-    }
+    prof_end(tok, 0, stream);
     if (e != cudaSuccess) {
         cudaFreeAsync(buf, stream);
         set_error("scan kernel launch failed: %s", cudaGetErrorString(e));
