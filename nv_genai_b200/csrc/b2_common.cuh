@@ -114,6 +114,38 @@ __device__ __forceinline__ uint64_t shfl_u64(uint64_t v, int src) {
     return ((uint64_t)hi << 32) | lo;
 }
 
+// Replace the worst entry of a warp-private list by c (if c still beats it) and recompute
+// the worst.  Warp-uniform; `c` must be identical in all lanes.
+__device__ __forceinline__ void warp_list_insert(uint64_t* L, int k, uint64_t c, volatile uint64_t* worst,
+                                                 volatile int* worstpos, int lane) {
+    if (c <= *worst) return;
+    if (lane == 0) L[*worstpos] = c;
+    __syncwarp();
+    uint64_t mn = ~0ull;
+    int mp = 0x7fffffff;
+    for (int i = lane; i < k; i += kWarp) {
+        const uint64_t e = L[i];
+        if (e < mn) {
+            mn = e;
+            mp = i;
+        }
+    }
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) {
+        const uint64_t o = shfl_xor_u64(mn, s);
+        const int op = __shfl_xor_sync(kFull, mp, s);
+        if (o < mn || (o == mn && op < mp)) {
+            mn = o;
+            mp = op;
+        }
+    }
+    if (lane == 0) {
+        *worst = mn;
+        *worstpos = mp;
+    }
+    __syncwarp();
+}
+
 // ---------------------------------------------------------------- block bitonic sort (descending)
 // Sorts buf[0..n) (n a power of two, in shared memory) so that buf[0] is the
 // best candidate.  All `nthreads` threads of the CTA must call it.

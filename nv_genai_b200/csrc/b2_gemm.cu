@@ -47,14 +47,12 @@
 //
 // Algorithmic work per launch: 2 * nq_pad * ntotal * K flop per product (x2 bf16, x3 fp32);
 // corpus bytes ntotal * pitch read ~once from HBM, query tile re-read from L2 per corpus tile.
-#include <cuda.h>
-
-#include <mutex>
-
-#include "b2_common.cuh"
 #include "b2_kernels.h"
+#include "b2_tc.cuh"
 
 namespace b2 {
+
+using namespace tc;
 
 namespace {
 
@@ -64,7 +62,6 @@ constexpr int kMaxStages = 8;
 constexpr int kCandCap = 1024;                     // candidate log entries per query per CTA
 constexpr int kGemmMaxK = 128;                     // heap slots per query (k <= 128 on this path)
 constexpr int kEpiThreads = 128;
-constexpr unsigned long long kWatchdogCycles = 20000000000ull;  // ~10 s: a broken pipeline traps instead of hanging
 
 struct GemmParams {
     int nq, nq_pad;
@@ -81,86 +78,6 @@ struct GemmParams {
     uint32_t* tau;      // [nq_pad] ordered image of an exclusive lower bound of the final k-th key
 };
 
-// ------------------------------------------------------------------ PTX wrappers
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t ok = 0;
-    unsigned long long t0 = 0;
-    while (true) {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(ok)
-            : "r"(bar), "r"(parity)
-            : "memory");
-        if (ok) break;
-        const unsigned long long now = clock64();
-        if (t0 == 0) t0 = now;
-        if (now - t0 > kWatchdogCycles) __trap();
-    }
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int x, int y, uint32_t bar) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-        ::"r"(dst), "l"(map), "r"(bar), "r"(x), "r"(y)
-        : "memory");
-}
-__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tcgen05_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-template <int KIND>
-__device__ __forceinline__ void umma(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-    if (KIND == 0) {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-            ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
-            : "memory");
-    } else {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-            "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
-            ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
-            : "memory");
-    }
-}
-// K-major operand tile, SWB-byte swizzle (64 or 128): rows of SWB bytes, 8-row groups 8*SWB bytes apart.
-template <int SWB>
-__device__ __forceinline__ uint64_t smem_desc(uint32_t addr) {
-    uint64_t d = 0;
-    d |= (uint64_t)((addr >> 4) & 0x3fff);        // start address
-    d |= (uint64_t)1 << 16;                       // leading byte offset (unused for swizzled K-major)
-    d |= (uint64_t)((8 * SWB) >> 4) << 32;        // stride byte offset: 8 rows x SWB bytes
-    d |= (uint64_t)1 << 46;                       // descriptor version (Blackwell)
-    d |= (uint64_t)(SWB == 128 ? 2 : 4) << 61;    // SWIZZLE_128B / SWIZZLE_64B
-    return d;
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
-          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
-          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-        : "r"(taddr)
-        : "memory");
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // Register-only v[c] for a run-time c (a dynamically indexed array would live in local memory).
 __device__ __forceinline__ float select32(const float (&v)[32], int c) {
@@ -595,53 +512,9 @@ __global__ void prep_queries_kernel(const float* __restrict__ q, int nq, int d, 
 #pragma unroll
     for (int s = 16; s >= 1; s >>= 1) ss += __shfl_xor_sync(kFull, ss, s);
     if (lane == 0) {
-        qn[row] = ss;
-        tau[row] = 0x00800000u;  // image of -FLT_MAX as the exclusive bound: admits every key > -FLT_MAX
+        if (qn != nullptr) qn[row] = ss;
+        if (tau != nullptr) tau[row] = 0x00800000u;  // image of -FLT_MAX as the exclusive bound: admits every key > -FLT_MAX
     }
-}
-
-// ------------------------------------------------------------------ host side
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-EncodeTiledFn encode_tiled() {
-    static EncodeTiledFn fn = nullptr;
-    static std::once_flag once;
-    std::call_once(once, [] {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult qres;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
-            qres == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<EncodeTiledFn>(p);
-        else
-            cudaGetLastError();
-    });
-    return fn;
-}
-
-int make_map(CUtensorMap* m, bool bf16, int swb, const void* base, uint64_t inner_elems, uint64_t rows,
-             uint64_t pitch_bytes, uint32_t box_rows) {
-    EncodeTiledFn fn = encode_tiled();
-    if (fn == nullptr) {
-        set_error("cuTensorMapEncodeTiled is not available from this driver");
-        return B2_ERR_UNSUPPORTED;
-    }
-    const cuuint64_t dims[2] = {inner_elems, rows};
-    const cuuint64_t strides[1] = {pitch_bytes};
-    const cuuint32_t box[2] = {(cuuint32_t)(swb / (bf16 ? 2 : 4)), box_rows};
-    const cuuint32_t estr[2] = {1, 1};
-    const CUresult r = fn(m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
-                          const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                          swb == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
-                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) {
-        set_error("cuTensorMapEncodeTiled failed (%d) for %llu x %llu, pitch %llu", (int)r,
-                  (unsigned long long)inner_elems, (unsigned long long)rows, (unsigned long long)pitch_bytes);
-        return B2_ERR_CUDA;
-    }
-    return B2_OK;
 }
 
 size_t gemm_smem_bytes(bool fp32_rows, int na, int swb, int stages, int k) {
@@ -672,6 +545,18 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
 }
 
 }  // namespace
+
+int prep_queries(const float* q_dev, int nq, int d, int nq_pad, int kp, int na, bool bf16, void* A, float* qn,
+                 uint32_t* tau, cudaStream_t stream) {
+    const int wpb = 8;
+    const int blocks = (nq_pad + wpb - 1) / wpb;
+    if (bf16)
+        prep_queries_kernel<0><<<blocks, wpb * 32, 0, stream>>>(q_dev, nq, d, nq_pad, kp, na, A, qn, tau);
+    else
+        prep_queries_kernel<1><<<blocks, wpb * 32, 0, stream>>>(q_dev, nq, d, nq_pad, kp, na, A, qn, tau);
+    B2_AFTER_LAUNCH();
+    return B2_OK;
+}
 
 bool gemm_path_supported(int64_t n, int d, int dtype, int k, int64_t nq) {
     if (getenv("B2_NO_TENSOR") != nullptr) return false;
@@ -756,19 +641,7 @@ int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtyp
     CUtensorMap tmA, tmB;
     rc = make_map(&tmA, bf16, swb, A, (uint64_t)kp, (uint64_t)na * p.nq_pad, kbytes, kTileM);
     if (rc == B2_OK) rc = make_map(&tmB, bf16, swb, rows, (uint64_t)(pitch_bytes / elem), (uint64_t)n, pitch_bytes, kTileN);
-    if (rc == B2_OK) {
-        const int wpb = 8;
-        const int blocks = (p.nq_pad + wpb - 1) / wpb;
-        if (bf16)
-            prep_queries_kernel<0><<<blocks, wpb * 32, 0, stream>>>(q_dev, (int)nq, d, p.nq_pad, kp, na, A, qn, p.tau);
-        else
-            prep_queries_kernel<1><<<blocks, wpb * 32, 0, stream>>>(q_dev, (int)nq, d, p.nq_pad, kp, na, A, qn, p.tau);
-        B2_COUNT_LAUNCH();
-        if (cudaGetLastError() != cudaSuccess) {
-            set_error("prep_queries launch failed");
-            rc = B2_ERR_CUDA;
-        }
-    }
+    if (rc == B2_OK) rc = prep_queries(q_dev, (int)nq, d, p.nq_pad, kp, na, bf16, A, qn, p.tau, stream);
     if (rc == B2_OK) {
         const int variant = (bf16 ? 0 : 4) + (na == 2 ? 2 : 0) + (swb == 128 ? 1 : 0);
         switch (variant) {

@@ -37,6 +37,10 @@ int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metri
 
 // b2_gemm.cu ---------------------------------------------------------------
 // Tensor-core search for batches of >= 20 queries (faiss's BLAS threshold), k <= 128.
+// q [nq][d] fp32 -> A [na][nq_pad][kp] operand parts (bf16 hi/lo, or fp32 words holding tf32 hi/lo), zero padded;
+// optional qn[row] = |q|^2 and tau[row] = initial admission bound.
+int prep_queries(const float* q_dev, int nq, int d, int nq_pad, int kp, int na, bool bf16, void* A, float* qn,
+                 uint32_t* tau, cudaStream_t stream);
 bool gemm_path_supported(int64_t n, int d, int dtype, int k, int64_t nq);
 int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* norms,
                 const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream);
@@ -61,6 +65,12 @@ int compact_rows(void* rows, size_t pitch_bytes, float* norms, const int64_t* sr
 int mmr_select(const float* q, int d, int nq, const float* cand_rows /*[nq][fetch_k][d]*/, const int64_t* cand_ids,
                const float* cand_scores, int fetch_k, int k, float lambda_mult, int64_t* out_ids, float* out_scores,
                cudaStream_t stream);
+
+// b2_scan_tc.cu ------------------------------------------------------------
+// Tensor-core scan for 3..16 queries (inner product): the corpus is the M operand, HBM-bound.
+bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t nq);
+int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, const float* q_dev, int nq, int k,
+                   int num_sms, float* D, int64_t* I, cudaStream_t stream);
 
 // b2_synth.cu --------------------------------------------------------------
 int synth_fill(float* out, int64_t row0, int64_t nrows, int d, uint64_t seed, cudaStream_t stream);

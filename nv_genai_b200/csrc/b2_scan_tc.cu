@@ -1,0 +1,363 @@
+// Small-batch exact scan on the tensor cores: 3..16 queries, inner product, one pass over the rows.
+//
+// Replaces faiss exhaustive_inner_product_seq + HeapResultHandler (faiss/utils/distances.cpp, the
+// nq < 20 path of IndexFlat::search), the same routine b2_scan.cu replaces, for the query counts
+// where the FP32 pipe cannot keep up with HBM: 16 queries x 10M x 1024 rows are 1.6e11 FMAs, 4.7 ms
+// at the FFMA peak against 5.8 ms of HBM time, and the FFMA scan reaches 13.7 ms.  Reached from
+// index.search at /root/reference/RetrievalAugmentedGeneration/examples/nvidia_api_catalog/chains.py:122-123
+// when a handful of requests are batched (BASELINE.json configs[1], batch 16).
+//
+// Mapping: the CORPUS is the M operand.  A tile is 128 consecutive rows (TMEM lanes), the 16 queries
+// are the N operand, K = the row, streamed by TMA in 128-byte swizzled slices straight from the row
+// store; the query slice ([q_hi; q_lo], 32 x 128 B) rides along with every row slice (L2-resident).
+//   bf16 rows:  D1[128 x 32] += A . [q_hi; q_lo]^T                      (kind::f16; q kept to ~16 bits)
+//   fp32 rows:  D1[128 x 32] += A_hi . [q_hi; q_lo]^T,  D2[128 x 16] += A_lo . q_hi^T   (3xTF32)
+//               A_hi is the raw tile (the tensor core ignores the low 13 mantissa bits),
+//               A_lo = x - trunc_tf32(x) is written by four transform warps into a 3-slot ring.
+//   score(row, j) = D1[row, j] + (D1[row, 16 + j] + D2[row, j]), summed in fp32 registers.
+// MMA time per slice is 64-96 cycles against ~650 cycles of HBM time per 16 KB slice and SM, so the
+// kernel is HBM-bound like the FFMA scan at batch 1; the tensor pipe is ~15 % busy by design.
+// Selection is the FFMA scan's: one thread = one row, per-(warp, query) top-k lists in shared
+// memory guarded by their worst entry, CTA merge at the end, same partial-list format, same merge
+// kernel, same tie rule (equal scores -> lowest id).
+//
+// Algorithmic HBM bytes per launch = n * pitch_bytes (each row read exactly once).
+#include "b2_kernels.h"
+#include "b2_tc.cuh"
+
+namespace b2 {
+
+using namespace tc;
+
+namespace {
+
+constexpr int kTileRows = 128;
+constexpr int kNQ = 16;                          // queries per pass (padded)
+constexpr int kSlice = 128;                      // bytes of K per stage (swizzle width)
+constexpr int kATile = kTileRows * kSlice;       // 16 KB
+constexpr int kBTile = 2 * kNQ * kSlice;         // 4 KB: [q_hi; q_lo]
+constexpr int kStage = kATile + kBTile;          // 20 KB
+constexpr int kLoSlots = 3;
+constexpr int kMaxStages = 8;
+constexpr int kEpi = 128;                        // epilogue threads
+constexpr int kEpiWarps = 4;
+
+struct ScanTcParams {
+    uint32_t n;
+    int nq, k, kpad, kslices, n_tiles, num_stages;
+    uint64_t* partial;  // [nq][gridDim.x][k] sorted best-first
+};
+
+__device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+// bitonic sort (descending) by the 128 epilogue threads, named barrier 1
+__device__ __forceinline__ void epi_bitonic_desc(uint64_t* buf, int n, int tid) {
+    for (int size = 2; size <= n; size <<= 1) {
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            epi_sync();
+            for (int t = tid; t < (n >> 1); t += kEpi) {
+                const int lo = 2 * t - (t & (stride - 1));
+                const int hi = lo + stride;
+                const bool desc = ((lo & size) == 0);
+                const uint64_t a = buf[lo], b = buf[hi];
+                if ((a < b) == desc) {
+                    buf[lo] = b;
+                    buf[hi] = a;
+                }
+            }
+        }
+    }
+    epi_sync();
+}
+
+// KIND 0: bf16 rows (kind::f16).  KIND 1: fp32 rows (kind::tf32, 3xTF32).
+template <int KIND>
+__global__ void __launch_bounds__(KIND == 1 ? 320 : 192, 1)
+scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant__ CUtensorMap tmQ, const ScanTcParams p) {
+    constexpr int ELEM = (KIND == 0) ? 2 : 4;
+    constexpr int KSLICE = kSlice / ELEM;
+    constexpr uint32_t FMT = (KIND == 0) ? 1u : 2u;
+    constexpr uint32_t IDESC_BASE = (1u << 4) | (FMT << 7) | (FMT << 10) | ((uint32_t)(kTileRows >> 4) << 24);
+    constexpr uint32_t IDESC_N32 = IDESC_BASE | ((32u >> 3) << 17);
+    constexpr uint32_t IDESC_N16 = IDESC_BASE | ((16u >> 3) << 17);
+    constexpr uint32_t kTmemCols = 128;  // 2 buffers x 64 columns (D1: 32, D2: 16)
+
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
+    const int S = p.num_stages;
+    uint8_t* stages = smem;
+    uint8_t* lo_tiles = stages + (size_t)S * kStage;
+    uint64_t* lists = reinterpret_cast<uint64_t*>(lo_tiles + (KIND == 1 ? kLoSlots * kATile : 0));  // [kNQ][4 warps][kpad]
+    uint64_t* worst_s = lists + (size_t)kNQ * kEpiWarps * p.kpad;                                    // [kNQ][4]
+    int* worstpos_s = reinterpret_cast<int*>(worst_s + kNQ * kEpiWarps);                             // [kNQ][4]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(worstpos_s + kNQ * kEpiWarps);
+    uint64_t* full_bar = bars;
+    uint64_t* empty_bar = bars + kMaxStages;
+    uint64_t* xf_bar = bars + 2 * kMaxStages;
+    uint64_t* lo_empty_bar = bars + 3 * kMaxStages;
+    uint64_t* tfull_bar = lo_empty_bar + kLoSlots;
+    uint64_t* tempty_bar = tfull_bar + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    if (tid == 0) {
+        for (int s = 0; s < S; ++s) {
+            mbar_init(smem_u32(full_bar + s), 1);
+            mbar_init(smem_u32(empty_bar + s), 1);
+            mbar_init(smem_u32(xf_bar + s), 4);
+        }
+        for (int s = 0; s < kLoSlots; ++s) mbar_init(smem_u32(lo_empty_bar + s), 1);
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(smem_u32(tfull_bar + b), 1);
+            mbar_init(smem_u32(tempty_bar + b), kEpiWarps);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 5) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (warp < kEpiWarps) {
+        for (int i = tid; i < kNQ * kEpiWarps * p.kpad; i += kEpi) lists[i] = B2_SENTINEL;
+        for (int i = tid; i < kNQ * kEpiWarps; i += kEpi) {
+            worst_s[i] = B2_SENTINEL;
+            worstpos_s[i] = 0;
+        }
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 4) {
+        // ================= TMA producer
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+                for (int ks = 0; ks < p.kslices; ++ks) {
+                    mbar_wait(smem_u32(empty_bar + stage), phase ^ 1u);
+                    const uint32_t fb = smem_u32(full_bar + stage);
+                    mbar_expect_tx(fb, (uint32_t)kStage);
+                    const uint32_t sb = smem_u32(stages + (size_t)stage * kStage);
+                    tma_load_2d(sb, &tmRows, ks * KSLICE, tile * kTileRows, fb);
+                    tma_load_2d(sb + kATile, &tmQ, ks * KSLICE, 0, fb);
+                    if (++stage == S) {
+                        stage = 0;
+                        phase ^= 1u;
+                    }
+                }
+            }
+        }
+    } else if (warp == 5) {
+        // ================= MMA issuer
+        if (lane == 0) {
+            int stage = 0, lo_slot = 0;
+            uint32_t phase = 0, tc = 0;
+            for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++tc) {
+                const uint32_t buf = tc & 1u, par = (tc >> 1) & 1u;
+                mbar_wait(smem_u32(tempty_bar + buf), par ^ 1u);
+                tcgen05_fence_after();
+                const uint32_t d1 = tmem_base + buf * 64u, d2 = d1 + 32u;
+                for (int ks = 0; ks < p.kslices; ++ks) {
+                    mbar_wait(smem_u32((KIND == 1 ? xf_bar : full_bar) + stage), phase);
+                    tcgen05_fence_after();
+                    const uint32_t a = smem_u32(stages + (size_t)stage * kStage);
+                    const uint32_t b = a + kATile;
+                    const uint32_t alo = smem_u32(lo_tiles + (size_t)lo_slot * kATile);
+#pragma unroll
+                    for (int j = 0; j < kSlice / 32; ++j) {
+                        const uint32_t acc = (ks | j) ? 1u : 0u;
+                        const uint64_t bd = smem_desc<kSlice>(b + j * 32);
+                        umma<KIND>(d1, smem_desc<kSlice>(a + j * 32), bd, IDESC_N32, acc);
+                        if (KIND == 1) umma<KIND>(d2, smem_desc<kSlice>(alo + j * 32), bd, IDESC_N16, acc);
+                    }
+                    tcgen05_commit(smem_u32(empty_bar + stage));
+                    if (KIND == 1) {
+                        tcgen05_commit(smem_u32(lo_empty_bar + lo_slot));
+                        if (++lo_slot == kLoSlots) lo_slot = 0;
+                    }
+                    if (++stage == S) {
+                        stage = 0;
+                        phase ^= 1u;
+                    }
+                }
+                tcgen05_commit(smem_u32(tfull_bar + buf));
+            }
+        }
+    } else if (warp >= 6) {
+        // ================= fp32 rows: remainder tile A_lo = x - trunc_tf32(x)
+        if (KIND == 1) {
+            const int xt = tid - 192;
+            int stage = 0, lo_slot = 0;
+            uint32_t phase = 0, lo_phase = 0;
+            for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+                for (int ks = 0; ks < p.kslices; ++ks) {
+                    mbar_wait(smem_u32(full_bar + stage), phase);
+                    mbar_wait(smem_u32(lo_empty_bar + lo_slot), lo_phase ^ 1u);
+                    const float4* src = reinterpret_cast<const float4*>(stages + (size_t)stage * kStage);
+                    float4* dst = reinterpret_cast<float4*>(lo_tiles + (size_t)lo_slot * kATile);
+#pragma unroll
+                    for (int i = 0; i < kATile / 16 / 128; ++i) {
+                        const float4 x = src[i * 128 + xt];
+                        float4 l;
+                        l.x = x.x - __uint_as_float(__float_as_uint(x.x) & 0xffffe000u);
+                        l.y = x.y - __uint_as_float(__float_as_uint(x.y) & 0xffffe000u);
+                        l.z = x.z - __uint_as_float(__float_as_uint(x.z) & 0xffffe000u);
+                        l.w = x.w - __uint_as_float(__float_as_uint(x.w) & 0xffffe000u);
+                        dst[i * 128 + xt] = l;
+                    }
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(smem_u32(xf_bar + stage));
+                    if (++lo_slot == kLoSlots) {
+                        lo_slot = 0;
+                        lo_phase ^= 1u;
+                    }
+                    if (++stage == S) {
+                        stage = 0;
+                        phase ^= 1u;
+                    }
+                }
+            }
+        }
+    } else {
+        // ================= epilogue: warps 0..3, thread = corpus row = TMEM lane
+        uint32_t tc = 0;
+        for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++tc) {
+            const uint32_t buf = tc & 1u, par = (tc >> 1) & 1u;
+            mbar_wait(smem_u32(tfull_bar + buf), par);
+            tcgen05_fence_after();
+            const uint32_t taddr = tmem_base + buf * 64u + ((uint32_t)(warp * 32) << 16);
+            uint32_t d1[32];
+            uint32_t d2[16];
+            tmem_ld32(taddr, d1);
+            if (KIND == 1) tmem_ld16(taddr + 32u, d2);
+            tmem_ld_wait();
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(tempty_bar + buf));  // registers hold the tile: TMEM is free again
+            const uint32_t row = (uint32_t)tile * kTileRows + warp * 32 + lane;
+#pragma unroll
+            for (int j = 0; j < kNQ; ++j) {
+                if (j < p.nq) {  // warp-uniform
+                    float small = __uint_as_float(d1[kNQ + j]);
+                    if (KIND == 1) small += __uint_as_float(d2[j]);
+                    const float key = (__uint_as_float(d1[j]) + small) + 0.0f;
+                    const uint64_t cand = pack_cand(key, row);
+                    const int li = j * kEpiWarps + warp;
+                    const bool pass = row < p.n && key > -FLT_MAX && cand > worst_s[li];
+                    unsigned m = __ballot_sync(kFull, pass);
+                    while (m) {
+                        const int src = __ffs(m) - 1;
+                        m &= m - 1;
+                        const uint64_t c = shfl_u64(cand, src);
+                        warp_list_insert(lists + (size_t)li * p.kpad, p.k, c, worst_s + li, worstpos_s + li, lane);
+                    }
+                }
+            }
+        }
+        // ---- CTA merge: per query, sort the four warps' lists (contiguous) and emit the best k
+        const int region = kEpiWarps * p.kpad;
+        for (int qi = 0; qi < p.nq; ++qi) {
+            uint64_t* buf = lists + (size_t)qi * region;
+            epi_bitonic_desc(buf, region, tid);
+            uint64_t* out = p.partial + ((size_t)qi * gridDim.x + blockIdx.x) * p.k;
+            for (int i = tid; i < p.k; i += kEpi) out[i] = buf[i];
+        }
+    }
+
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 5) {
+        tcgen05_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+    }
+}
+
+size_t scan_tc_smem_bytes(bool fp32_rows, int stages, int kpad) {
+    return 1024 + (size_t)stages * kStage + (fp32_rows ? (size_t)kLoSlots * kATile : 0) +
+           (size_t)kNQ * kEpiWarps * kpad * 8 + (size_t)kNQ * kEpiWarps * 12 + (3 * kMaxStages + kLoSlots + 4) * 8 + 16;
+}
+
+template <int KIND>
+int launch_scan_tc(const CUtensorMap& tmRows, const CUtensorMap& tmQ, const ScanTcParams& p, int grid, size_t smem,
+                   cudaStream_t stream) {
+    auto kern = scan_tc_kernel<KIND>;
+    static std::mutex mu;
+    static size_t attr[64] = {0};
+    int dev = 0;
+    B2_CUDA_TRY(cudaGetDevice(&dev));
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (smem > attr[dev & 63]) {
+            B2_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            attr[dev & 63] = smem;
+        }
+    }
+    void* tok = prof_begin(stream);
+    kern<<<grid, KIND == 1 ? 320 : 192, smem, stream>>>(tmRows, tmQ, p);
+    prof_end(tok, 0, stream);
+    B2_AFTER_LAUNCH();
+    return B2_OK;
+}
+
+}  // namespace
+
+bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t nq) {
+    if (getenv("B2_NO_TENSOR") != nullptr || getenv("B2_NO_SCAN_TC") != nullptr) return false;
+    const int elem = dtype == B2_DTYPE_BF16 ? 2 : 4;
+    int min_nq = 3;
+    if (const char* e = getenv("B2_SCAN_TC_MIN_NQ")) min_nq = atoi(e);
+    return metric == B2_METRIC_IP && nq >= min_nq && nq <= kNQ && k <= 128 && n >= 4096 && n < ((int64_t)1 << 31) &&
+           (int64_t)d * elem >= kSlice;
+}
+
+int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, const float* q_dev, int nq, int k,
+                   int num_sms, float* D, int64_t* I, cudaStream_t stream) {
+    const bool bf16 = dtype == B2_DTYPE_BF16;
+    const int elem = bf16 ? 2 : 4;
+    const size_t kbytes = (((size_t)d * elem + kSlice - 1) / kSlice) * kSlice;
+    const int kp = (int)(kbytes / elem);
+
+    ScanTcParams p;
+    p.n = (uint32_t)n;
+    p.nq = nq;
+    p.k = k;
+    p.kpad = next_pow2(k < 32 ? 32 : k);
+    p.kslices = (int)(kbytes / kSlice);
+    p.n_tiles = (int)((n + kTileRows - 1) / kTileRows);
+    int stages = kMaxStages;
+    while (stages > 2 && scan_tc_smem_bytes(!bf16, stages, p.kpad) > 227 * 1024) --stages;
+    const size_t smem = scan_tc_smem_bytes(!bf16, stages, p.kpad);
+    if (smem > 227 * 1024) {
+        set_error("tensor-core scan: k=%d does not fit shared memory", k);
+        return B2_ERR_UNSUPPORTED;
+    }
+    p.num_stages = stages;
+    const int grid = (int)std::min<long long>(num_sms, p.n_tiles);
+
+    auto al = [](size_t v) { return (v + 1023) / 1024 * 1024; };
+    const size_t q_bytes = al((size_t)2 * kNQ * kbytes);
+    const size_t part_bytes = al((size_t)nq * grid * k * 8);
+    char* blk = nullptr;
+    B2_CUDA_TRY(cudaMallocAsync(&blk, q_bytes + part_bytes, stream));
+    void* Q = blk;
+    p.partial = reinterpret_cast<uint64_t*>(blk + q_bytes);
+
+    CUtensorMap tmRows, tmQ;
+    int rc = make_map(&tmRows, bf16, kSlice, rows, (uint64_t)(pitch_bytes / elem), (uint64_t)n, pitch_bytes, kTileRows);
+    if (rc == B2_OK) rc = make_map(&tmQ, bf16, kSlice, Q, (uint64_t)kp, (uint64_t)2 * kNQ, kbytes, 2 * kNQ);
+    if (rc == B2_OK) rc = prep_queries(q_dev, nq, d, kNQ, kp, 2, bf16, Q, nullptr, nullptr, stream);
+    if (rc == B2_OK)
+        rc = bf16 ? launch_scan_tc<0>(tmRows, tmQ, p, grid, smem, stream) : launch_scan_tc<1>(tmRows, tmQ, p, grid, smem, stream);
+    if (rc == B2_OK) rc = merge_partials(p.partial, nq, grid, k, B2_METRIC_IP, 0, D, I, (size_t)k, stream);
+    cudaFreeAsync(blk, stream);
+    return rc;
+}
+
+}  // namespace b2

@@ -172,3 +172,48 @@ def test_large_batch_1024_queries_k100_property():
     sample = [0, 1, 127, 128, 500, 1023]
     Ds, Is = idx.search(q[sample], k)  # 6 queries -> scan kernel
     assert_parity(D[sample], I[sample], Ds, Is, x, q[sample], metric_ip=True)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# tensor-core scan (b2_scan_tc.cu): 3..16 queries, inner product, corpus as the M operand
+@pytest.mark.parametrize("dtype", ["float32", "bfloat16"])
+@pytest.mark.parametrize("nq,k", [(3, 10), (9, 1), (16, 10), (16, 100), (5, 128)])
+def test_small_batch_tensor_scan_matches_sequential_oracle(dtype, nq, k):
+    n, d = 70_001, 1024  # ragged last tile (128-row tiles)
+    x, q = _data(n, d, nq, True, seed=100 + nq)
+    idx = _mk(flat.METRIC_IP, d, dtype)
+    idx.add(x)
+    (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, k))
+    assert launches == 3, launches  # prep + scan_tc + merge (the FFMA scan is 2)
+    xr = flat.round_bf16(x) if dtype == "bfloat16" else x
+    Dr, Ir, _ = flat.search_seq(xr, q, k, flat.METRIC_IP)
+    assert_parity(D, I, Dr, Ir, xr, q, metric_ip=True)
+    assert np.all(np.diff(D, axis=1) <= 0)
+
+
+def test_small_batch_tensor_scan_ties_and_dims():
+    """Planted duplicates (lowest id first) and a dimension that is not a multiple of the 128-byte K slice."""
+    n, d, nq, k = 30_000, 200, 7, 6
+    x, q = _data(n, d, nq, True, seed=21)
+    planted = np.array([3, 121, 128, 4_000, 12_345, 20_000, 29_999 - 7])  # + r, r < 7: all distinct; 121+6 and 128 straddle a tile
+    for r in range(nq):
+        x[planted + r] = q[r]
+    idx = _mk(flat.METRIC_IP, d)
+    idx.add(x)
+    D, I = idx.search(q, k)
+    for r in range(nq):
+        assert np.array_equal(I[r], np.sort(planted + r)[:k]), (r, I[r])
+    Dr, Ir, _ = flat.search_seq(x, q, k, flat.METRIC_IP)
+    assert_parity(D, I, Dr, Ir, x, q, metric_ip=True)
+
+
+def test_small_batch_l2_keeps_the_direct_form():
+    """L2 below 20 queries stays on the FFMA scan (faiss's direct form: a stored copy of the query is at distance 0.0)."""
+    n, d, nq = 10_000, 256, 8
+    x, q = _data(n, d, nq, False, seed=31)
+    x[77] = q[2]
+    idx = _mk(flat.METRIC_L2, d)
+    idx.add(x)
+    (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, 4))
+    assert launches == 2
+    assert I[2, 0] == 77 and D[2, 0] == 0.0
