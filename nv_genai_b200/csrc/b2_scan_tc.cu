@@ -13,7 +13,10 @@
 //   bf16 rows:  D1[128 x 32] += A . [q_hi; q_lo]^T                      (kind::f16; q kept to ~16 bits)
 //   fp32 rows:  D1[128 x 32] += A_hi . [q_hi; q_lo]^T,  D2[128 x 16] += A_lo . q_hi^T   (3xTF32)
 //               A_hi is the raw tile (the tensor core ignores the low 13 mantissa bits),
-//               A_lo = x - trunc_tf32(x) is written by four transform warps into a 3-slot ring.
+//               A_lo = x - trunc_tf32(x) is computed by eight transform warps (thread = row) and stored
+//               straight into TENSOR MEMORY (tcgen05.st, 4-slot ring of 32 columns); the second MMA
+//               takes its A operand from TMEM, so the remainder never costs shared-memory bandwidth
+//               (with A_lo in shared memory the kernel was smem-bound: 8.4 ms vs 5.8 ms of HBM time).
 //   score(row, j) = D1[row, j] + (D1[row, 16 + j] + D2[row, j]), summed in fp32 registers.
 // MMA time per slice is 64-96 cycles against ~650 cycles of HBM time per 16 KB slice and SM, so the
 // kernel is HBM-bound like the FFMA scan at batch 1; the tensor pipe is ~15 % busy by design.
@@ -37,10 +40,12 @@ constexpr int kSlice = 128;                      // bytes of K per stage (swizzl
 constexpr int kATile = kTileRows * kSlice;       // 16 KB
 constexpr int kBTile = 2 * kNQ * kSlice;         // 4 KB: [q_hi; q_lo]
 constexpr int kStage = kATile + kBTile;          // 20 KB
-constexpr int kLoSlots = 3;
-constexpr int kMaxStages = 8;
+constexpr int kLoSlots = 4;                       // fp32 rows: A_lo slices resident in TMEM
+constexpr int kMaxStages = 10;
 constexpr int kEpi = 128;                        // epilogue threads
 constexpr int kEpiWarps = 4;
+constexpr int kXfWarps = 8;                       // fp32 rows: transform warps (256 threads, 4 x 16 B each per slice)
+constexpr int kThreadsBf16 = 192, kThreadsFp32 = 192 + kXfWarps * 32;
 
 struct ScanTcParams {
     uint32_t n;
@@ -72,7 +77,7 @@ __device__ __forceinline__ void epi_bitonic_desc(uint64_t* buf, int n, int tid) 
 
 // KIND 0: bf16 rows (kind::f16).  KIND 1: fp32 rows (kind::tf32, 3xTF32).
 template <int KIND>
-__global__ void __launch_bounds__(KIND == 1 ? 320 : 192, 1)
+__global__ void __launch_bounds__(KIND == 1 ? kThreadsFp32 : kThreadsBf16, 1)
 scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant__ CUtensorMap tmQ, const ScanTcParams p) {
     constexpr int ELEM = (KIND == 0) ? 2 : 4;
     constexpr int KSLICE = kSlice / ELEM;
@@ -80,15 +85,15 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
     constexpr uint32_t IDESC_BASE = (1u << 4) | (FMT << 7) | (FMT << 10) | ((uint32_t)(kTileRows >> 4) << 24);
     constexpr uint32_t IDESC_N32 = IDESC_BASE | ((32u >> 3) << 17);
     constexpr uint32_t IDESC_N16 = IDESC_BASE | ((16u >> 3) << 17);
-    constexpr uint32_t kTmemCols = 128;  // 2 buffers x 64 columns (D1: 32, D2: 16)
+    constexpr uint32_t kTmemCols = 256;  // 2 buffers x 64 columns (D1: 32, D2: 16) + 4 x 32 columns of A_lo slices
+    constexpr uint32_t kLoCol0 = 128;
 
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
     const int S = p.num_stages;
     uint8_t* stages = smem;
-    uint8_t* lo_tiles = stages + (size_t)S * kStage;
-    uint64_t* lists = reinterpret_cast<uint64_t*>(lo_tiles + (KIND == 1 ? kLoSlots * kATile : 0));  // [kNQ][4 warps][kpad]
+    uint64_t* lists = reinterpret_cast<uint64_t*>(stages + (size_t)S * kStage);  // [kNQ][4 warps][kpad]
     uint64_t* worst_s = lists + (size_t)kNQ * kEpiWarps * p.kpad;                                    // [kNQ][4]
     int* worstpos_s = reinterpret_cast<int*>(worst_s + kNQ * kEpiWarps);                             // [kNQ][4]
     uint64_t* bars = reinterpret_cast<uint64_t*>(worstpos_s + kNQ * kEpiWarps);
@@ -106,7 +111,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
         for (int s = 0; s < S; ++s) {
             mbar_init(smem_u32(full_bar + s), 1);
             mbar_init(smem_u32(empty_bar + s), 1);
-            mbar_init(smem_u32(xf_bar + s), 4);
+            mbar_init(smem_u32(xf_bar + s), kXfWarps);
         }
         for (int s = 0; s < kLoSlots; ++s) mbar_init(smem_u32(lo_empty_bar + s), 1);
         for (int b = 0; b < 2; ++b) {
@@ -168,13 +173,13 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
                     tcgen05_fence_after();
                     const uint32_t a = smem_u32(stages + (size_t)stage * kStage);
                     const uint32_t b = a + kATile;
-                    const uint32_t alo = smem_u32(lo_tiles + (size_t)lo_slot * kATile);
+                    const uint32_t alo = tmem_base + kLoCol0 + (uint32_t)lo_slot * 32u;  // TMEM columns of this slice's A_lo
 #pragma unroll
                     for (int j = 0; j < kSlice / 32; ++j) {
                         const uint32_t acc = (ks | j) ? 1u : 0u;
                         const uint64_t bd = smem_desc<kSlice>(b + j * 32);
                         umma<KIND>(d1, smem_desc<kSlice>(a + j * 32), bd, IDESC_N32, acc);
-                        if (KIND == 1) umma<KIND>(d2, smem_desc<kSlice>(alo + j * 32), bd, IDESC_N16, acc);
+                        if (KIND == 1) umma_tf32_ts(d2, alo + j * 8, bd, IDESC_N16, acc);
                     }
                     tcgen05_commit(smem_u32(empty_bar + stage));
                     if (KIND == 1) {
@@ -190,28 +195,32 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
             }
         }
     } else if (warp >= 6) {
-        // ================= fp32 rows: remainder tile A_lo = x - trunc_tf32(x)
+        // ================= fp32 rows: A_lo = x - trunc_tf32(x), thread = row, written to TMEM
         if (KIND == 1) {
-            const int xt = tid - 192;
+            const int quarter = warp & 3;                 // the TMEM lanes this warp may touch: 32 * (warp % 4) ..
+            const int half = (warp - 6) >> 2;             // which 64 bytes of the 128-byte row slice
+            const int r = quarter * 32 + lane;            // row of the tile = TMEM lane
             int stage = 0, lo_slot = 0;
             uint32_t phase = 0, lo_phase = 0;
             for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
                 for (int ks = 0; ks < p.kslices; ++ks) {
                     mbar_wait(smem_u32(full_bar + stage), phase);
                     mbar_wait(smem_u32(lo_empty_bar + lo_slot), lo_phase ^ 1u);
-                    const float4* src = reinterpret_cast<const float4*>(stages + (size_t)stage * kStage);
-                    float4* dst = reinterpret_cast<float4*>(lo_tiles + (size_t)lo_slot * kATile);
+                    tcgen05_fence_after();
+                    const uint8_t* rowp = stages + (size_t)stage * kStage + r * kSlice;
+                    uint32_t lo[16];
 #pragma unroll
-                    for (int i = 0; i < kATile / 16 / 128; ++i) {
-                        const float4 x = src[i * 128 + xt];
-                        float4 l;
-                        l.x = x.x - __uint_as_float(__float_as_uint(x.x) & 0xffffe000u);
-                        l.y = x.y - __uint_as_float(__float_as_uint(x.y) & 0xffffe000u);
-                        l.z = x.z - __uint_as_float(__float_as_uint(x.z) & 0xffffe000u);
-                        l.w = x.w - __uint_as_float(__float_as_uint(x.w) & 0xffffe000u);
-                        dst[i * 128 + xt] = l;
+                    for (int c = 0; c < 4; ++c) {
+                        const int chunk = (half * 4 + c) ^ (r & 7);  // 128-byte swizzle: 16-byte chunk index XOR row % 8
+                        const float4 x = *reinterpret_cast<const float4*>(rowp + chunk * 16);
+                        lo[4 * c + 0] = __float_as_uint(x.x - __uint_as_float(__float_as_uint(x.x) & 0xffffe000u));
+                        lo[4 * c + 1] = __float_as_uint(x.y - __uint_as_float(__float_as_uint(x.y) & 0xffffe000u));
+                        lo[4 * c + 2] = __float_as_uint(x.z - __uint_as_float(__float_as_uint(x.z) & 0xffffe000u));
+                        lo[4 * c + 3] = __float_as_uint(x.w - __uint_as_float(__float_as_uint(x.w) & 0xffffe000u));
                     }
-                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    tmem_st16(tmem_base + kLoCol0 + (uint32_t)lo_slot * 32u + (uint32_t)half * 16u + ((uint32_t)(quarter * 32) << 16), lo);
+                    tmem_st_wait();
+                    tcgen05_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(smem_u32(xf_bar + stage));
                     if (++lo_slot == kLoSlots) {
@@ -280,8 +289,8 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
 }
 
 size_t scan_tc_smem_bytes(bool fp32_rows, int stages, int kpad) {
-    return 1024 + (size_t)stages * kStage + (fp32_rows ? (size_t)kLoSlots * kATile : 0) +
-           (size_t)kNQ * kEpiWarps * kpad * 8 + (size_t)kNQ * kEpiWarps * 12 + (3 * kMaxStages + kLoSlots + 4) * 8 + 16;
+    (void)fp32_rows;
+    return 1024 + (size_t)stages * kStage + (size_t)kNQ * kEpiWarps * kpad * 8 + (size_t)kNQ * kEpiWarps * 12 + (3 * kMaxStages + kLoSlots + 4) * 8 + 16;
 }
 
 template <int KIND>
@@ -300,7 +309,7 @@ int launch_scan_tc(const CUtensorMap& tmRows, const CUtensorMap& tmQ, const Scan
         }
     }
     void* tok = prof_begin(stream);
-    kern<<<grid, KIND == 1 ? 320 : 192, smem, stream>>>(tmRows, tmQ, p);
+    kern<<<grid, KIND == 1 ? kThreadsFp32 : kThreadsBf16, smem, stream>>>(tmRows, tmQ, p);
     prof_end(tok, 0, stream);
     B2_AFTER_LAUNCH();
     return B2_OK;
