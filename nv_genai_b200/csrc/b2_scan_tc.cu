@@ -17,7 +17,8 @@
 //               straight into TENSOR MEMORY (tcgen05.st, 4-slot ring of 32 columns); the second MMA
 //               takes its A operand from TMEM, so the remainder never costs shared-memory bandwidth
 //               (with A_lo in shared memory the kernel was smem-bound: 8.4 ms vs 5.8 ms of HBM time).
-//   score(row, j) = D1[row, j] + (D1[row, 16 + j] + D2[row, j]), summed in fp32 registers.
+//   score(row, j) = sum of D1[row, j] + (sum of D1[row, 16 + j] + D2[row, j]) over four accumulator chains
+//   (one per 32-byte K step of a slice), added in fp32 registers.
 // MMA time per slice is 64-96 cycles against ~650 cycles of HBM time per 16 KB slice and SM, so the
 // kernel is HBM-bound like the FFMA scan at batch 1; the tensor pipe is ~15 % busy by design.
 // Selection is the FFMA scan's: one thread = one row, per-(warp, query) top-k lists in shared
@@ -85,8 +86,14 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
     constexpr uint32_t IDESC_BASE = (1u << 4) | (FMT << 7) | (FMT << 10) | ((uint32_t)(kTileRows >> 4) << 24);
     constexpr uint32_t IDESC_N32 = IDESC_BASE | ((32u >> 3) << 17);
     constexpr uint32_t IDESC_N16 = IDESC_BASE | ((16u >> 3) << 17);
-    constexpr uint32_t kTmemCols = 256;  // 2 buffers x 64 columns (D1: 32, D2: 16) + 4 x 32 columns of A_lo slices
-    constexpr uint32_t kLoCol0 = 128;
+    // TMEM: 2 tile buffers x 4 accumulator chains x 48 columns (D1: 32, D2: 16), then 4 x 32 columns of A_lo
+    // slices.  The four 32-byte K steps of a slice accumulate into four INDEPENDENT chains that the epilogue
+    // adds up: back-to-back tcgen05.mma on one small accumulator serialise on the MMA latency (measured: the
+    // MMA side, not HBM, paced the kernel with a single chain), and shorter chains also halve the truncation bias.
+    constexpr uint32_t kChains = kSlice / 32;
+    constexpr uint32_t kBufCols = kChains * 48u;  // 192
+    constexpr uint32_t kTmemCols = 512;
+    constexpr uint32_t kLoCol0 = 2 * kBufCols;    // 384
 
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
@@ -139,60 +146,62 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 4) {
-        // ================= TMA producer
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-                for (int ks = 0; ks < p.kslices; ++ks) {
-                    mbar_wait(smem_u32(empty_bar + stage), phase ^ 1u);
+        // ================= TMA producer (whole warp loops, one elected lane issues)
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+            for (int ks = 0; ks < p.kslices; ++ks) {
+                mbar_wait(smem_u32(empty_bar + stage), phase ^ 1u);
+                if (elect_one()) {
                     const uint32_t fb = smem_u32(full_bar + stage);
                     mbar_expect_tx(fb, (uint32_t)kStage);
                     const uint32_t sb = smem_u32(stages + (size_t)stage * kStage);
                     tma_load_2d(sb, &tmRows, ks * KSLICE, tile * kTileRows, fb);
                     tma_load_2d(sb + kATile, &tmQ, ks * KSLICE, 0, fb);
-                    if (++stage == S) {
-                        stage = 0;
-                        phase ^= 1u;
-                    }
+                }
+                __syncwarp();
+                if (++stage == S) {
+                    stage = 0;
+                    phase ^= 1u;
                 }
             }
         }
     } else if (warp == 5) {
-        // ================= MMA issuer
-        if (lane == 0) {
-            int stage = 0, lo_slot = 0;
-            uint32_t phase = 0, tc = 0;
-            for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++tc) {
-                const uint32_t buf = tc & 1u, par = (tc >> 1) & 1u;
-                mbar_wait(smem_u32(tempty_bar + buf), par ^ 1u);
+        // ================= MMA issuer (whole warp loops, one elected lane issues)
+        int stage = 0, lo_slot = 0;
+        uint32_t phase = 0, tc = 0;
+        for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++tc) {
+            const uint32_t buf = tc & 1u, par = (tc >> 1) & 1u;
+            mbar_wait(smem_u32(tempty_bar + buf), par ^ 1u);
+            tcgen05_fence_after();
+            const uint32_t dbase = tmem_base + buf * kBufCols;
+            for (int ks = 0; ks < p.kslices; ++ks) {
+                mbar_wait(smem_u32((KIND == 1 ? xf_bar : full_bar) + stage), phase);
                 tcgen05_fence_after();
-                const uint32_t d1 = tmem_base + buf * 64u, d2 = d1 + 32u;
-                for (int ks = 0; ks < p.kslices; ++ks) {
-                    mbar_wait(smem_u32((KIND == 1 ? xf_bar : full_bar) + stage), phase);
-                    tcgen05_fence_after();
+                if (elect_one()) {
                     const uint32_t a = smem_u32(stages + (size_t)stage * kStage);
-                    const uint32_t b = a + kATile;
+                    const uint64_t ad = smem_desc<kSlice>(a);
+                    const uint64_t bd = smem_desc<kSlice>(a + kATile);
                     const uint32_t alo = tmem_base + kLoCol0 + (uint32_t)lo_slot * 32u;  // TMEM columns of this slice's A_lo
+                    const uint32_t acc = ks ? 1u : 0u;
 #pragma unroll
                     for (int j = 0; j < kSlice / 32; ++j) {
-                        const uint32_t acc = (ks | j) ? 1u : 0u;
-                        const uint64_t bd = smem_desc<kSlice>(b + j * 32);
-                        umma<KIND>(d1, smem_desc<kSlice>(a + j * 32), bd, IDESC_N32, acc);
-                        if (KIND == 1) umma_tf32_ts(d2, alo + j * 8, bd, IDESC_N16, acc);
+                        const uint32_t d1 = dbase + j * 48u, d2 = d1 + 32u;
+                        umma<KIND>(d1, ad + (uint64_t)(j * 2), bd + (uint64_t)(j * 2), IDESC_N32, acc);  // +32 B in the address field
+                        if (KIND == 1) umma_tf32_ts(d2, alo + j * 8, bd + (uint64_t)(j * 2), IDESC_N16, acc);
                     }
                     tcgen05_commit(smem_u32(empty_bar + stage));
-                    if (KIND == 1) {
-                        tcgen05_commit(smem_u32(lo_empty_bar + lo_slot));
-                        if (++lo_slot == kLoSlots) lo_slot = 0;
-                    }
-                    if (++stage == S) {
-                        stage = 0;
-                        phase ^= 1u;
-                    }
+                    if (KIND == 1) tcgen05_commit(smem_u32(lo_empty_bar + lo_slot));
                 }
-                tcgen05_commit(smem_u32(tfull_bar + buf));
+                __syncwarp();
+                if (KIND == 1 && ++lo_slot == kLoSlots) lo_slot = 0;
+                if (++stage == S) {
+                    stage = 0;
+                    phase ^= 1u;
+                }
             }
+            if (elect_one()) tcgen05_commit(smem_u32(tfull_bar + buf));
+            __syncwarp();
         }
     } else if (warp >= 6) {
         // ================= fp32 rows: A_lo = x - trunc_tf32(x), thread = row, written to TMEM
@@ -241,12 +250,24 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
             const uint32_t buf = tc & 1u, par = (tc >> 1) & 1u;
             mbar_wait(smem_u32(tfull_bar + buf), par);
             tcgen05_fence_after();
-            const uint32_t taddr = tmem_base + buf * 64u + ((uint32_t)(warp * 32) << 16);
-            uint32_t d1[32];
-            uint32_t d2[16];
-            tmem_ld32(taddr, d1);
-            if (KIND == 1) tmem_ld16(taddr + 32u, d2);
-            tmem_ld_wait();
+            const uint32_t taddr = tmem_base + buf * kBufCols + ((uint32_t)(warp * 32) << 16);
+            float big[kNQ], small[kNQ];  // main products / correction products, summed over the four chains
+#pragma unroll
+            for (int j = 0; j < kNQ; ++j) big[j] = small[j] = 0.f;
+#pragma unroll
+            for (int c = 0; c < (int)kChains; ++c) {
+                uint32_t d1[32];
+                uint32_t d2[16];
+                tmem_ld32(taddr + c * 48u, d1);
+                if (KIND == 1) tmem_ld16(taddr + c * 48u + 32u, d2);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < kNQ; ++j) {
+                    big[j] += __uint_as_float(d1[j]);
+                    small[j] += __uint_as_float(d1[kNQ + j]);
+                    if (KIND == 1) small[j] += __uint_as_float(d2[j]);
+                }
+            }
             tcgen05_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(smem_u32(tempty_bar + buf));  // registers hold the tile: TMEM is free again
@@ -254,9 +275,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
 #pragma unroll
             for (int j = 0; j < kNQ; ++j) {
                 if (j < p.nq) {  // warp-uniform
-                    float small = __uint_as_float(d1[kNQ + j]);
-                    if (KIND == 1) small += __uint_as_float(d2[j]);
-                    const float key = (__uint_as_float(d1[j]) + small) + 0.0f;
+                    const float key = (big[j] + small[j]) + 0.0f;
                     const uint64_t cand = pack_cand(key, row);
                     const int li = j * kEpiWarps + warp;
                     const bool pass = row < p.n && key > -FLT_MAX && cand > worst_s[li];
@@ -359,7 +378,9 @@ int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int d
     p.partial = reinterpret_cast<uint64_t*>(blk + q_bytes);
 
     CUtensorMap tmRows, tmQ;
-    int rc = make_map(&tmRows, bf16, kSlice, rows, (uint64_t)(pitch_bytes / elem), (uint64_t)n, pitch_bytes, kTileRows);
+    int promo = 256;  // consecutive K slices of a row are fetched back to back: let L2 bring in 256 B per miss
+    if (const char* e = getenv("B2_SCAN_TC_L2PROMO")) promo = atoi(e);
+    int rc = make_map(&tmRows, bf16, kSlice, rows, (uint64_t)(pitch_bytes / elem), (uint64_t)n, pitch_bytes, kTileRows, promo);
     if (rc == B2_OK) rc = make_map(&tmQ, bf16, kSlice, Q, (uint64_t)kp, (uint64_t)2 * kNQ, kbytes, 2 * kNQ);
     if (rc == B2_OK) rc = prep_queries(q_dev, nq, d, kNQ, kp, 2, bf16, Q, nullptr, nullptr, stream);
     if (rc == B2_OK)

@@ -49,6 +49,15 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
         ::"r"(dst), "l"(map), "r"(bar), "r"(x), "r"(y)
         : "memory");
 }
+// One lane of a converged warp.  The producer / MMA warps run their loops with ALL lanes (so that loop state is
+// provably warp-uniform and lives in uniform registers) and elect one lane only around the issuing instructions;
+// guarding the whole loop with `lane == 0` instead makes the compiler wrap every TMA / MMA instruction in a
+// waterfall loop, which made the single issuing thread the bottleneck of the small-batch scan.
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_commit(uint32_t bar) {
@@ -143,7 +152,7 @@ inline EncodeTiledFn encode_tiled() {
 }
 
 inline int make_map(CUtensorMap* m, bool bf16, int swb, const void* base, uint64_t inner_elems, uint64_t rows,
-             uint64_t pitch_bytes, uint32_t box_rows) {
+             uint64_t pitch_bytes, uint32_t box_rows, int l2_promotion_bytes = 128) {
     EncodeTiledFn fn = encode_tiled();
     if (fn == nullptr) {
         set_error("cuTensorMapEncodeTiled is not available from this driver");
@@ -156,7 +165,7 @@ inline int make_map(CUtensorMap* m, bool bf16, int swb, const void* base, uint64
     const CUresult r = fn(m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
                           const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                           swb == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
-                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          l2_promotion_bytes == 256 ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         set_error("cuTensorMapEncodeTiled failed (%d) for %llu x %llu, pitch %llu", (int)r,
