@@ -377,7 +377,7 @@ def run_b200(a):
             roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": (achieved / peak) if achieved else None,
                     "traffic": ncu_traffic() if (batch == 1 and dtype == "float32" and world == 1) else None,
-                    "kernel": "scan_tc_kernel" if 3 <= batch <= 16 else "scan_topk_kernel",
+                    "kernel": "scan_tc_kernel" if (3 if dtype == "bfloat16" else 5) <= batch <= 16 else "scan_topk_kernel",
                     "algorithmic_bytes_per_launch": shard_bytes,
                     "avg_launch_ms": k_avg_ms, "launches_timed": k_n, "peak_source": peak_src,
                     "scan_share_of_step": (k_avg_ms * k_n / ms) if k_n else None, "scan_passes_per_step": per_step}

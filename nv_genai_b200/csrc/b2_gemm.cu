@@ -232,17 +232,17 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 4) {
-        // ================= TMA producer
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
-                const int qt = item % p.n_qt, seg = item / p.n_qt;
-                const int t0 = seg * p.tiles_per_seg;
-                const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
-                for (int t = t0; t < t1; ++t) {
-                    for (int ks = 0; ks < p.kstages; ++ks) {
-                        mbar_wait(smem_u32(empty_bar + stage), phase ^ 1u);
+        // ================= TMA producer (whole warp loops, one elected lane issues; see tc::elect_one)
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+            const int qt = item % p.n_qt, seg = item / p.n_qt;
+            const int t0 = seg * p.tiles_per_seg;
+            const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
+            for (int t = t0; t < t1; ++t) {
+                for (int ks = 0; ks < p.kstages; ++ks) {
+                    mbar_wait(smem_u32(empty_bar + stage), phase ^ 1u);
+                    if (elect_one()) {
                         const uint32_t fb = smem_u32(full_bar + stage);
                         mbar_expect_tx(fb, STAGE_TX);
                         const uint32_t sb = smem_u32(stages + (size_t)stage * STAGE_BYTES);
@@ -250,62 +250,61 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         tma_load_2d(sb, &tmA, x, qt * kTileM, fb);
                         if (NA == 2) tma_load_2d(sb + kAPartBytes, &tmA, x, p.nq_pad + qt * kTileM, fb);
                         tma_load_2d(sb + B_OFF, &tmB, x, t * kTileN, fb);
-                        if (++stage == S) {
-                            stage = 0;
-                            phase ^= 1u;
-                        }
+                    }
+                    __syncwarp();
+                    if (++stage == S) {
+                        stage = 0;
+                        phase ^= 1u;
                     }
                 }
             }
         }
     } else if (warp == 5) {
-        // ================= MMA issuer (one thread)
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            uint32_t tc = 0;
-            for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
-                const int seg = item / p.n_qt;
-                const int t0 = seg * p.tiles_per_seg;
-                const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
-                for (int t = t0; t < t1; ++t, ++tc) {
-                    const uint32_t buf = tc % NBUF, par = (tc / NBUF) & 1u;
-                    mbar_wait(smem_u32(tempty_bar + buf), par ^ 1u);
+        // ================= MMA issuer (whole warp loops, one elected lane issues)
+        int stage = 0;
+        uint32_t phase = 0;
+        uint32_t tc = 0;
+        for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+            const int seg = item / p.n_qt;
+            const int t0 = seg * p.tiles_per_seg;
+            const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
+            for (int t = t0; t < t1; ++t, ++tc) {
+                const uint32_t buf = tc % NBUF, par = (tc / NBUF) & 1u;
+                mbar_wait(smem_u32(tempty_bar + buf), par ^ 1u);
+                tcgen05_fence_after();
+                const uint32_t d_tmem = tmem_base + buf * kTileN;
+                const uint32_t c_tmem = tmem_base + kTileN;  // fp32 rows: correction accumulator
+                for (int ks = 0; ks < p.kstages; ++ks) {
+                    mbar_wait(smem_u32((KIND == 1 ? xf_bar : full_bar) + stage), phase);
                     tcgen05_fence_after();
-                    const uint32_t d_tmem = tmem_base + buf * kTileN;
-                    const uint32_t c_tmem = tmem_base + kTileN;  // fp32 rows: correction accumulator
-                    for (int ks = 0; ks < p.kstages; ++ks) {
-                        mbar_wait(smem_u32((KIND == 1 ? xf_bar : full_bar) + stage), phase);
-                        tcgen05_fence_after();
+                    if (elect_one()) {
                         const uint32_t sb = smem_u32(stages + (size_t)stage * STAGE_BYTES);
+                        const uint64_t a_hi0 = smem_desc<SWB>(sb);
+                        const uint64_t a_lo0 = smem_desc<SWB>(sb + kAPartBytes);
+                        const uint64_t b_hi0 = smem_desc<SWB>(sb + B_OFF);
+                        const uint64_t b_lo0 = smem_desc<SWB>(sb + BLO_OFF);
 #pragma unroll
                         for (int j = 0; j < kSwizzleBytes / 32; ++j) {
                             const uint32_t acc = (ks | j) ? 1u : 0u;
-                            const uint64_t a_hi = smem_desc<SWB>(sb + j * 32);
-                            const uint64_t b_hi = smem_desc<SWB>(sb + B_OFF + j * 32);
-                            umma<KIND>(d_tmem, a_hi, b_hi, IDESC, acc);
+                            const uint64_t dj = (uint64_t)(j * 2);  // +32 bytes in the descriptor's address field
+                            umma<KIND>(d_tmem, a_hi0 + dj, b_hi0 + dj, IDESC, acc);
                             if (KIND == 0) {
-                                if (NA == 2) {
-                                    const uint64_t a_lo = smem_desc<SWB>(sb + kAPartBytes + j * 32);
-                                    umma<KIND>(d_tmem, a_lo, b_hi, IDESC, 1u);
-                                }
+                                if (NA == 2) umma<KIND>(d_tmem, a_lo0 + dj, b_hi0 + dj, IDESC, 1u);
                             } else {
-                                const uint64_t b_lo = smem_desc<SWB>(sb + BLO_OFF + j * 32);
-                                umma<KIND>(c_tmem, a_hi, b_lo, IDESC, acc);
-                                if (NA == 2) {
-                                    const uint64_t a_lo = smem_desc<SWB>(sb + kAPartBytes + j * 32);
-                                    umma<KIND>(c_tmem, a_lo, b_hi, IDESC, 1u);
-                                }
+                                umma<KIND>(c_tmem, a_hi0 + dj, b_lo0 + dj, IDESC, acc);
+                                if (NA == 2) umma<KIND>(c_tmem, a_lo0 + dj, b_hi0 + dj, IDESC, 1u);
                             }
                         }
                         tcgen05_commit(smem_u32(empty_bar + stage));
-                        if (++stage == S) {
-                            stage = 0;
-                            phase ^= 1u;
-                        }
                     }
-                    tcgen05_commit(smem_u32(tfull_bar + buf));
+                    __syncwarp();
+                    if (++stage == S) {
+                        stage = 0;
+                        phase ^= 1u;
+                    }
                 }
+                if (elect_one()) tcgen05_commit(smem_u32(tfull_bar + buf));
+                __syncwarp();
             }
         }
     } else if (warp >= 6) {

@@ -1,4 +1,4 @@
-// Small-batch exact scan on the tensor cores: 3..16 queries, inner product, one pass over the rows.
+// Small-batch exact scan on the tensor cores: 3..16 queries (fp32 rows: 5..16), inner product, one pass over the rows.
 //
 // Replaces faiss exhaustive_inner_product_seq + HeapResultHandler (faiss/utils/distances.cpp, the
 // nq < 20 path of IndexFlat::search), the same routine b2_scan.cu replaces, for the query counts
@@ -339,7 +339,9 @@ int launch_scan_tc(const CUtensorMap& tmRows, const CUtensorMap& tmQ, const Scan
 bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t nq) {
     if (getenv("B2_NO_TENSOR") != nullptr || getenv("B2_NO_SCAN_TC") != nullptr) return false;
     const int elem = dtype == B2_DTYPE_BF16 ? 2 : 4;
-    int min_nq = 3;
+    // measured at 10M x 1024 on B200: fp32 rows, FFMA scan 5.9-6.0 ms up to 4 queries and 7.2 ms at 5..8, this kernel
+    // 6.7-7.3 ms for 3..16; bf16 rows, this kernel 3.1-3.6 ms for 3..16 (the FFMA scan needs 3.3 ms for ONE query)
+    int min_nq = (dtype == B2_DTYPE_BF16) ? 3 : 5;
     if (const char* e = getenv("B2_SCAN_TC_MIN_NQ")) min_nq = atoi(e);
     return metric == B2_METRIC_IP && nq >= min_nq && nq <= kNQ && k <= 128 && n >= 4096 && n < ((int64_t)1 << 31) &&
            (int64_t)d * elem >= kSlice;

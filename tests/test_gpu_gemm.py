@@ -177,7 +177,7 @@ def test_large_batch_1024_queries_k100_property():
 # ---------------------------------------------------------------------------------------------------------------
 # tensor-core scan (b2_scan_tc.cu): 3..16 queries, inner product, corpus as the M operand
 @pytest.mark.parametrize("dtype", ["float32", "bfloat16"])
-@pytest.mark.parametrize("nq,k", [(3, 10), (9, 1), (16, 10), (16, 100), (5, 128)])
+@pytest.mark.parametrize("nq,k", [(6, 10), (9, 1), (16, 10), (16, 100), (5, 128)])
 def test_small_batch_tensor_scan_matches_sequential_oracle(dtype, nq, k):
     n, d = 70_001, 1024  # ragged last tile (128-row tiles)
     x, q = _data(n, d, nq, True, seed=100 + nq)
