@@ -31,6 +31,12 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 METRIC = "queries/sec, exact top-k (IndexFlatIP) over 10M x 1024 fp32"
+
+
+def metric_name(a):
+    if a.rows == 10_000_000 and a.dim == 1024 and a.dtype == "float32":
+        return METRIC
+    return f"queries/sec, exact top-k (IndexFlatIP) over {a.rows} x {a.dim} {a.dtype}"
 UNIT = "queries/s"
 
 
@@ -202,7 +208,7 @@ def run_reference(a):
     sample = (f"each step scans {rows} of {a.rows} rows (x{scale:g} linear scaling), batch {a.batch}, k={a.k}; "
               f"C restatement of faiss IndexFlat (oracle/flat_oracle.c), OpenMP over queries only; "
               f"host has {os.cpu_count()} logical cores")
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+    line = {"impl": "reference", "metric": metric_name(a), "value": value, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": t_step * 1e3, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_name(a), "rows": a.rows, "dim": a.dim, "batch": a.batch, "k": a.k},
@@ -422,7 +428,7 @@ def run_b200(a):
 
     if rank == 0:
         line = {
-            "metric": METRIC, "value": main["value"], "unit": UNIT, "n_gpus": world, "steps": a.steps,
+            "metric": metric_name(a), "value": main["value"], "unit": UNIT, "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32" if a.dtype == "float32" else "bf16 rows, f32 accumulate",
             "data": "synthetic",

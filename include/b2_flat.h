@@ -159,6 +159,16 @@ B2_API int b2_index_mmr(b2_index* h, int64_t nq, const float* q, int q_where, in
 B2_API int b2_merge_shard_lists(int metric, int64_t nq, int k, int nparts, const float* D_parts, const int64_t* I_parts,
                          float* D, int64_t* I, int device, void* stream);
 
+/* The same exchange step for the layout the all-gather produces directly: part g's lists are at
+ * D_parts + g * part_stride_bytes and I_parts + g * part_stride_bytes (each rank sends one packed
+ * block [I: nq x k int64 | D: nq x k fp32], so D_parts = I_parts + nq * k * 8 bytes), ids are LOCAL to
+ * their shard and id_bases[g] (host array, nparts entries) is the global id of shard g's first row.
+ * At most B2_MAX_SHARDS parts. */
+#define B2_MAX_SHARDS 64
+B2_API int b2_merge_shard_lists_packed(int metric, int64_t nq, int k, int nparts, const float* D_parts,
+                                const int64_t* I_parts, int64_t part_stride_bytes, const int64_t* id_bases, float* D,
+                                int64_t* I, int device, void* stream);
+
 /* faiss.normalize_L2(x) on a caller-owned device array (n x d fp32, in place). */
 B2_API int b2_normalize_l2(float* x, int64_t n, int d, int device, void* stream);
 

@@ -778,6 +778,24 @@ int b2_merge_shard_lists(int metric, int64_t nq, int k, int nparts, const float*
     return merge_shards(metric, (int)nq, k, nparts, D_parts, I_parts, D, I, static_cast<cudaStream_t>(stream_));
 }
 
+int b2_merge_shard_lists_packed(int metric, int64_t nq, int k, int nparts, const float* D_parts, const int64_t* I_parts,
+                                int64_t part_stride_bytes, const int64_t* id_bases, float* D, int64_t* I, int device,
+                                void* stream_) {
+    if (nq < 0 || k <= 0 || nparts <= 0 || nparts > B2_MAX_SHARDS || part_stride_bytes <= 0 ||
+        (nq > 0 && (!D_parts || !I_parts || !D || !I || !id_bases))) {
+        set_error("b2_merge_shard_lists_packed: bad arguments");
+        return B2_ERR_INVALID;
+    }
+    if (nq == 0) return B2_OK;
+    DeviceGuard g(device);
+    if (!g.ok) {
+        set_error("cannot select device %d", device);
+        return B2_ERR_CUDA;
+    }
+    return merge_shards(metric, (int)nq, k, nparts, D_parts, I_parts, D, I, static_cast<cudaStream_t>(stream_),
+                        (size_t)part_stride_bytes, (size_t)part_stride_bytes, id_bases);
+}
+
 int b2_normalize_l2(float* x, int64_t n, int d, int device, void* stream_) {
     if (n < 0 || d <= 0 || (n > 0 && x == nullptr)) {
         set_error("b2_normalize_l2: bad arguments");

@@ -45,8 +45,11 @@ bool gemm_path_supported(int64_t n, int d, int dtype, int k, int64_t nq);
 int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* norms,
                 const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream);
 // (D_parts, I_parts): [nparts][nq][k] -> [nq][k]
+// part g's lists start d_stride_bytes / i_stride_bytes after part g-1's (0 = natural [nparts][nq][k] arrays);
+// id_bases (host, nparts entries, optional): ids in the lists are local to their part, global = base + local.
 int merge_shards(int metric, int nq, int k, int nparts, const float* D_parts, const int64_t* I_parts, float* D,
-                 int64_t* I, cudaStream_t stream);
+                 int64_t* I, cudaStream_t stream, size_t d_stride_bytes = 0, size_t i_stride_bytes = 0,
+                 const int64_t* id_bases = nullptr);
 
 // b2_ingest.cu -------------------------------------------------------------
 // src: n x d fp32 dense (device) -> dst rows at `pitch_bytes`, fp32 or bf16, padding zeroed;

@@ -69,10 +69,17 @@ int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metri
 // ---------------------------------------------------------------- shard lists
 // Candidate position = part * k + rank: parts are in global id order and each part's list
 // is already ordered lowest-id-first among equal keys, so "lower position first" is exactly
-// "lower global id first".
+// "lower global id first".  Part g's lists start at D_parts + g * d_stride and I_parts +
+// g * i_stride (bytes); ids are local to the part when `bases` is given (global id =
+// bases.v[g] + local id), global otherwise.
+struct ShardBases {
+    int64_t v[B2_MAX_SHARDS];
+};
+
 __global__ void __launch_bounds__(kMergeThreads) merge_shards_kernel(int metric, int k, int nparts, int nq,
-                                                                    const float* __restrict__ Dp,
-                                                                    const int64_t* __restrict__ Ip, int sort_n,
+                                                                    const char* __restrict__ Dp,
+                                                                    const char* __restrict__ Ip, size_t d_stride, size_t i_stride,
+                                                                    const ShardBases bases, int use_bases, int sort_n,
                                                                     float* D, int64_t* I) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw);
@@ -82,10 +89,10 @@ __global__ void __launch_bounds__(kMergeThreads) merge_shards_kernel(int metric,
         uint64_t c = B2_SENTINEL;
         if (i < total) {
             const int part = i / k, r = i - part * k;
-            const size_t src = ((size_t)part * nq + q) * k + r;
-            const int64_t id = Ip[src];
+            const size_t off = (size_t)q * k + r;
+            const int64_t id = reinterpret_cast<const int64_t*>(Ip + (size_t)part * i_stride)[off];
             if (id >= 0) {
-                const float d = Dp[src];
+                const float d = reinterpret_cast<const float*>(Dp + (size_t)part * d_stride)[off];
                 c = pack_cand(metric == B2_METRIC_IP ? d : -d, (uint32_t)i);
             }
         }
@@ -102,24 +109,36 @@ __global__ void __launch_bounds__(kMergeThreads) merge_shards_kernel(int metric,
             *Dq = (metric == B2_METRIC_IP) ? -FLT_MAX : FLT_MAX;
         } else {
             const int part = pos / k, r = pos - part * k;
-            const size_t src = ((size_t)part * nq + q) * k + r;
-            *Iq = Ip[src];
-            *Dq = Dp[src];
+            const size_t off = (size_t)q * k + r;
+            const int64_t id = reinterpret_cast<const int64_t*>(Ip + (size_t)part * i_stride)[off];
+            *Iq = use_bases ? id + bases.v[part] : id;
+            *Dq = reinterpret_cast<const float*>(Dp + (size_t)part * d_stride)[off];
         }
     }
 }
 
 int merge_shards(int metric, int nq, int k, int nparts, const float* D_parts, const int64_t* I_parts, float* D,
-                 int64_t* I, cudaStream_t stream) {
+                 int64_t* I, cudaStream_t stream, size_t d_stride_bytes, size_t i_stride_bytes,
+                 const int64_t* id_bases) {
     const long long total = (long long)nparts * k;
     const int sort_n = next_pow2((int)(total < 32 ? 32 : total));
     const size_t smem = (size_t)sort_n * sizeof(uint64_t);
-    if (smem > 200 * 1024) {
-        set_error("merge_shards: nparts*k = %lld too large", total);
+    if (smem > 200 * 1024 || nparts > B2_MAX_SHARDS) {
+        set_error("merge_shards: nparts=%d x k=%d too large", nparts, k);
         return B2_ERR_UNSUPPORTED;
     }
-    B2_CUDA_TRY(cudaFuncSetAttribute(merge_shards_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    merge_shards_kernel<<<nq, kMergeThreads, smem, stream>>>(metric, k, nparts, nq, D_parts, I_parts, sort_n, D, I);
+    if (d_stride_bytes == 0) d_stride_bytes = (size_t)nq * k * sizeof(float);
+    if (i_stride_bytes == 0) i_stride_bytes = (size_t)nq * k * sizeof(int64_t);
+    ShardBases bases;
+    for (int g = 0; g < B2_MAX_SHARDS; ++g) bases.v[g] = (id_bases != nullptr && g < nparts) ? id_bases[g] : 0;
+    static size_t attr = 0;
+    if (smem > attr) {
+        B2_CUDA_TRY(cudaFuncSetAttribute(merge_shards_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr = smem;
+    }
+    merge_shards_kernel<<<nq, kMergeThreads, smem, stream>>>(metric, k, nparts, nq, reinterpret_cast<const char*>(D_parts),
+                                                             reinterpret_cast<const char*>(I_parts), d_stride_bytes,
+                                                             i_stride_bytes, bases, id_bases != nullptr, sort_n, D, I);
     B2_AFTER_LAUNCH();
     return B2_OK;
 }

@@ -163,6 +163,15 @@ class IndexFlat:
                                       _stream_for(self.device)))
         return D, I
 
+    def search_into(self, x, k: int, D, I) -> None:
+        """`search` into caller-provided CUDA tensors D [n, k] float32 and I [n, k] int64 (contiguous), asynchronous on
+        the current stream: the batched device path without any allocation on the Python side."""
+        b = _Buf(x, self.d, self.device, "search")
+        assert b.is_tensor and D.is_cuda and I.is_cuda and D.is_contiguous() and I.is_contiguous()
+        assert tuple(D.shape) == (b.n, int(k)) and tuple(I.shape) == (b.n, int(k))
+        N.check(N.lib.b2_index_search(self._h, b.n, b.ptr, N.DEVICE, int(k), D.data_ptr(), I.data_ptr(), N.DEVICE,
+                                      _stream_for(self.device)))
+
     # ---- index.reconstruct*
     def reconstruct_batch(self, ids):
         if _is_tensor(ids) and ids.is_cuda:
@@ -281,6 +290,24 @@ def synth_fill(out, row0: int, seed: int) -> None:
     assert _is_tensor(out) and out.is_cuda and out.is_contiguous() and out.dim() == 2
     N.check(N.lib.b2_synth_fill(out.data_ptr(), int(row0), out.shape[0], out.shape[1], int(seed), out.device.index,
                                 _stream_for(out.device.index)))
+
+
+def merge_shard_lists_packed(metric: int, gathered, nq: int, k: int, bases):
+    """`gathered`: uint8 [G, nq*k*12] as the all-gather leaves it, each part = [I local ids int64 | D fp32];
+    `bases`: G global ids of the shards' first rows.  Returns the global (D, I) [nq, k]."""
+    t = _torch()
+    assert gathered.is_cuda and gathered.is_contiguous() and gathered.dim() == 2
+    G = gathered.shape[0]
+    stride = gathered.shape[1]
+    assert stride == nq * k * 12 and len(bases) >= G
+    D = t.empty((nq, k), dtype=t.float32, device=gathered.device)
+    I = t.empty((nq, k), dtype=t.int64, device=gathered.device)
+    arr = (ctypes.c_int64 * G)(*[int(b) for b in bases[:G]])
+    dev = gathered.device.index
+    base_ptr = gathered.data_ptr()
+    N.check(N.lib.b2_merge_shard_lists_packed(int(metric), nq, k, G, base_ptr + nq * k * 8, base_ptr, stride, arr,
+                                              D.data_ptr(), I.data_ptr(), dev, _stream_for(dev)))
+    return D, I
 
 
 def merge_shard_lists(metric: int, D_parts, I_parts):

@@ -44,11 +44,13 @@ class ShardedFlatIndex:
 
             local_index = IndexFlat(d, metric, dtype, device)
         self.local = local_index
+        self._fast = merge_fn is None and hasattr(local_index, "search_into")  # CUDA path: packed exchange
         if merge_fn is None:
             from .index import merge_shard_lists
 
             merge_fn = merge_shard_lists
         self._merge = merge_fn
+        self._ws = {}  # (nq, k) -> (packed send block, gathered blocks)
         self.bases = [0] * (self.world + 1)  # bases[g] = global id of shard g's first row
 
     # ------------------------------------------------------------------ build
@@ -97,6 +99,26 @@ class ShardedFlatIndex:
         t, dist = self._torch, self._dist
         if not replicated:
             dist.broadcast(q, src=src, group=self.group)
+        if self._fast and isinstance(q, t.Tensor) and q.is_cuda:
+            # CUDA path: the local search writes (I, D) straight into the block that is all-gathered, ids stay
+            # local and the merge kernel adds the shard bases: 4 launches + 1 collective per search, no torch glue
+            from .index import merge_shard_lists_packed
+
+            nq = q.shape[0] if q.dim() == 2 else 1
+            nres = nq * k
+            ws = self._ws.get((nq, k))
+            if ws is None:
+                ws = (t.empty(nres * 12, dtype=t.uint8, device=q.device),
+                      t.empty((self.world, nres * 12), dtype=t.uint8, device=q.device))
+                if len(self._ws) > 16:
+                    self._ws.clear()
+                self._ws[(nq, k)] = ws
+            packed, gathered = ws
+            I_loc = packed[: nres * 8].view(t.int64).view(nq, k)
+            D_loc = packed[nres * 8:].view(t.float32).view(nq, k)
+            self.local.search_into(q, k, D_loc, I_loc)
+            dist.all_gather_into_tensor(gathered, packed, group=self.group)
+            return merge_shard_lists_packed(self.metric, gathered, nq, k, self.bases)
         D_loc, I_loc = self.local.search(q, k)
         if not isinstance(D_loc, t.Tensor):
             D_loc, I_loc = t.from_numpy(D_loc), t.from_numpy(I_loc)

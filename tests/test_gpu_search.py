@@ -268,3 +268,42 @@ def test_sharded_merge_equals_single_index_bit_for_bit():
     ref.add(x[:5])
     Dr, Ir = ref.search(qd, 4)
     assert torch.equal(I, Ir) and torch.equal(D, Dr)
+
+
+def test_packed_shard_exchange_layout_equals_single_index_bit_for_bit():
+    """The layout ShardedFlatIndex all-gathers on GPUs: each shard writes (I local ids | D) into one packed block
+    with search_into, the merge kernel adds the shard bases.  G ranks emulated on this GPU, including a batch that
+    takes the tensor-core path on every shard."""
+    import torch
+
+    from nv_genai_b200.index import merge_shard_lists_packed
+    from nv_genai_b200.sharded import shard_bounds
+
+    x, q = _data(60_001, 256, 40, True, seed=16)
+    x[45_000] = x[10]
+    q[0] = x[10]
+    whole = _mk(flat.METRIC_IP, 256)
+    whole.add(x)
+    for nq, k in ((1, 10), (9, 20), (40, 100)):
+        qd = torch.from_numpy(q[:nq]).cuda()
+        Dw, Iw = whole.search(qd, k)
+        for G in (2, 8):
+            nres = nq * k
+            gathered = torch.empty((G, nres * 12), dtype=torch.uint8, device="cuda")
+            bases = []
+            for g in range(G):
+                lo, hi = shard_bounds(len(x), G, g)
+                bases.append(lo)
+                sh = _mk(flat.METRIC_IP, 256)
+                sh.add(x[lo:hi])
+                I_loc = gathered[g, : nres * 8].view(torch.int64).view(nq, k)
+                D_loc = gathered[g, nres * 8:].view(torch.float32).view(nq, k)
+                sh.search_into(qd, k, D_loc, I_loc)
+            D, I = merge_shard_lists_packed(flat.METRIC_IP, gathered, nq, k, bases)
+            assert torch.equal(I, Iw), (nq, k, G)
+            if nq < 20:
+                assert torch.equal(D, Dw)  # same kernel scores each row: bit for bit
+            else:
+                # tensor path: the segment boundaries differ between the whole index and the shards, the scores
+                # of a row do not (same MMA sequence per row)
+                assert torch.equal(D, Dw)
