@@ -6,16 +6,21 @@ device-wide synchronisation an allocator call may cause.  For them the library o
 extra entry point that keeps the scan kernel's per-CTA partial lists in a fixed 2 MiB array
 inside the library image instead of taking them from cudaMallocAsync.
 
-This file checks, through the C ABI only, that the entry point returns exactly what
-b2_index_search returns (the same kernels run, so the comparison is bit for bit), on two calls
-in a row — the second call reuses the array with the first call's contents still in it — and
-that it refuses sizes beyond its fixed scratch with a clear error.  It is named test_zz_* so
+This file checks, through the C ABI only, that the entry point returns what b2_index_search
+returns, on two calls in a row — the second call reuses the array with the first call's
+contents still in it — and that it refuses sizes beyond its fixed scratch with a clear error.
+The entry point always runs the FFMA scan kernel; b2_index_search runs the same kernel for L2
+and for very small batches (then the comparison is bit for bit) and the tensor-core scan for
+5..16 inner-product queries (3..16 on bf16 rows), where the two agree within the 1e-5 relative
+score tolerance every parity test here uses (tests/parity.py).  It is named test_zz_* so
 that pytest collects it after every other test file.
 """
 import ctypes
 
 import numpy as np
 import pytest
+
+from parity import assert_parity
 
 pytestmark = pytest.mark.gpu
 
@@ -65,8 +70,11 @@ def test_static_scratch_search_equals_the_allocating_search_twice_in_a_row(metri
         for nq, k, first in ((16, 10, 0), (3, 100, 5)):
             qs = q[first:first + nq].contiguous()
             D0, I0, D1, I1 = _search_pair(N, h, qs, k, None)
-            assert np.array_equal(I0, I1), (nq, k)
-            assert np.array_equal(D0, D1), (nq, k)  # identical kernels: bit for bit, tolerance 0
+            same_kernel = metric_name == "l2" or nq < (5 if dtype_name == "f32" else 3)
+            if same_kernel:
+                assert np.array_equal(I0, I1) and np.array_equal(D0, D1), (nq, k)  # bit for bit
+            else:
+                assert_parity(D1, I1, D0, I0, metric_ip=(metric_name == "ip"))  # 1e-5 relative, ties may swap
             assert (I1 >= 0).all() and (I1 < n).all()
             if metric_name == "ip":
                 assert np.all(np.diff(D1, axis=1) <= 0)
