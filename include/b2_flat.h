@@ -171,6 +171,24 @@ B2_API int b2_merge_shard_lists_packed(int metric, int64_t nq, int k, int nparts
                                 const int64_t* I_parts, int64_t part_stride_bytes, const int64_t* id_bases, float* D,
                                 int64_t* I, int device, void* stream);
 
+/* Row-sharded search, exchange over NVLink peer memory instead of a collective (no counterpart in the
+ * reference).  b2_index_search_push runs the local search and, in the kernel that produces the final lists,
+ * stores them straight into every rank's receive block: peer_blocks[g] = the address, mapped into THIS process,
+ * of rank g's block for this rank's lists (layout [I: nq x k int64 local ids | D: nq x k fp32]); when a query's
+ * k results are stored on all ranks, peer_flags[g][q] = epoch is released system-wide (peer_flags[g] = rank g's
+ * nq flag words for this rank).  Nothing is written locally except through the entry for this rank itself.
+ * b2_merge_shard_lists_wait is the receiving side: per query it waits until flags[g * flag_stride + q] == epoch
+ * for all g, then merges the nparts blocks (blocks + g * part_stride_bytes) like b2_merge_shard_lists_packed.
+ * The caller owns the peer-mapped memory (e.g. torch symmetric memory / cudaIpc), alternates between two sets of
+ * blocks and flags from one search to the next, and increases `epoch` every search; every rank must call both
+ * functions for every search (the wait spins on the GPU until all peers have delivered, traps after ~20 s).
+ * At most 16 peers. */
+B2_API int b2_index_search_push(b2_index* h, int64_t nq, const float* q_dev, int k, int nparts, void* const* peer_blocks,
+                         uint32_t* const* peer_flags, uint32_t epoch, void* stream);
+B2_API int b2_merge_shard_lists_wait(int metric, int64_t nq, int k, int nparts, const void* blocks,
+                              int64_t part_stride_bytes, const uint32_t* flags, int64_t flag_stride, uint32_t epoch,
+                              const int64_t* id_bases, float* D, int64_t* I, int device, void* stream);
+
 /* faiss.normalize_L2(x) on a caller-owned device array (n x d fp32, in place). */
 B2_API int b2_normalize_l2(float* x, int64_t n, int d, int device, void* stream);
 

@@ -23,7 +23,7 @@ MAX_K = 2048
 SYMBOLS = [
     "b2_index_create", "b2_index_destroy", "b2_index_ntotal", "b2_index_d", "b2_index_metric", "b2_index_dtype",
     "b2_index_device", "b2_index_add", "b2_index_search", "b2_index_search_static", "b2_index_reconstruct_batch", "b2_index_remove_ids",
-    "b2_index_merge_from", "b2_index_reset", "b2_index_mmr", "b2_merge_shard_lists", "b2_merge_shard_lists_packed", "b2_normalize_l2",
+    "b2_index_merge_from", "b2_index_reset", "b2_index_mmr", "b2_merge_shard_lists", "b2_merge_shard_lists_packed", "b2_index_search_push", "b2_merge_shard_lists_wait", "b2_normalize_l2",
     "b2_synth_fill", "b2_launch_count", "b2_launch_count_reset", "b2_prof_enable", "b2_prof_read", "b2_prof_read_kernel", "b2_last_error",
     "b2_version",
 ]
@@ -62,6 +62,10 @@ def _load() -> ctypes.CDLL:
     L.b2_merge_shard_lists.argtypes = [i32, i64, i32, i32, vp, vp, vp, vp, i32, vp]
     L.b2_merge_shard_lists_packed.argtypes = [i32, i64, i32, i32, vp, vp, i64, vp, vp, vp, i32, vp]
     L.b2_merge_shard_lists_packed.restype = i32
+    L.b2_index_search_push.argtypes = [vp, i64, vp, i32, i32, vp, vp, u32, vp]
+    L.b2_index_search_push.restype = i32
+    L.b2_merge_shard_lists_wait.argtypes = [i32, i64, i32, i32, vp, i64, vp, i64, u32, vp, vp, vp, i32, vp]
+    L.b2_merge_shard_lists_wait.restype = i32
     L.b2_normalize_l2.argtypes = [vp, i64, i32, i32, vp]
     L.b2_synth_fill.argtypes = [vp, i64, i64, i32, u64, i32, vp]
     L.b2_launch_count.argtypes = []
@@ -80,7 +84,7 @@ def _load() -> ctypes.CDLL:
     L.b2_version.restype = ctypes.c_char_p
     for name in ("b2_index_create", "b2_index_destroy", "b2_index_add", "b2_index_search",
                  "b2_index_reconstruct_batch", "b2_index_remove_ids", "b2_index_merge_from", "b2_index_reset",
-                 "b2_index_mmr", "b2_merge_shard_lists", "b2_merge_shard_lists_packed", "b2_normalize_l2", "b2_synth_fill"):
+                 "b2_index_mmr", "b2_merge_shard_lists", "b2_merge_shard_lists_packed", "b2_index_search_push", "b2_merge_shard_lists_wait", "b2_normalize_l2", "b2_synth_fill"):
         getattr(L, name).restype = i32
     return L
 

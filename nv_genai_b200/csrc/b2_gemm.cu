@@ -564,7 +564,8 @@ bool gemm_path_supported(int64_t n, int d, int dtype, int k, int64_t nq) {
 }
 
 int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* norms,
-                const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream) {
+                const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream,
+                const PeerPush* push) {
     const bool bf16 = dtype == B2_DTYPE_BF16;
     const int elem = bf16 ? 2 : 4;
     int na = 2;
@@ -656,7 +657,7 @@ int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtyp
     }
     if (rc == B2_OK)
         rc = merge_partials(p.partial, (int)nq, p.n_seg, k, metric, 0, D, I, (size_t)k, stream,
-                            metric == B2_METRIC_L2 ? qn : nullptr);
+                            metric == B2_METRIC_L2 ? qn : nullptr, push);
     cudaFreeAsync(blk, stream);
     return rc;
 }

@@ -465,7 +465,17 @@ __global__ void fill_empty_kernel(float* D, int64_t* I, int64_t n, float dval) {
 
 // Device-side search: q_dev [nq][d], D_dev/I_dev [nq][k]; caller holds the shared lock and the device.
 static int search_device(b2_index* h, int64_t nq, const float* q_dev, int k, float* D_dev, int64_t* I_dev,
-                         cudaStream_t stream) {
+                         cudaStream_t stream, const PeerPush* push = nullptr) {
+    if (h->ntotal == 0 && push != nullptr) {
+        // an empty shard still has to deliver its (all-padding) lists and raise its flags
+        for (int64_t off = 0; off < nq; off += 1024) {
+            PeerPush pp = *push;
+            pp.q_offset = off;
+            B2_TRY(merge_partials(nullptr, (int)std::min<int64_t>(1024, nq - off), 0, k, h->metric, 0, nullptr, nullptr,
+                                  (size_t)k, stream, nullptr, &pp));
+        }
+        return B2_OK;
+    }
     if (h->ntotal == 0) {
         const int64_t tot = nq * k;
         fill_empty_kernel<<<(unsigned)std::min<int64_t>((tot + 255) / 256, 1024), 256, 0, stream>>>(
@@ -475,10 +485,10 @@ static int search_device(b2_index* h, int64_t nq, const float* q_dev, int k, flo
     }
     if (gemm_path_supported(h->ntotal, h->d, h->dtype, k, nq))
         return gemm_search(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, h->metric, h->norms, q_dev, nq, k,
-                           h->num_sms, D_dev, I_dev, stream);
+                           h->num_sms, D_dev, I_dev, stream, push);
     if (scan_tc_supported(h->ntotal, h->d, h->dtype, h->metric, k, nq))
         return scan_tc_search(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, q_dev, (int)nq, k, h->num_sms,
-                              D_dev, I_dev, stream);
+                              D_dev, I_dev, stream, push);
     const int kpad = next_pow2(k < 32 ? 32 : k);
     const int tmax = max_query_tile(h, kpad);
     if (tmax == 0) {
@@ -493,8 +503,14 @@ static int search_device(b2_index* h, int64_t nq, const float* q_dev, int k, flo
         int grid = 0;
         B2_TRY(scan_pass(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, h->metric, q_dev + (size_t)off * h->d,
                          valid, tile, k, h->num_sms, stream, &partial, &grid));
-        int rc = merge_partials(partial, valid, grid, k, h->metric, 0, D_dev + (size_t)off * k, I_dev + (size_t)off * k,
-                                (size_t)k, stream);
+        PeerPush pp;
+        if (push != nullptr) {
+            pp = *push;
+            pp.q_offset = off;
+        }
+        int rc = merge_partials(partial, valid, grid, k, h->metric, 0, D_dev ? D_dev + (size_t)off * k : nullptr,
+                                I_dev ? I_dev + (size_t)off * k : nullptr, (size_t)k, stream, nullptr,
+                                push != nullptr ? &pp : nullptr);
         cudaFreeAsync(partial, stream);
         B2_TRY(rc);
         off += valid;
@@ -776,6 +792,57 @@ int b2_merge_shard_lists(int metric, int64_t nq, int k, int nparts, const float*
         return B2_ERR_CUDA;
     }
     return merge_shards(metric, (int)nq, k, nparts, D_parts, I_parts, D, I, static_cast<cudaStream_t>(stream_));
+}
+
+int b2_index_search_push(b2_index* h, int64_t nq, const float* q_dev, int k, int nparts, void* const* peer_blocks,
+                         uint32_t* const* peer_flags, uint32_t epoch, void* stream_) {
+    B2_TRY(check_handle(h));
+    if (nq <= 0 || k <= 0 || q_dev == nullptr || nparts <= 0 || peer_blocks == nullptr || peer_flags == nullptr) {
+        set_error("b2_index_search_push: bad arguments (nq=%lld, k=%d, nparts=%d)", (long long)nq, k, nparts);
+        return B2_ERR_INVALID;
+    }
+    if (nparts > kMaxPushPeers || k > B2_MAX_K) {
+        set_error("b2_index_search_push: at most %d peers and k <= %d", kMaxPushPeers, B2_MAX_K);
+        return B2_ERR_UNSUPPORTED;
+    }
+    PeerPush push;
+    push.nparts = nparts;
+    push.epoch = epoch;
+    push.nq_total = nq;
+    push.q_offset = 0;
+    for (int g = 0; g < kMaxPushPeers; ++g) {
+        push.block[g] = g < nparts ? static_cast<char*>(peer_blocks[g]) : nullptr;
+        push.flag[g] = g < nparts ? peer_flags[g] : nullptr;
+        if (g < nparts && (push.block[g] == nullptr || push.flag[g] == nullptr)) {
+            set_error("b2_index_search_push: null peer pointer for part %d", g);
+            return B2_ERR_INVALID;
+        }
+    }
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    std::shared_lock<std::shared_mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    if (!g.ok) {
+        set_error("cannot select device %d", h->device);
+        return B2_ERR_CUDA;
+    }
+    return search_device(h, nq, q_dev, k, nullptr, nullptr, stream, &push);
+}
+
+int b2_merge_shard_lists_wait(int metric, int64_t nq, int k, int nparts, const void* blocks, int64_t part_stride_bytes,
+                              const uint32_t* flags, int64_t flag_stride, uint32_t epoch, const int64_t* id_bases,
+                              float* D, int64_t* I, int device, void* stream_) {
+    if (nq <= 0 || k <= 0 || nparts <= 0 || nparts > B2_MAX_SHARDS || part_stride_bytes <= 0 || flag_stride < nq ||
+        !blocks || !flags || !id_bases || !D || !I) {
+        set_error("b2_merge_shard_lists_wait: bad arguments");
+        return B2_ERR_INVALID;
+    }
+    DeviceGuard g(device);
+    if (!g.ok) {
+        set_error("cannot select device %d", device);
+        return B2_ERR_CUDA;
+    }
+    return merge_shards_wait(metric, (int)nq, k, nparts, static_cast<const char*>(blocks), (size_t)part_stride_bytes,
+                             flags, (size_t)flag_stride, epoch, id_bases, D, I, static_cast<cudaStream_t>(stream_));
 }
 
 int b2_merge_shard_lists_packed(int metric, int64_t nq, int k, int nparts, const float* D_parts, const int64_t* I_parts,

@@ -29,11 +29,30 @@ struct IndexView {
 int index_view_lock_shared(b2_index* h, IndexView* v);
 void index_unlock_shared(b2_index* h);
 
+// Peer-memory exchange of the row-sharded search: where the final lists of this rank go instead of local D / I.
+// block[g] = peer g's receive block for THIS rank's lists ([I: nq_total x k int64 | D: nq_total x k fp32]),
+// flag[g] = peer g's flag words for this rank (one per query); after a query's k results are stored to every
+// peer, flag[g][q] = epoch is released system-wide.  Pointers are NVLink peer mappings (or local for g == self).
+constexpr int kMaxPushPeers = 16;
+struct PeerPush {
+    int nparts;
+    uint32_t epoch;
+    int64_t nq_total;
+    int64_t q_offset;  // first query of a merge launch within the call (multi-pass scans)
+    char* block[kMaxPushPeers];
+    uint32_t* flag[kMaxPushPeers];
+};
+
 // b2_merge.cu --------------------------------------------------------------
 // partial: [nq][nlists][k] candidates (pos = local row id) -> D/I [nq][k] with I = id_base + pos.
 // qnorm (optional, L2 only): keys are 2 q.x - |x|^2 and D = max(0, qnorm[q] - key) (the BLAS-path form).
 int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metric, int64_t id_base, float* D,
-                   int64_t* I, size_t out_stride, cudaStream_t stream, const float* qnorm = nullptr);
+                   int64_t* I, size_t out_stride, cudaStream_t stream, const float* qnorm = nullptr,
+                   const PeerPush* push = nullptr);
+// merge of exchanged blocks that first waits (per query) for every part's flag to reach `epoch`
+int merge_shards_wait(int metric, int nq, int k, int nparts, const char* blocks, size_t part_stride_bytes,
+                      const uint32_t* flags, size_t flag_stride_elems, uint32_t epoch, const int64_t* id_bases, float* D,
+                      int64_t* I, cudaStream_t stream);
 
 // b2_gemm.cu ---------------------------------------------------------------
 // Tensor-core search for batches of >= 20 queries (faiss's BLAS threshold), k <= 128.
@@ -43,7 +62,8 @@ int prep_queries(const float* q_dev, int nq, int d, int nq_pad, int kp, int na, 
                  uint32_t* tau, cudaStream_t stream);
 bool gemm_path_supported(int64_t n, int d, int dtype, int k, int64_t nq);
 int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* norms,
-                const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream);
+                const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream,
+                const PeerPush* push = nullptr);
 // (D_parts, I_parts): [nparts][nq][k] -> [nq][k]
 // part g's lists start d_stride_bytes / i_stride_bytes after part g-1's (0 = natural [nparts][nq][k] arrays);
 // id_bases (host, nparts entries, optional): ids in the lists are local to their part, global = base + local.
@@ -73,7 +93,7 @@ int mmr_select(const float* q, int d, int nq, const float* cand_rows /*[nq][fetc
 // Tensor-core scan for 3..16 queries (inner product): the corpus is the M operand, HBM-bound.
 bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t nq);
 int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, const float* q_dev, int nq, int k,
-                   int num_sms, float* D, int64_t* I, cudaStream_t stream);
+                   int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push = nullptr);
 
 // b2_synth.cu --------------------------------------------------------------
 int synth_fill(float* out, int64_t row0, int64_t nrows, int d, uint64_t seed, cudaStream_t stream);

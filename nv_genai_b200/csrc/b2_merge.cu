@@ -15,6 +15,16 @@ namespace b2 {
 
 constexpr int kMergeThreads = 512;
 
+// Peer stores and flags (row-sharded search over NVLink peer memory, see PeerPush in b2_kernels.h)
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
 __device__ __forceinline__ void emit_result(uint64_t c, int metric, int64_t id_base, float* D, int64_t* I,
                                             const float* qn = nullptr) {
     const uint32_t pos = cand_pos(c);
@@ -31,11 +41,39 @@ __device__ __forceinline__ void emit_result(uint64_t c, int metric, int64_t id_b
     }
 }
 
+// Result i of query q (index within this launch): to local D / I, or to every peer's receive block.
+__device__ __forceinline__ void emit_out(uint64_t c, int q, int i, int k, int metric, int64_t id_base, float* D,
+                                         int64_t* I, size_t out_stride, const float* qnorm, const PeerPush& push) {
+    if (push.nparts == 0) {
+        emit_result(c, metric, id_base, D + (size_t)q * out_stride + i, I + (size_t)q * out_stride + i,
+                    qnorm ? qnorm + q : nullptr);
+        return;
+    }
+    float d;
+    int64_t id;
+    emit_result(c, metric, id_base, &d, &id, qnorm ? qnorm + q : nullptr);
+    const size_t off = (size_t)(push.q_offset + q) * k + i;
+    const size_t d_base = (size_t)push.nq_total * k * sizeof(int64_t);
+    for (int g = 0; g < push.nparts; ++g) {
+        reinterpret_cast<int64_t*>(push.block[g])[off] = id;
+        reinterpret_cast<float*>(push.block[g] + d_base)[off] = d;
+    }
+}
+// After a query's results are stored everywhere: make them visible system-wide, then raise the query's flag on
+// every peer.  Called by all threads of the CTA.
+__device__ __forceinline__ void push_signal(int q, const PeerPush& push) {
+    if (push.nparts == 0) return;
+    __threadfence_system();
+    __syncthreads();
+    if ((int)threadIdx.x < push.nparts) st_release_sys(push.flag[threadIdx.x] + push.q_offset + q, push.epoch);
+}
+
 __global__ void __launch_bounds__(kMergeThreads) merge_partials_kernel(const uint64_t* __restrict__ partial,
                                                                       int total, int k, int kpad, int sort_n,
                                                                       int metric, int64_t id_base, float* D,
                                                                       int64_t* I, size_t out_stride,
-                                                                      const float* __restrict__ qnorm) {
+                                                                      const float* __restrict__ qnorm,
+                                                                      const PeerPush push) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw);
     const int q = blockIdx.x, tid = threadIdx.x;
@@ -47,9 +85,8 @@ __global__ void __launch_bounds__(kMergeThreads) merge_partials_kernel(const uin
         block_bitonic_desc(buf, sort_n, tid, kMergeThreads);
     }
     __syncthreads();
-    for (int i = tid; i < k; i += kMergeThreads)
-        emit_result(buf[i], metric, id_base, D + (size_t)q * out_stride + i, I + (size_t)q * out_stride + i,
-                    qnorm ? qnorm + q : nullptr);
+    for (int i = tid; i < k; i += kMergeThreads) emit_out(buf[i], q, i, k, metric, id_base, D, I, out_stride, qnorm, push);
+    push_signal(q, push);
 }
 
 // ---------------------------------------------------------------- k <= 32: register merge
@@ -86,7 +123,8 @@ __global__ void __launch_bounds__(kMergeThreads) merge_partials_small_kernel(con
                                                                             int total, int k, int metric,
                                                                             int64_t id_base, float* D, int64_t* I,
                                                                             size_t out_stride,
-                                                                            const float* __restrict__ qnorm) {
+                                                                            const float* __restrict__ qnorm,
+                                                                            const PeerPush push) {
     __shared__ uint64_t lists[kMergeThreads / 32][32];
     const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int kWarps = kMergeThreads / 32;
@@ -107,19 +145,30 @@ __global__ void __launch_bounds__(kMergeThreads) merge_partials_small_kernel(con
             const uint64_t worst = shfl_u64(best, 31);
             if (__any_sync(kFull, c > worst)) best = warp_merge_desc(best, c, lane);
         }
-        if (lane < k)
-            emit_result(best, metric, id_base, D + (size_t)q * out_stride + lane, I + (size_t)q * out_stride + lane,
-                        qnorm ? qnorm + q : nullptr);
+        if (lane < k) emit_out(best, q, lane, k, metric, id_base, D, I, out_stride, qnorm, push);
     }
+    push_signal(q, push);
 }
 
 int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metric, int64_t id_base, float* D,
-                   int64_t* I, size_t out_stride, cudaStream_t stream, const float* qnorm) {
+                   int64_t* I, size_t out_stride, cudaStream_t stream, const float* qnorm, const PeerPush* push_in) {
     const int kpad = next_pow2(k < 32 ? 32 : k);
     const int total = nlists * k;
+    PeerPush push;
+    if (push_in != nullptr) {
+        push = *push_in;
+    } else {
+        push.nparts = 0;
+        push.epoch = 0;
+        push.nq_total = push.q_offset = 0;
+        for (int g = 0; g < kMaxPushPeers; ++g) {
+            push.block[g] = nullptr;
+            push.flag[g] = nullptr;
+        }
+    }
     if (kpad == 32) {
         merge_partials_small_kernel<<<nq, kMergeThreads, 0, stream>>>(partial, total, k, metric, id_base, D, I,
-                                                                      out_stride, qnorm);
+                                                                      out_stride, qnorm, push);
         B2_AFTER_LAUNCH();
         return B2_OK;
     }
@@ -128,7 +177,7 @@ int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metri
     while (sort_n < want && sort_n < 4096) sort_n <<= 1;
     const size_t smem = (size_t)sort_n * sizeof(uint64_t);
     merge_partials_kernel<<<nq, kMergeThreads, smem, stream>>>(partial, total, k, kpad, sort_n, metric, id_base, D, I,
-                                                               out_stride, qnorm);
+                                                               out_stride, qnorm, push);
     B2_AFTER_LAUNCH();
     return B2_OK;
 }
@@ -147,19 +196,34 @@ __global__ void __launch_bounds__(kMergeThreads) merge_shards_kernel(int metric,
                                                                     const char* __restrict__ Dp,
                                                                     const char* __restrict__ Ip, size_t d_stride, size_t i_stride,
                                                                     const ShardBases bases, int use_bases, int sort_n,
-                                                                    float* D, int64_t* I) {
+                                                                    float* D, int64_t* I,
+                                                                    const uint32_t* __restrict__ flags,
+                                                                    size_t flag_stride, uint32_t epoch) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw);
     const int q = blockIdx.x, tid = threadIdx.x;
     const int total = nparts * k;
+    if (flags != nullptr) {
+        // peer-memory exchange: part g's lists for this query are complete once its flag shows this epoch
+        if (tid < nparts) {
+            const uint32_t* f = flags + (size_t)tid * flag_stride + q;
+            const unsigned long long t0 = clock64();
+            while (ld_acquire_sys(f) != epoch) {
+                __nanosleep(64);
+                if (clock64() - t0 > 40000000000ull) __trap();  // ~20 s: a peer never delivered
+            }
+        }
+        __syncthreads();
+        __threadfence_system();
+    }
     for (int i = tid; i < sort_n; i += kMergeThreads) {
         uint64_t c = B2_SENTINEL;
         if (i < total) {
             const int part = i / k, r = i - part * k;
             const size_t off = (size_t)q * k + r;
-            const int64_t id = reinterpret_cast<const int64_t*>(Ip + (size_t)part * i_stride)[off];
+            const int64_t id = __ldcg(reinterpret_cast<const long long*>(Ip + (size_t)part * i_stride) + off);
             if (id >= 0) {
-                const float d = reinterpret_cast<const float*>(Dp + (size_t)part * d_stride)[off];
+                const float d = __ldcg(reinterpret_cast<const float*>(Dp + (size_t)part * d_stride) + off);
                 c = pack_cand(metric == B2_METRIC_IP ? d : -d, (uint32_t)i);
             }
         }
@@ -177,16 +241,16 @@ __global__ void __launch_bounds__(kMergeThreads) merge_shards_kernel(int metric,
         } else {
             const int part = pos / k, r = pos - part * k;
             const size_t off = (size_t)q * k + r;
-            const int64_t id = reinterpret_cast<const int64_t*>(Ip + (size_t)part * i_stride)[off];
+            const int64_t id = __ldcg(reinterpret_cast<const long long*>(Ip + (size_t)part * i_stride) + off);
             *Iq = use_bases ? id + bases.v[part] : id;
-            *Dq = reinterpret_cast<const float*>(Dp + (size_t)part * d_stride)[off];
+            *Dq = __ldcg(reinterpret_cast<const float*>(Dp + (size_t)part * d_stride) + off);
         }
     }
 }
 
-int merge_shards(int metric, int nq, int k, int nparts, const float* D_parts, const int64_t* I_parts, float* D,
-                 int64_t* I, cudaStream_t stream, size_t d_stride_bytes, size_t i_stride_bytes,
-                 const int64_t* id_bases) {
+static int merge_shards_impl(int metric, int nq, int k, int nparts, const float* D_parts, const int64_t* I_parts,
+                             float* D, int64_t* I, cudaStream_t stream, size_t d_stride_bytes, size_t i_stride_bytes,
+                             const int64_t* id_bases, const uint32_t* flags, size_t flag_stride, uint32_t epoch) {
     const long long total = (long long)nparts * k;
     const int sort_n = next_pow2((int)(total < 32 ? 32 : total));
     const size_t smem = (size_t)sort_n * sizeof(uint64_t);
@@ -205,9 +269,26 @@ int merge_shards(int metric, int nq, int k, int nparts, const float* D_parts, co
     }
     merge_shards_kernel<<<nq, kMergeThreads, smem, stream>>>(metric, k, nparts, nq, reinterpret_cast<const char*>(D_parts),
                                                              reinterpret_cast<const char*>(I_parts), d_stride_bytes,
-                                                             i_stride_bytes, bases, id_bases != nullptr, sort_n, D, I);
+                                                             i_stride_bytes, bases, id_bases != nullptr, sort_n, D, I,
+                                                             flags, flag_stride, epoch);
     B2_AFTER_LAUNCH();
     return B2_OK;
+}
+
+int merge_shards(int metric, int nq, int k, int nparts, const float* D_parts, const int64_t* I_parts, float* D,
+                 int64_t* I, cudaStream_t stream, size_t d_stride_bytes, size_t i_stride_bytes,
+                 const int64_t* id_bases) {
+    return merge_shards_impl(metric, nq, k, nparts, D_parts, I_parts, D, I, stream, d_stride_bytes, i_stride_bytes,
+                             id_bases, nullptr, 0, 0);
+}
+
+int merge_shards_wait(int metric, int nq, int k, int nparts, const char* blocks, size_t part_stride_bytes,
+                      const uint32_t* flags, size_t flag_stride_elems, uint32_t epoch, const int64_t* id_bases, float* D,
+                      int64_t* I, cudaStream_t stream) {
+    const int64_t* Ip = reinterpret_cast<const int64_t*>(blocks);
+    const float* Dp = reinterpret_cast<const float*>(blocks + (size_t)nq * k * sizeof(int64_t));
+    return merge_shards_impl(metric, nq, k, nparts, Dp, Ip, D, I, stream, part_stride_bytes, part_stride_bytes, id_bases,
+                             flags, flag_stride_elems, epoch);
 }
 
 }  // namespace b2

@@ -348,7 +348,7 @@ bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t n
 }
 
 int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, const float* q_dev, int nq, int k,
-                   int num_sms, float* D, int64_t* I, cudaStream_t stream) {
+                   int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push) {
     const bool bf16 = dtype == B2_DTYPE_BF16;
     const int elem = bf16 ? 2 : 4;
     const size_t kbytes = (((size_t)d * elem + kSlice - 1) / kSlice) * kSlice;
@@ -387,7 +387,7 @@ int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int d
     if (rc == B2_OK) rc = prep_queries(q_dev, nq, d, kNQ, kp, 2, bf16, Q, nullptr, nullptr, stream);
     if (rc == B2_OK)
         rc = bf16 ? launch_scan_tc<0>(tmRows, tmQ, p, grid, smem, stream) : launch_scan_tc<1>(tmRows, tmQ, p, grid, smem, stream);
-    if (rc == B2_OK) rc = merge_partials(p.partial, nq, grid, k, B2_METRIC_IP, 0, D, I, (size_t)k, stream);
+    if (rc == B2_OK) rc = merge_partials(p.partial, nq, grid, k, B2_METRIC_IP, 0, D, I, (size_t)k, stream, nullptr, push);
     cudaFreeAsync(blk, stream);
     return rc;
 }

@@ -14,6 +14,8 @@ and there is no CPU fallback in the product path.
 """
 from __future__ import annotations
 
+import ctypes
+import os
 from typing import Any, Callable, Optional, Tuple
 
 
@@ -22,6 +24,48 @@ def shard_bounds(n: int, world: int, rank: int) -> Tuple[int, int]:
     base, rem = divmod(int(n), int(world))
     lo = rank * base + min(rank, rem)
     return lo, lo + base + (1 if rank < rem else 0)
+
+
+class _PeerExchange:
+    """NVLink peer-memory exchange for the sharded search (b2_index_search_push / b2_merge_shard_lists_wait):
+    one symmetric allocation per rank = 2 alternating sets of `world` receive blocks + per-query flag words,
+    mapped into every rank's address space by torch symmetric memory (torch is plumbing: it only provides the
+    peer mappings).  The merge kernel that produces a rank's final lists stores them into every rank's block and
+    raises the flags; the receiving merge kernel waits on its own flags.  No collective on the data path."""
+
+    MAX_RESULTS = 1 << 17  # nq * k per search (12 B each -> 1.5 MB blocks)
+    MAX_NQ = 4096
+
+    def __init__(self, torch, dist, group, device, world: int, rank: int):
+        import torch.distributed._symmetric_memory as symm
+
+        self.world, self.rank = world, rank
+        self.blk = self.MAX_RESULTS * 12
+        self.slot_bytes = world * self.blk
+        self.flag_off = 2 * self.slot_bytes
+        total = self.flag_off + 2 * world * self.MAX_NQ * 4
+        self.buf = symm.empty(total, dtype=torch.uint8, device=device)
+        self.buf.zero_()
+        torch.cuda.synchronize(device)
+        self.hdl = symm.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+        self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        if len(self.ptrs) != world or any(p == 0 for p in self.ptrs):
+            raise RuntimeError("symmetric memory rendezvous returned no peer pointers")
+        self.epoch = 0
+
+    def fits(self, nq: int, k: int) -> bool:
+        return nq <= self.MAX_NQ and nq * k <= self.MAX_RESULTS
+
+    def next_slot(self):
+        """(epoch, push block pointers, push flag pointers, local blocks, local flags) of the next search."""
+        self.epoch = (self.epoch + 1) & 0xFFFFFFFF or 1
+        e, w, r = self.epoch, self.world, self.rank
+        slot = e & 1
+        blocks = [self.ptrs[g] + slot * self.slot_bytes + r * self.blk for g in range(w)]
+        flags = [self.ptrs[g] + self.flag_off + (slot * w + r) * self.MAX_NQ * 4 for g in range(w)]
+        local_blocks = self.ptrs[r] + slot * self.slot_bytes
+        local_flags = self.ptrs[r] + self.flag_off + slot * w * self.MAX_NQ * 4
+        return e, blocks, flags, local_blocks, local_flags
 
 
 class ShardedFlatIndex:
@@ -51,6 +95,19 @@ class ShardedFlatIndex:
             merge_fn = merge_shard_lists
         self._merge = merge_fn
         self._ws = {}  # (nq, k) -> (packed send block, gathered blocks)
+        self._peer = None
+        if self._fast and dist.get_backend(group) == "nccl" and not os.environ.get("B2_NO_PEER_PUSH"):
+            ok = 1
+            try:
+                dev = torch.device("cuda", getattr(local_index, "device", torch.cuda.current_device()))
+                self._peer = _PeerExchange(torch, dist, group, dev, self.world, self.rank)
+            except Exception as exc:  # no P2P / symmetric memory on this system: NCCL all-gather path
+                self._peer, ok = None, 0
+                self._peer_error = repr(exc)
+            flag = torch.tensor([ok], dtype=torch.int32, device=self._comm_device())
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)  # all ranks take the same path
+            if int(flag.item()) == 0:
+                self._peer = None
         self.bases = [0] * (self.world + 1)  # bases[g] = global id of shard g's first row
 
     # ------------------------------------------------------------------ build
@@ -106,6 +163,27 @@ class ShardedFlatIndex:
 
             nq = q.shape[0] if q.dim() == 2 else 1
             nres = nq * k
+            if self._peer is not None and self._peer.fits(nq, k):
+                # peer-memory exchange: the merge kernel stores this rank's lists into every rank's block over
+                # NVLink and raises per-query flags; the receiving merge waits on its flags.  3 launches, no collective.
+                from . import _native as N
+                from .index import _stream_for
+
+                e, blocks, flags, lblocks, lflags = self._peer.next_slot()
+                w = self.world
+                dev = q.device.index
+                stream = _stream_for(dev)
+                assert q.dim() == 2 and q.shape[1] == self.d, "query dimension does not match the index"
+                qc = q if (q.dtype == t.float32 and q.is_contiguous()) else q.to(t.float32).contiguous()
+                N.check(N.lib.b2_index_search_push(self.local._h, nq, qc.data_ptr(), k, w, (ctypes.c_void_p * w)(*blocks),
+                                                   (ctypes.c_void_p * w)(*flags), e, stream))
+                D = t.empty((nq, k), dtype=t.float32, device=q.device)
+                I = t.empty((nq, k), dtype=t.int64, device=q.device)
+                bases = (ctypes.c_int64 * w)(*[int(b) for b in self.bases[:w]])
+                N.check(N.lib.b2_merge_shard_lists_wait(self.metric, nq, k, w, lblocks, self._peer.blk, lflags,
+                                                        self._peer.MAX_NQ, e, bases, D.data_ptr(), I.data_ptr(), dev,
+                                                        stream))
+                return D, I
             ws = self._ws.get((nq, k))
             if ws is None:
                 ws = (t.empty(nres * 12, dtype=t.uint8, device=q.device),

@@ -307,3 +307,22 @@ def test_packed_shard_exchange_layout_equals_single_index_bit_for_bit():
                 # tensor path: the segment boundaries differ between the whole index and the shards, the scores
                 # of a row do not (same MMA sequence per row)
                 assert torch.equal(D, Dw)
+
+
+def test_multi_gpu_sharded_search_peer_and_nccl_exchange():
+    """Two real ranks (one per GPU) when the box has them: tests/mp_sharded_gpu.py under torchrun."""
+    import subprocess
+    import sys
+
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    script = os.path.join(HERE, "mp_sharded_gpu.py")
+    res = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29533", script],
+                         capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    line = [ln for ln in res.stdout.splitlines() if ln.startswith("{")][-1]
+    rep = json.loads(line)
+    assert rep["ok"] and all(c["equal"] for c in rep["cases"])
