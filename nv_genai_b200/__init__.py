@@ -7,6 +7,7 @@ loads nv_genai_b200/lib/libb2flat.so (hand-written sm_100a CUDA behind the C ABI
 include/b2_flat.h); there is no CPU or PyTorch fallback.
 """
 from . import _native
+from .batching import BatchingIndex
 from .documents import DistanceStrategy, Document, Embeddings, InMemoryDocstore
 from .index import (METRIC_INNER_PRODUCT, METRIC_L2, IndexFlat, IndexFlatIP, IndexFlatL2, merge_shard_lists,
                     normalize_L2, synth_fill)
@@ -19,6 +20,6 @@ B200FlatStore = FAISS  # the working name used in SURVEY.md 8b
 __all__ = [
     "FAISS", "B200FlatStore", "VectorStoreRetriever", "IndexFlat", "IndexFlatL2", "IndexFlatIP",
     "METRIC_INNER_PRODUCT", "METRIC_L2", "normalize_L2", "read_index", "write_index", "Document", "Embeddings",
-    "InMemoryDocstore", "DistanceStrategy", "ShardedFlatIndex", "shard_bounds", "merge_shard_lists", "synth_fill",
+    "InMemoryDocstore", "DistanceStrategy", "ShardedFlatIndex", "BatchingIndex", "shard_bounds", "merge_shard_lists", "synth_fill",
 ]
 __version__ = "0.1.0"

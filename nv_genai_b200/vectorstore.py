@@ -56,7 +56,7 @@ class FAISS:
         if not hasattr(embedding_function, "embed_documents") and not hasattr(embedding_function, "embed_query"):
             logger.warning("`embedding_function` is expected to be an Embeddings object, support for passing in a "
                            "function will soon be removed.")
-        if not isinstance(index, _ix.IndexFlat):
+        if not isinstance(getattr(index, "wrapped", index), _ix.IndexFlat):
             raise TypeError("index must be a nv_genai_b200 IndexFlatL2 / IndexFlatIP (there is no CPU faiss path)")
         self.embedding_function = embedding_function
         self.index = index
@@ -229,6 +229,23 @@ class FAISS:
         pairs = self.similarity_search_with_score(query, k, filter=filter, fetch_k=fetch_k, **kwargs)
         return [doc for doc, _ in pairs]
 
+    def enable_request_batching(self, max_batch: int = 16, max_wait_us: float = 200.0) -> None:
+        """Coalesce concurrent single-query searches (thread-pool / `asyncio.gather` callers such as
+        /root/reference/experimental/event-driven-rag-cve-analysis/cyber_dev_day/faiss_vdb_service.py:169-174) into
+        batched scans: one pass over the rows serves up to `max_batch` requests.  See nv_genai_b200/batching.py."""
+        from .batching import BatchingIndex
+
+        if not isinstance(self.index, BatchingIndex):
+            self.index = BatchingIndex(self.index, max_batch=max_batch, max_wait_us=max_wait_us)
+
+    def disable_request_batching(self) -> None:
+        from .batching import BatchingIndex
+
+        if isinstance(self.index, BatchingIndex):
+            proxy = self.index
+            self.index = proxy.wrapped
+            proxy.close()
+
     def search_batch(self, X: Any, k: int = 4):
         """Batched fast path: X [B, d] (numpy or torch CUDA) -> (D [B, k], I [B, k]); no Python per row."""
         if self._normalize_L2:
@@ -364,7 +381,7 @@ class FAISS:
         clash = {tid for _, tid, _ in full_info}.intersection(self.docstore._dict)
         if clash:
             raise ValueError(f"Tried to add ids that already exist: {clash}")
-        self.index.merge_from(target.index)
+        self.index.merge_from(getattr(target.index, "wrapped", target.index))
         self.docstore.add({_id: doc for _, _id, doc in full_info})
         self.index_to_docstore_id.update({index: _id for index, _id, _ in full_info})
 
@@ -434,7 +451,7 @@ class FAISS:
         """`<index_name>.faiss` in faiss's own IndexFlat file format + `<index_name>.pkl` (docstore, id map)."""
         path = Path(folder_path)
         path.mkdir(exist_ok=True, parents=True)
-        write_index(self.index, str(path / f"{index_name}.faiss"))
+        write_index(getattr(self.index, "wrapped", self.index), str(path / f"{index_name}.faiss"))
         with open(path / f"{index_name}.pkl", "wb") as f:
             pickle.dump((self.docstore, self.index_to_docstore_id), f)
 
@@ -457,7 +474,7 @@ class FAISS:
         return cls(embeddings, index, docstore, index_to_docstore_id, **kwargs)
 
     def serialize_to_bytes(self) -> bytes:
-        return pickle.dumps((self.index, self.docstore, self.index_to_docstore_id))
+        return pickle.dumps((getattr(self.index, "wrapped", self.index), self.docstore, self.index_to_docstore_id))
 
     @classmethod
     def deserialize_from_bytes(cls, serialized: bytes, embeddings: Embeddings, **kwargs: Any) -> "FAISS":

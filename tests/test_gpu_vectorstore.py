@@ -115,3 +115,38 @@ def test_normalize_l2_store_and_mmr_and_async():
 
     res = asyncio.run(many())
     assert [r[0].page_content for r in res] == TEXTS[:16]
+
+
+def test_concurrent_single_vector_searches_are_coalesced_into_batched_scans():
+    """faiss_vdb_service.py:169-174 fires many asimilarity_search_by_vector at once: with request batching on, they
+    share scans of the corpus (fewer kernel launches) and return what the one-at-a-time searches return."""
+    from nv_genai_b200 import FAISS, IndexFlatIP, InMemoryDocstore, DistanceStrategy, _native
+
+    emb = HashEmbeddings(D)
+    n = 20_000
+    x = flat.synth(0, n, D, 77)
+    flat.normalize_L2(x)
+    vs = FAISS(emb, IndexFlatIP(D), InMemoryDocstore(), {}, distance_strategy=DistanceStrategy.MAX_INNER_PRODUCT)
+    vs.add_embeddings(([f"row {i}" for i in range(n)], x))
+    qs = flat.synth(0, 48, D, 78)
+    flat.normalize_L2(qs)
+    want = [vs.similarity_search_with_score_by_vector(q.tolist(), k=5) for q in qs]
+    _native.launch_count_reset()
+    for q in qs[:8]:
+        vs.similarity_search_with_score_by_vector(q.tolist(), k=5)
+    alone = _native.launch_count() / 8
+
+    vs.enable_request_batching(max_batch=16, max_wait_us=20_000)
+    try:
+        async def fire():
+            return await asyncio.gather(*[vs.asimilarity_search_with_score_by_vector(q.tolist(), k=5) for q in qs])
+
+        _native.launch_count_reset()
+        got = asyncio.run(fire())
+        launches = _native.launch_count()
+    finally:
+        vs.disable_request_batching()
+    assert launches < alone * len(qs) * 0.6, (launches, alone)  # scans were shared
+    for a, b in zip(got, want):
+        assert [d.page_content for d, _ in a] == [d.page_content for d, _ in b]
+        np.testing.assert_allclose([float(s) for _, s in a], [float(s) for _, s in b], rtol=1e-5, atol=1e-6)

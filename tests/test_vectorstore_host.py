@@ -268,3 +268,77 @@ def test_plain_function_embedding_still_works_with_a_warning(caplog):
 def test_rejects_foreign_index_objects():
     with pytest.raises(TypeError):
         FAISS(HashEmbeddings(D), object(), InMemoryDocstore(), {})
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# request coalescing (nv_genai_b200/batching.py), host logic on CPU with the oracle-backed index
+def test_request_batching_coalesces_concurrent_single_vector_searches():
+    import threading
+
+    from nv_genai_b200.batching import BatchingIndex
+
+    d, n = 32, 500
+    x = flat.synth(0, n, d, 123)
+    base = OracleIndex(d, METRIC_L2)
+    base.add(x)
+    calls = []
+    orig = base.search
+
+    def counting_search(q, k):
+        calls.append(np.atleast_2d(q).shape[0])
+        return orig(q, k)
+
+    base.search = counting_search
+    proxy = BatchingIndex(base, max_batch=8, max_wait_us=200_000)  # generous window: the test must coalesce
+    try:
+        assert proxy.d == d and proxy.ntotal == n  # the faiss-shaped interface passes through
+        qs = flat.synth(0, 8, d, 456)
+        ks = [4, 1, 7, 4, 4, 2, 4, 3]
+        out = [None] * 8
+
+        def worker(i):
+            out[i] = proxy.search(qs[i:i + 1], ks[i])
+
+        threads = [threading.Thread(target=worker, args=(i,)) for i in range(8)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join(timeout=30)
+        assert proxy.requests_served == 8 and proxy.batches_run < 8  # at least some were merged
+        assert sum(calls) == 8 and max(calls) > 1
+        for i in range(8):
+            D, I = out[i]
+            Dr, Ir = flat.search(x, qs[i:i + 1], ks[i], METRIC_L2)
+            assert D.shape == (1, ks[i]) and np.array_equal(I, Ir) and np.allclose(D, Dr, rtol=1e-6)
+        # a call that already is a batch, and k validation, bypass / behave like the wrapped index
+        D, I = proxy.search(qs[:3], 2)
+        assert D.shape == (3, 2)
+        with pytest.raises(AssertionError):
+            proxy.search(qs[:1], 0)
+        with pytest.raises(AssertionError):
+            proxy.search(np.zeros((1, d + 1), np.float32), 2)
+    finally:
+        proxy.close()
+
+
+def test_vectorstore_with_request_batching_gives_the_same_documents():
+    from concurrent.futures import ThreadPoolExecutor
+
+    emb = HashEmbeddings(48)
+    texts = [f"document number {i}" for i in range(200)]
+    vs = FAISS(emb, OracleIndex(48, METRIC_L2), InMemoryDocstore(), {})
+    vs.add_texts(texts)
+    want = [vs.similarity_search_with_score(t, k=3) for t in texts[:20]]
+    vs.enable_request_batching(max_batch=16, max_wait_us=50_000)
+    try:
+        with ThreadPoolExecutor(max_workers=20) as ex:
+            got = list(ex.map(lambda t: vs.similarity_search_with_score(t, k=3), texts[:20]))
+        for a, b in zip(got, want):
+            assert [d.page_content for d, _ in a] == [d.page_content for d, _ in b]
+            assert np.allclose([s for _, s in a], [s for _, s in b], rtol=1e-6)
+        assert vs.index.batches_run < 20
+        data = vs.serialize_to_bytes()  # the proxy (a thread) is not what gets pickled
+        assert isinstance(data, bytes)
+    finally:
+        vs.disable_request_batching()
+    assert isinstance(vs.index, OracleIndex)
