@@ -62,6 +62,8 @@ constexpr int kMaxStages = 8;
 constexpr int kCandCap = 1024;                     // candidate log entries per query per CTA
 constexpr int kGemmMaxK = 128;                     // heap slots per query (k <= 128 on this path)
 constexpr int kEpiThreads = 128;
+constexpr int kXfThreads = 256;                    // fp32 rows: transform threads (warps 6..13)
+constexpr int kThreadsBf16 = 192, kThreadsFp32 = 192 + kXfThreads;
 
 struct GemmParams {
     int nq, nq_pad;
@@ -72,6 +74,7 @@ struct GemmParams {
     int n_qt, n_seg, tiles_per_seg, n_tiles, n_items;
     int num_stages;
     int trunc_hi;       // fp32 rows: 1 = leave the raw tile as the hi operand (hardware truncation), 0 = round it in place
+    int mixed;          // fp32 rows: 1 = correction products on the bf16 pipe (see kernel comment), 0 = plain 3xTF32
     const float* norms; // |x|^2 per stored row
     uint64_t* cand;     // [grid][kCandCap][128]
     uint64_t* partial;  // [nq_pad][n_seg][k]
@@ -173,7 +176,7 @@ __device__ __forceinline__ void compact_log(uint64_t* __restrict__ log, int& cnt
 // KIND 0: bf16 rows, kind::f16.  KIND 1: fp32 rows, kind::tf32 (3xTF32).  NA: query parts (1 = hi only, 2 = hi + lo).
 // SWB: bytes of K per pipeline stage = the shared-memory swizzle width (64 or 128).
 template <int KIND, int NA, int SWB>
-__global__ void __launch_bounds__(KIND == 1 ? 320 : 192, 1)
+__global__ void __launch_bounds__(KIND == 1 ? kThreadsFp32 : kThreadsBf16, 1)
 gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
     constexpr int ELEM = (KIND == 0) ? 2 : 4;
     constexpr int kSwizzleBytes = SWB;
@@ -189,6 +192,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     constexpr uint32_t FMT = (KIND == 0) ? 1u : 2u;
     constexpr uint32_t IDESC = (1u << 4) | (FMT << 7) | (FMT << 10) | ((uint32_t)(kTileN >> 3) << 17) |
                                ((uint32_t)(kTileM >> 4) << 24);
+    constexpr uint32_t IDESC_BF16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kTileN >> 3) << 17) |
+                                    ((uint32_t)(kTileM >> 4) << 24);
 
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
@@ -212,7 +217,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int s = 0; s < S; ++s) {
             mbar_init(smem_u32(full_bar + s), 1);
             mbar_init(smem_u32(empty_bar + s), 1);
-            mbar_init(smem_u32(xf_bar + s), 4);
+            mbar_init(smem_u32(xf_bar + s), kXfThreads / 32);
         }
         for (int b = 0; b < 2; ++b) {  // fp32 rows use only buffer 0
             mbar_init(smem_u32(tfull_bar + b), 1);
@@ -290,6 +295,9 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             umma<KIND>(d_tmem, a_hi0 + dj, b_hi0 + dj, IDESC, acc);
                             if (KIND == 0) {
                                 if (NA == 2) umma<KIND>(d_tmem, a_lo0 + dj, b_hi0 + dj, IDESC, 1u);
+                            } else if (p.mixed) {
+                                // both correction products in ONE bf16 MMA: [q_hi | q_lo] . [x_lo | x_hi] over a doubled K
+                                if (NA == 2) umma<0>(c_tmem, a_lo0 + dj, b_lo0 + dj, IDESC_BF16, acc);
                             } else {
                                 umma<KIND>(c_tmem, a_hi0 + dj, b_lo0 + dj, IDESC, acc);
                                 if (NA == 2) umma<KIND>(c_tmem, a_lo0 + dj, b_hi0 + dj, IDESC, 1u);
@@ -310,7 +318,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     } else if (warp >= 6) {
         // ================= fp32 rows: split the landed B slice into tf32 hi (in place) + lo
         if (KIND == 1) {
-            const int xt = tid - 192;  // 0..127
+            const int xt = tid - 192;  // 0..kXfThreads-1
             int stage = 0;
             uint32_t phase = 0;
             for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
@@ -322,9 +330,39 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         mbar_wait(smem_u32(full_bar + stage), phase);
                         float4* b_hi = reinterpret_cast<float4*>(stages + (size_t)stage * STAGE_BYTES + B_OFF);
                         float4* b_lo = reinterpret_cast<float4*>(stages + (size_t)stage * STAGE_BYTES + BLO_OFF);
+                        if (p.mixed) {
+                            // correction operand: per row, [bf16(x - trunc_tf32(x)) | bf16(x)] over this K slice, written
+                            // in the same swizzled K-major layout (16-byte chunk index XOR a row-dependent mask)
+                            constexpr int ITEMS_PER_ROW = SWB / 32;  // 8 floats in, one lo chunk + one hi chunk out
 #pragma unroll
-                        for (int i = 0; i < kBTileBytes / 16 / 128; ++i) {
-                            const int idx = i * 128 + xt;
+                            for (int i = 0; i < kTileN * ITEMS_PER_ROW / kXfThreads; ++i) {
+                                const int w = i * kXfThreads + xt;
+                                const int r = w / ITEMS_PER_ROW, g = w % ITEMS_PER_ROW;
+                                const int sw = (SWB == 128) ? (r & 7) : ((r >> 1) & 3);
+                                const int rowc = r * (SWB / 16);  // first chunk of the row
+                                const float4 x0 = b_hi[rowc + ((2 * g) ^ sw)];
+                                const float4 x1 = b_hi[rowc + ((2 * g + 1) ^ sw)];
+                                const float xs[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+                                uint32_t lo[4], hi[4];
+#pragma unroll
+                                for (int e = 0; e < 4; ++e) {
+                                    const float a = xs[2 * e], b = xs[2 * e + 1];
+                                    const float la = a - __uint_as_float(__float_as_uint(a) & 0xffffe000u);
+                                    const float lb = b - __uint_as_float(__float_as_uint(b) & 0xffffe000u);
+                                    __nv_bfloat162 pl = __floats2bfloat162_rn(la, lb), ph = __floats2bfloat162_rn(a, b);
+                                    lo[e] = *reinterpret_cast<uint32_t*>(&pl);
+                                    hi[e] = *reinterpret_cast<uint32_t*>(&ph);
+                                }
+                                b_lo[rowc + (g ^ sw)] = make_float4(__uint_as_float(lo[0]), __uint_as_float(lo[1]),
+                                                                    __uint_as_float(lo[2]), __uint_as_float(lo[3]));
+                                b_lo[rowc + ((ITEMS_PER_ROW + g) ^ sw)] =
+                                    make_float4(__uint_as_float(hi[0]), __uint_as_float(hi[1]), __uint_as_float(hi[2]),
+                                                __uint_as_float(hi[3]));
+                            }
+                        } else {
+#pragma unroll
+                        for (int i = 0; i < kBTileBytes / 16 / kXfThreads; ++i) {
+                            const int idx = i * kXfThreads + xt;
                             const float4 x = b_hi[idx];
                             float4 h, l;
                             if (p.trunc_hi) {
@@ -344,6 +382,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             }
                             l.x = x.x - h.x; l.y = x.y - h.y; l.z = x.z - h.z; l.w = x.w - h.w;
                             b_lo[idx] = l;
+                        }
                         }
                         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                         __syncwarp();
@@ -486,7 +525,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 // q [nq][d] fp32 -> A [NA][nq_pad][kp] (bf16 or fp32-holding-tf32), zero padded; qn[q] = |q|^2.
 template <int KIND>
 __global__ void prep_queries_kernel(const float* __restrict__ q, int nq, int d, int nq_pad, int kp, int na, void* A,
-                                    float* __restrict__ qn, uint32_t* __restrict__ tau) {
+                                    float* __restrict__ qn, uint32_t* __restrict__ tau, int mixed_slice) {
     const int lane = threadIdx.x & 31;
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= nq_pad) return;
@@ -505,7 +544,15 @@ __global__ void prep_queries_kernel(const float* __restrict__ q, int nq, int d, 
             asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
             const float h = __uint_as_float(u);
             a[(size_t)row * kp + c] = h;
-            if (na == 2) a[((size_t)nq_pad + row) * kp + c] = x - h;
+            if (na == 2 && mixed_slice > 0) {
+                // part 1 = the bf16 correction operand: per K slice [bf16(q) | bf16(q - tf32(q))], same bytes per row
+                __nv_bfloat16* a1 = reinterpret_cast<__nv_bfloat16*>(a + ((size_t)nq_pad + row) * kp);
+                const int sl = c / mixed_slice, j = c - sl * mixed_slice;
+                a1[sl * 2 * mixed_slice + j] = __float2bfloat16_rn(x);
+                a1[sl * 2 * mixed_slice + mixed_slice + j] = __float2bfloat16_rn(x - h);
+            } else if (na == 2) {
+                a[((size_t)nq_pad + row) * kp + c] = x - h;
+            }
         }
     }
 #pragma unroll
@@ -537,7 +584,7 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
         }
     }
     void* tok = prof_begin(stream);
-    kern<<<grid, KIND == 1 ? 320 : 192, smem, stream>>>(tmA, tmB, p);
+    kern<<<grid, KIND == 1 ? kThreadsFp32 : kThreadsBf16, smem, stream>>>(tmA, tmB, p);
     prof_end(tok, 1, stream);
     B2_AFTER_LAUNCH();
     return B2_OK;
@@ -546,13 +593,13 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
 }  // namespace
 
 int prep_queries(const float* q_dev, int nq, int d, int nq_pad, int kp, int na, bool bf16, void* A, float* qn,
-                 uint32_t* tau, cudaStream_t stream) {
+                 uint32_t* tau, cudaStream_t stream, int mixed_slice) {
     const int wpb = 8;
     const int blocks = (nq_pad + wpb - 1) / wpb;
     if (bf16)
-        prep_queries_kernel<0><<<blocks, wpb * 32, 0, stream>>>(q_dev, nq, d, nq_pad, kp, na, A, qn, tau);
+        prep_queries_kernel<0><<<blocks, wpb * 32, 0, stream>>>(q_dev, nq, d, nq_pad, kp, na, A, qn, tau, 0);
     else
-        prep_queries_kernel<1><<<blocks, wpb * 32, 0, stream>>>(q_dev, nq, d, nq_pad, kp, na, A, qn, tau);
+        prep_queries_kernel<1><<<blocks, wpb * 32, 0, stream>>>(q_dev, nq, d, nq_pad, kp, na, A, qn, tau, mixed_slice);
     B2_AFTER_LAUNCH();
     return B2_OK;
 }
@@ -621,6 +668,8 @@ int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtyp
     p.num_stages = stages;
     p.trunc_hi = 1;  // measured on B200: identical accuracy to rounding in place (recall_check), one smem write less
     if (const char* e = getenv("B2_GEMM_TRUNC")) p.trunc_hi = atoi(e) ? 1 : 0;
+    p.mixed = (!bf16 && na == 2) ? 1 : 0;
+    if (const char* e = getenv("B2_GEMM_MIXED")) p.mixed = (!bf16 && na == 2 && atoi(e)) ? 1 : 0;
 
     // scratch: [A parts][qn][tau][partial][candidate logs]
     auto al = [](size_t v) { return (v + 1023) / 1024 * 1024; };
@@ -641,7 +690,7 @@ int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtyp
     CUtensorMap tmA, tmB;
     rc = make_map(&tmA, bf16, swb, A, (uint64_t)kp, (uint64_t)na * p.nq_pad, kbytes, kTileM);
     if (rc == B2_OK) rc = make_map(&tmB, bf16, swb, rows, (uint64_t)(pitch_bytes / elem), (uint64_t)n, pitch_bytes, kTileN);
-    if (rc == B2_OK) rc = prep_queries(q_dev, (int)nq, d, p.nq_pad, kp, na, bf16, A, qn, p.tau, stream);
+    if (rc == B2_OK) rc = prep_queries(q_dev, (int)nq, d, p.nq_pad, kp, na, bf16, A, qn, p.tau, stream, p.mixed ? swb / 4 : 0);
     if (rc == B2_OK) {
         const int variant = (bf16 ? 0 : 4) + (na == 2 ? 2 : 0) + (swb == 128 ? 1 : 0);
         switch (variant) {

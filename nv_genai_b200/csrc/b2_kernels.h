@@ -58,8 +58,10 @@ int merge_shards_wait(int metric, int nq, int k, int nparts, const char* blocks,
 // Tensor-core search for batches of >= 20 queries (faiss's BLAS threshold), k <= 128.
 // q [nq][d] fp32 -> A [na][nq_pad][kp] operand parts (bf16 hi/lo, or fp32 words holding tf32 hi/lo), zero padded;
 // optional qn[row] = |q|^2 and tau[row] = initial admission bound.
+// mixed_slice > 0 (fp32 operands only): part 1 becomes the bf16 correction operand, per mixed_slice-element K slice
+// [bf16(q) | bf16(q - tf32(q))] (same bytes per row).
 int prep_queries(const float* q_dev, int nq, int d, int nq_pad, int kp, int na, bool bf16, void* A, float* qn,
-                 uint32_t* tau, cudaStream_t stream);
+                 uint32_t* tau, cudaStream_t stream, int mixed_slice = 0);
 bool gemm_path_supported(int64_t n, int d, int dtype, int k, int64_t nq);
 int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* norms,
                 const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream,

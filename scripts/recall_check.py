@@ -52,7 +52,7 @@ def main():
 
     Dx, Ix = run(f32, B2_NO_TENSOR="1")
     out = {"rows": a.rows, "nq": a.nq, "k": a.k}
-    for name, idx, env in (("f32_tensor_rna", f32, {}), ("f32_tensor_trunc", f32, {"B2_GEMM_TRUNC": "1"}),
+    for name, idx, env in (("f32_tensor_default", f32, {}), ("f32_tensor_3xtf32", f32, {"B2_GEMM_MIXED": "0"}),
                            ("bf16_scan", b16, {"B2_NO_TENSOR": "1"}), ("bf16_tensor_2parts", b16, {}),
                            ("bf16_tensor_1part", b16, {"B2_GEMM_QUERY_PARTS": "1"})):
         D, I = run(idx, **env)

@@ -78,7 +78,7 @@ def run_one(a, idx, q, torch):
     maxrel = float(((Ds - D[s]).abs() / Ds.abs().clamp_min(1e-6)).max().item())
     print(json.dumps({"rows": a.rows, "dim": a.dim, "nq": a.nq, "k": a.k, "dtype": a.dtype, "metric": a.metric,
                       "ms": ms, "all_ms": times, "qps": a.nq / (ms * 1e-3), "useful_tflops": useful,
-                      "mma_tflops": mma, "products": products, "swizzle": os.environ.get("B2_GEMM_SWIZZLE", "auto"), "ids_equal_scan_sample": same,
+                      "mma_tflops": mma, "products": products, "swizzle": os.environ.get("B2_GEMM_SWIZZLE", "auto"), "mixed": os.environ.get("B2_GEMM_MIXED", "default"), "ids_equal_scan_sample": same,
                       "max_rel_score_diff_vs_scan": maxrel}), flush=True)
 
 
