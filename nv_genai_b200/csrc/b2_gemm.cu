@@ -47,6 +47,8 @@
 //
 // Algorithmic work per launch: 2 * nq_pad * ntotal * K flop per product (x2 bf16, x3 fp32);
 // corpus bytes ntotal * pitch read ~once from HBM, query tile re-read from L2 per corpus tile.
+#include <cstring>
+
 #include "b2_kernels.h"
 #include "b2_tc.cuh"
 
@@ -175,13 +177,19 @@ __device__ __forceinline__ void compact_log(uint64_t* __restrict__ log, int& cnt
 // ------------------------------------------------------------------ the kernel
 // KIND 0: bf16 rows, kind::f16.  KIND 1: fp32 rows, kind::tf32 (3xTF32).  NA: query parts (1 = hi only, 2 = hi + lo).
 // SWB: bytes of K per pipeline stage = the shared-memory swizzle width (64 or 128).
-template <int KIND, int NA, int SWB>
+// CG: CTAs per MMA (tcgen05 cta_group).  CG = 2 launches clusters of two CTAs on the two SMs of a TPC: the pair
+// computes a 256-query x 256-row tile with ONE M = 256 instruction stream issued by the leader CTA; each CTA holds its
+// own 128 queries (A), HALF of the corpus tile (B, 128 rows) and its own 128 TMEM lanes of the accumulators.  Per CTA
+// that halves the B bytes pulled from L2, the transform work and the shared-memory traffic of the MMAs (the fp32 path
+// was shared-memory-bandwidth-bound with one CTA per MMA) and makes room for more pipeline stages.
+template <int KIND, int NA, int SWB, int CG>
 __global__ void __launch_bounds__(KIND == 1 ? kThreadsFp32 : kThreadsBf16, 1)
 gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
     constexpr int ELEM = (KIND == 0) ? 2 : 4;
     constexpr int kSwizzleBytes = SWB;
     constexpr int kAPartBytes = kTileM * SWB;
-    constexpr int kBTileBytes = kTileN * SWB;
+    constexpr int kBRows = kTileN / CG;                   // corpus rows of the tile held by this CTA
+    constexpr int kBTileBytes = kBRows * SWB;
     constexpr int KSLICE = kSwizzleBytes / ELEM;          // elements per stage along K
     constexpr int STAGE_BYTES = NA * kAPartBytes + kBTileBytes + (KIND == 1 ? kBTileBytes : 0);
     constexpr uint32_t STAGE_TX = NA * kAPartBytes + kBTileBytes;
@@ -191,9 +199,11 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // instruction descriptor: D fp32, A/B bf16 or tf32, both K-major, N = 256, M = 128
     constexpr uint32_t FMT = (KIND == 0) ? 1u : 2u;
     constexpr uint32_t IDESC = (1u << 4) | (FMT << 7) | (FMT << 10) | ((uint32_t)(kTileN >> 3) << 17) |
-                               ((uint32_t)(kTileM >> 4) << 24);
+                               ((uint32_t)((kTileM * CG) >> 4) << 24);
     constexpr uint32_t IDESC_BF16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kTileN >> 3) << 17) |
-                                    ((uint32_t)(kTileM >> 4) << 24);
+                                    ((uint32_t)((kTileM * CG) >> 4) << 24);
+    // bf16 rows, CG = 2: both CTAs' TMA loads complete on the LEADER's full barrier (no transform stage in between)
+    constexpr bool PAIR_FULL = (CG == 2 && KIND == 0);
 
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
@@ -212,27 +222,37 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t cta_rank = (CG == 2) ? cluster_ctarank() : 0u;  // 0 = leader (issues the MMAs)
+    const int unit = blockIdx.x / CG, n_units = gridDim.x / CG;    // a unit = one CTA, or one CTA pair
 
     if (tid == 0) {
         for (int s = 0; s < S; ++s) {
             mbar_init(smem_u32(full_bar + s), 1);
             mbar_init(smem_u32(empty_bar + s), 1);
-            mbar_init(smem_u32(xf_bar + s), kXfThreads / 32);
+            mbar_init(smem_u32(xf_bar + s), CG * (kXfThreads / 32));
         }
         for (int b = 0; b < 2; ++b) {  // fp32 rows use only buffer 0
             mbar_init(smem_u32(tfull_bar + b), 1);
-            mbar_init(smem_u32(tempty_bar + b), 4);
+            mbar_init(smem_u32(tempty_bar + b), CG * 4);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 5) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                     "r"(512u)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if (CG == 2) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                         "r"(512u)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                         "r"(512u)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tcgen05_fence_before();
     __syncthreads();
+    if (CG == 2) cluster_sync_all();  // the peer's barriers are initialised before anything is signalled across
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -240,8 +260,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // ================= TMA producer (whole warp loops, one elected lane issues; see tc::elect_one)
         int stage = 0;
         uint32_t phase = 0;
-        for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
-            const int qt = item % p.n_qt, seg = item / p.n_qt;
+        for (int item = unit; item < p.n_items; item += n_units) {
+            const int qt = (item % p.n_qt) * CG + (int)cta_rank, seg = item / p.n_qt;
             const int t0 = seg * p.tiles_per_seg;
             const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
             for (int t = t0; t < t1; ++t) {
@@ -249,12 +269,21 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     mbar_wait(smem_u32(empty_bar + stage), phase ^ 1u);
                     if (elect_one()) {
                         const uint32_t fb = smem_u32(full_bar + stage);
-                        mbar_expect_tx(fb, STAGE_TX);
                         const uint32_t sb = smem_u32(stages + (size_t)stage * STAGE_BYTES);
                         const int x = ks * KSLICE;
-                        tma_load_2d(sb, &tmA, x, qt * kTileM, fb);
-                        if (NA == 2) tma_load_2d(sb + kAPartBytes, &tmA, x, p.nq_pad + qt * kTileM, fb);
-                        tma_load_2d(sb + B_OFF, &tmB, x, t * kTileN, fb);
+                        const int brow = t * kTileN + (int)cta_rank * kBRows;
+                        if (PAIR_FULL) {
+                            const uint32_t lfb = map_to_cta(fb, 0);  // the leader's barrier counts both CTAs' bytes
+                            if (cta_rank == 0) mbar_expect_tx(fb, 2 * STAGE_TX);
+                            tma_load_2d_pair(sb, &tmA, x, qt * kTileM, lfb);
+                            if (NA == 2) tma_load_2d_pair(sb + kAPartBytes, &tmA, x, p.nq_pad + qt * kTileM, lfb);
+                            tma_load_2d_pair(sb + B_OFF, &tmB, x, brow, lfb);
+                        } else {
+                            mbar_expect_tx(fb, STAGE_TX);
+                            tma_load_2d(sb, &tmA, x, qt * kTileM, fb);
+                            if (NA == 2) tma_load_2d(sb + kAPartBytes, &tmA, x, p.nq_pad + qt * kTileM, fb);
+                            tma_load_2d(sb + B_OFF, &tmB, x, brow, fb);
+                        }
                     }
                     __syncwarp();
                     if (++stage == S) {
@@ -265,11 +294,11 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
         }
     } else if (warp == 5) {
-        // ================= MMA issuer (whole warp loops, one elected lane issues)
+        // ================= MMA issuer (whole warp loops, one elected lane issues; CG = 2: the leader CTA only)
         int stage = 0;
         uint32_t phase = 0;
         uint32_t tc = 0;
-        for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+        for (int item = unit; cta_rank == 0 && item < p.n_items; item += n_units) {
             const int seg = item / p.n_qt;
             const int t0 = seg * p.tiles_per_seg;
             const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
@@ -292,6 +321,18 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         for (int j = 0; j < kSwizzleBytes / 32; ++j) {
                             const uint32_t acc = (ks | j) ? 1u : 0u;
                             const uint64_t dj = (uint64_t)(j * 2);  // +32 bytes in the descriptor's address field
+                            if (CG == 2) {
+                                umma_pair<KIND>(d_tmem, a_hi0 + dj, b_hi0 + dj, IDESC, acc);
+                                if (KIND == 0) {
+                                    if (NA == 2) umma_pair<KIND>(d_tmem, a_lo0 + dj, b_hi0 + dj, IDESC, 1u);
+                                } else if (p.mixed) {
+                                    if (NA == 2) umma_pair<0>(c_tmem, a_lo0 + dj, b_lo0 + dj, IDESC_BF16, acc);
+                                } else {
+                                    umma_pair<KIND>(c_tmem, a_hi0 + dj, b_lo0 + dj, IDESC, acc);
+                                    if (NA == 2) umma_pair<KIND>(c_tmem, a_lo0 + dj, b_hi0 + dj, IDESC, 1u);
+                                }
+                                continue;
+                            }
                             umma<KIND>(d_tmem, a_hi0 + dj, b_hi0 + dj, IDESC, acc);
                             if (KIND == 0) {
                                 if (NA == 2) umma<KIND>(d_tmem, a_lo0 + dj, b_hi0 + dj, IDESC, 1u);
@@ -303,7 +344,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                 if (NA == 2) umma<KIND>(c_tmem, a_lo0 + dj, b_hi0 + dj, IDESC, 1u);
                             }
                         }
-                        tcgen05_commit(smem_u32(empty_bar + stage));
+                        if (CG == 2) tcgen05_commit_pair(smem_u32(empty_bar + stage));
+                        else tcgen05_commit(smem_u32(empty_bar + stage));
                     }
                     __syncwarp();
                     if (++stage == S) {
@@ -311,7 +353,10 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         phase ^= 1u;
                     }
                 }
-                if (elect_one()) tcgen05_commit(smem_u32(tfull_bar + buf));
+                if (elect_one()) {
+                    if (CG == 2) tcgen05_commit_pair(smem_u32(tfull_bar + buf));
+                    else tcgen05_commit(smem_u32(tfull_bar + buf));
+                }
                 __syncwarp();
             }
         }
@@ -321,7 +366,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int xt = tid - 192;  // 0..kXfThreads-1
             int stage = 0;
             uint32_t phase = 0;
-            for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+            for (int item = unit; item < p.n_items; item += n_units) {
                 const int seg = item / p.n_qt;
                 const int t0 = seg * p.tiles_per_seg;
                 const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
@@ -335,7 +380,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             // in the same swizzled K-major layout (16-byte chunk index XOR a row-dependent mask)
                             constexpr int ITEMS_PER_ROW = SWB / 32;  // 8 floats in, one lo chunk + one hi chunk out
 #pragma unroll
-                            for (int i = 0; i < kTileN * ITEMS_PER_ROW / kXfThreads; ++i) {
+                            for (int i = 0; i < kBRows * ITEMS_PER_ROW / kXfThreads; ++i) {
                                 const int w = i * kXfThreads + xt;
                                 const int r = w / ITEMS_PER_ROW, g = w % ITEMS_PER_ROW;
                                 const int sw = (SWB == 128) ? (r & 7) : ((r >> 1) & 3);
@@ -386,7 +431,10 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         }
                         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                         __syncwarp();
-                        if (lane == 0) mbar_arrive(smem_u32(xf_bar + stage));
+                        if (lane == 0) {
+                            if (CG == 2) mbar_arrive_cluster(map_to_cta(smem_u32(xf_bar + stage), 0));  // the leader waits
+                            else mbar_arrive(smem_u32(xf_bar + stage));
+                        }
                         if (++stage == S) {
                             stage = 0;
                             phase ^= 1u;
@@ -404,8 +452,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint64_t* log = p.cand + (size_t)blockIdx.x * kCandCap * kEpiThreads + ql;
         const bool l2 = p.metric == B2_METRIC_L2;
         uint32_t tc = 0;
-        for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
-            const int qt = item % p.n_qt, seg = item / p.n_qt;
+        for (int item = unit; item < p.n_items; item += n_units) {
+            const int qt = (item % p.n_qt) * CG + (int)cta_rank, seg = item / p.n_qt;
             const int t0 = seg * p.tiles_per_seg;
             const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
             const int q = qt * kTileM + ql;
@@ -490,7 +538,10 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
                 tcgen05_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(smem_u32(tempty_bar + buf));
+                if (lane == 0) {
+                    if (CG == 2) mbar_arrive_cluster(map_to_cta(smem_u32(tempty_bar + buf), 0));  // the leader's MMA waits
+                    else mbar_arrive(smem_u32(tempty_bar + buf));
+                }
             }
             // ---- item done: emit this query's k best of the segment, publish the bound
             const float tau = keys_w[(size_t)lane * k + (k - 1)];
@@ -515,9 +566,13 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
     tcgen05_fence_before();
     __syncthreads();
+    if (CG == 2) cluster_sync_all();  // neither CTA may leave (or free TMEM) while its peer can still signal it
     if (warp == 5) {
         tcgen05_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+        if (CG == 2)
+            asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+        else
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
     }
 }
 
@@ -563,15 +618,15 @@ __global__ void prep_queries_kernel(const float* __restrict__ q, int nq, int d, 
     }
 }
 
-size_t gemm_smem_bytes(bool fp32_rows, int na, int swb, int stages, int k) {
-    const size_t stage = (size_t)na * kTileM * swb + (size_t)kTileN * swb * (fp32_rows ? 2 : 1);
+size_t gemm_smem_bytes(bool fp32_rows, int na, int swb, int stages, int k, int cg = 1) {
+    const size_t stage = (size_t)na * kTileM * swb + (size_t)(kTileN / cg) * swb * (fp32_rows ? 2 : 1);
     return 1024 + stages * stage + (size_t)k * kEpiThreads * 4 + 2 * kTileN * 4 + (3 * kMaxStages + 4) * 8 + 16;
 }
 
-template <int KIND, int NA, int SWB>
+template <int KIND, int NA, int SWB, int CG>
 int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int grid, size_t smem,
                 cudaStream_t stream) {
-    auto kern = gemm_topk_kernel<KIND, NA, SWB>;
+    auto kern = gemm_topk_kernel<KIND, NA, SWB, CG>;
     static std::mutex mu;
     static size_t attr[64] = {0};
     int dev = 0;
@@ -584,6 +639,30 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
         }
     }
     void* tok = prof_begin(stream);
+    if (CG == 2) {
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3((unsigned)grid);
+        cfg.blockDim = dim3(KIND == 1 ? kThreadsFp32 : kThreadsBf16);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, p);
+        prof_end(tok, 1, stream);
+        B2_COUNT_LAUNCH();
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            set_error("cluster launch of the tensor-core kernel failed: %s", cudaGetErrorString(e));
+            return B2_ERR_CUDA;
+        }
+        return B2_OK;
+    }
     kern<<<grid, KIND == 1 ? kThreadsFp32 : kThreadsBf16, smem, stream>>>(tmA, tmB, p);
     prof_end(tok, 1, stream);
     B2_AFTER_LAUNCH();
@@ -617,26 +696,32 @@ int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtyp
     const int elem = bf16 ? 2 : 4;
     int na = 2;
     if (const char* e = getenv("B2_GEMM_QUERY_PARTS")) na = (atoi(e) == 1) ? 1 : 2;
+    // CTA pairs (cta_group::2) for bf16 rows when the SM count is even.  Measured at 10M x 1024, nq = 4096, k = 100:
+    // bf16 rows 132.7 ms with pairs vs 141.0 ms without; fp32 rows 536 ms with pairs vs 388 ms without (every K slice
+    // then needs 16 cluster-scope arrivals from the two CTAs' transform warps before the leader may issue), so fp32
+    // rows keep one CTA per MMA.  B2_GEMM_CTA_GROUP overrides.
+    int cg = (bf16 && num_sms % 2 == 0) ? 2 : 1;
+    if (const char* e = getenv("B2_GEMM_CTA_GROUP")) cg = (atoi(e) == 2 && num_sms % 2 == 0) ? 2 : 1;
     // stage width: 128-byte swizzle when at least three stages of it fit beside the k-slot heaps, else 64
-    int swb = (gemm_smem_bytes(!bf16, na, 128, 3, k) <= 227 * 1024) ? 128 : 64;
+    int swb = (gemm_smem_bytes(!bf16, na, 128, 3, k, cg) <= 227 * 1024) ? 128 : 64;
     if (const char* e = getenv("B2_GEMM_SWIZZLE")) swb = (atoi(e) == 128) ? 128 : 64;  // tuning override
-    if (swb == 128 && gemm_smem_bytes(!bf16, na, 128, 2, k) > 227 * 1024) swb = 64;
+    if (swb == 128 && gemm_smem_bytes(!bf16, na, 128, 2, k, cg) > 227 * 1024) swb = 64;
     const size_t kbytes = (((size_t)d * elem + swb - 1) / swb) * swb;
     const int kp = (int)(kbytes / elem);
 
     GemmParams p;
     p.nq = (int)nq;
-    p.nq_pad = (int)((nq + kTileM - 1) / kTileM) * kTileM;
+    p.nq_pad = (int)((nq + kTileM * cg - 1) / (kTileM * cg)) * kTileM * cg;
     p.n = (uint32_t)n;
     p.k = k;
     p.kstages = (int)(kbytes / swb);
     p.metric = metric;
-    p.n_qt = p.nq_pad / kTileM;
+    p.n_qt = p.nq_pad / (kTileM * cg);  // query-tile groups: one per CTA, or per CTA pair
     p.n_tiles = (int)((n + kTileN - 1) / kTileN);
     p.norms = norms;
 
     // segments: make (query tiles x segments) a near multiple of the CTA count, segments >= 8 tiles
-    const int grid_max = num_sms;
+    const int grid_max = num_sms / cg;  // units that run at once: CTAs, or CTA pairs
     int best_s = 1;
     double best_cost = 1e30;
     const int max_s = std::max(1, std::min(p.n_tiles / 8, 4 * grid_max));
@@ -655,12 +740,12 @@ int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtyp
     p.tiles_per_seg = (p.n_tiles + best_s - 1) / best_s;
     p.n_seg = (p.n_tiles + p.tiles_per_seg - 1) / p.tiles_per_seg;
     p.n_items = p.n_qt * p.n_seg;
-    const int grid = (int)std::min<long long>(grid_max, p.n_items);
+    const int grid = (int)std::min<long long>(grid_max, p.n_items) * cg;
 
     // pipeline depth from the shared-memory budget
     int stages = kMaxStages;
-    while (stages > 2 && gemm_smem_bytes(!bf16, na, swb, stages, k) > 227 * 1024) --stages;
-    const size_t smem = gemm_smem_bytes(!bf16, na, swb, stages, k);
+    while (stages > 2 && gemm_smem_bytes(!bf16, na, swb, stages, k, cg) > 227 * 1024) --stages;
+    const size_t smem = gemm_smem_bytes(!bf16, na, swb, stages, k, cg);
     if (smem > 227 * 1024) {
         set_error("tensor-core search: k=%d does not fit shared memory", k);
         return B2_ERR_UNSUPPORTED;
@@ -689,19 +774,27 @@ int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtyp
     int rc = B2_OK;
     CUtensorMap tmA, tmB;
     rc = make_map(&tmA, bf16, swb, A, (uint64_t)kp, (uint64_t)na * p.nq_pad, kbytes, kTileM);
-    if (rc == B2_OK) rc = make_map(&tmB, bf16, swb, rows, (uint64_t)(pitch_bytes / elem), (uint64_t)n, pitch_bytes, kTileN);
+    if (rc == B2_OK) rc = make_map(&tmB, bf16, swb, rows, (uint64_t)(pitch_bytes / elem), (uint64_t)n, pitch_bytes, kTileN / cg);
     if (rc == B2_OK) rc = prep_queries(q_dev, (int)nq, d, p.nq_pad, kp, na, bf16, A, qn, p.tau, stream, p.mixed ? swb / 4 : 0);
     if (rc == B2_OK) {
-        const int variant = (bf16 ? 0 : 4) + (na == 2 ? 2 : 0) + (swb == 128 ? 1 : 0);
+        const int variant = (cg == 2 ? 8 : 0) + (bf16 ? 0 : 4) + (na == 2 ? 2 : 0) + (swb == 128 ? 1 : 0);
         switch (variant) {
-            case 0: rc = launch_gemm<0, 1, 64>(tmA, tmB, p, grid, smem, stream); break;
-            case 1: rc = launch_gemm<0, 1, 128>(tmA, tmB, p, grid, smem, stream); break;
-            case 2: rc = launch_gemm<0, 2, 64>(tmA, tmB, p, grid, smem, stream); break;
-            case 3: rc = launch_gemm<0, 2, 128>(tmA, tmB, p, grid, smem, stream); break;
-            case 4: rc = launch_gemm<1, 1, 64>(tmA, tmB, p, grid, smem, stream); break;
-            case 5: rc = launch_gemm<1, 1, 128>(tmA, tmB, p, grid, smem, stream); break;
-            case 6: rc = launch_gemm<1, 2, 64>(tmA, tmB, p, grid, smem, stream); break;
-            default: rc = launch_gemm<1, 2, 128>(tmA, tmB, p, grid, smem, stream); break;
+            case 0: rc = launch_gemm<0, 1, 64, 1>(tmA, tmB, p, grid, smem, stream); break;
+            case 1: rc = launch_gemm<0, 1, 128, 1>(tmA, tmB, p, grid, smem, stream); break;
+            case 2: rc = launch_gemm<0, 2, 64, 1>(tmA, tmB, p, grid, smem, stream); break;
+            case 3: rc = launch_gemm<0, 2, 128, 1>(tmA, tmB, p, grid, smem, stream); break;
+            case 4: rc = launch_gemm<1, 1, 64, 1>(tmA, tmB, p, grid, smem, stream); break;
+            case 5: rc = launch_gemm<1, 1, 128, 1>(tmA, tmB, p, grid, smem, stream); break;
+            case 6: rc = launch_gemm<1, 2, 64, 1>(tmA, tmB, p, grid, smem, stream); break;
+            case 7: rc = launch_gemm<1, 2, 128, 1>(tmA, tmB, p, grid, smem, stream); break;
+            case 8: rc = launch_gemm<0, 1, 64, 2>(tmA, tmB, p, grid, smem, stream); break;
+            case 9: rc = launch_gemm<0, 1, 128, 2>(tmA, tmB, p, grid, smem, stream); break;
+            case 10: rc = launch_gemm<0, 2, 64, 2>(tmA, tmB, p, grid, smem, stream); break;
+            case 11: rc = launch_gemm<0, 2, 128, 2>(tmA, tmB, p, grid, smem, stream); break;
+            case 12: rc = launch_gemm<1, 1, 64, 2>(tmA, tmB, p, grid, smem, stream); break;
+            case 13: rc = launch_gemm<1, 1, 128, 2>(tmA, tmB, p, grid, smem, stream); break;
+            case 14: rc = launch_gemm<1, 2, 64, 2>(tmA, tmB, p, grid, smem, stream); break;
+            default: rc = launch_gemm<1, 2, 128, 2>(tmA, tmB, p, grid, smem, stream); break;
         }
     }
     if (rc == B2_OK)

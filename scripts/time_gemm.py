@@ -44,6 +44,9 @@ def main():
     combos = [c.split(":") for c in a.sweep.split(",") if c] or [[str(a.k), "", ""]]
     for kk, sw, parts in combos:
         a.k = int(kk)
+        extra = {}
+        if ":" in parts:  # parts may carry more overrides: parts:cg:mixed
+            parts, *rest = parts.split(":")
         for name, val in (("B2_GEMM_SWIZZLE", sw), ("B2_GEMM_QUERY_PARTS", parts)):
             if val:
                 os.environ[name] = val
@@ -78,7 +81,7 @@ def run_one(a, idx, q, torch):
     maxrel = float(((Ds - D[s]).abs() / Ds.abs().clamp_min(1e-6)).max().item())
     print(json.dumps({"rows": a.rows, "dim": a.dim, "nq": a.nq, "k": a.k, "dtype": a.dtype, "metric": a.metric,
                       "ms": ms, "all_ms": times, "qps": a.nq / (ms * 1e-3), "useful_tflops": useful,
-                      "mma_tflops": mma, "products": products, "swizzle": os.environ.get("B2_GEMM_SWIZZLE", "auto"), "mixed": os.environ.get("B2_GEMM_MIXED", "default"), "ids_equal_scan_sample": same,
+                      "mma_tflops": mma, "products": products, "swizzle": os.environ.get("B2_GEMM_SWIZZLE", "auto"), "mixed": os.environ.get("B2_GEMM_MIXED", "default"), "cta_group": os.environ.get("B2_GEMM_CTA_GROUP", "default"), "ids_equal_scan_sample": same,
                       "max_rel_score_diff_vs_scan": maxrel}), flush=True)
 
 
