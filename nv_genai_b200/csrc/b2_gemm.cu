@@ -10,32 +10,34 @@
 // Like faiss's BLAS path, L2 is |q|^2 + |x|^2 - 2 q.x clamped at 0 (the |x|^2 come from the
 // ingest kernel's side array), IP is the plain dot product.
 //
-// Mapping (one persistent CTA per SM, warp-specialised):
-//   M = 128 queries (TMEM lanes), N = 256 corpus rows (TMEM columns), K = the row, streamed
-//   in 64-byte slices.  Both operands are K-major, 64-byte swizzled, brought in by TMA:
-//     A = the query tile, pre-split by prep_queries_kernel into hi + lo parts
-//         (bf16 store: bf16 hi/lo, so q is carried to ~16 mantissa bits;
-//          fp32 store: tf32 hi/lo for the 3xTF32 scheme),
-//     B = corpus rows straight from the row store (bf16), or fp32 rows of which four transform
-//         warps write the tf32 remainder lo = x - trunc_tf32(x) into a second buffer (the tensor
-//         core ignores the low 13 mantissa bits of a tf32 operand, so the raw tile is the hi part).
-//         (A separate 2-slot ring for the remainder tiles, to deepen the TMA pipeline, was tried and
-//         was slower: 460 vs 424 ms at 10M x 1024, nq = 4096 - the transform then trails the MMA.)
-//   MMAs per K slice: bf16  D += A_hi.B + A_lo.B            (kind::f16,  2 products)
-//                     fp32  D += A_hi.B_hi + A_lo.B_hi + A_hi.B_lo   (kind::tf32, 3xTF32)
-//   The tensor core adds each product into the fp32 accumulator with truncation, a bias that
-//   grows with the number of accumulation steps (measured: -1e-5 relative at d = 1536 with all
-//   three 3xTF32 products in one accumulator).  The fp32 path therefore keeps TWO accumulators
-//   per tile in TMEM: columns [0,256) take A_hi.B_hi, columns [256,512) take the two small
-//   correction products (2^-11 of the main term, so their truncation is negligible); the
-//   epilogue adds them in fp32 registers.  That uses all 512 TMEM columns, so the fp32 path is
-//   single-buffered (tile time ~49k cycles vs ~2k for the read-out); the bf16 path (2 x 256
-//   columns) is double-buffered: while the MMA warp fills one accumulator, the four epilogue
-//   warps read the other with tcgen05.ld (one thread = one query = one TMEM lane).
-//   The epilogue compares every score with the thread's running threshold and pushes the few survivors
-//   into (a) the query's sorted list of its k best keys in shared memory (warp-cooperative
-//   insertion; slot k-1 is the exact running k-th best = the threshold), and (b) a candidate
-//   log in global memory.
+// Mapping (one persistent CTA per SM, warp-specialised: TMA producer warp, MMA issuer warp, four
+// epilogue warps, and for fp32 rows eight transform warps):
+//   M = 128 queries per CTA (TMEM lanes), N = 256 corpus rows (TMEM columns), K = the row,
+//   streamed in 64- or 128-byte slices.  Both operands are K-major, swizzled, brought in by TMA:
+//     A = the query tile, prepared by prep_queries_kernel,
+//     B = corpus rows straight from the row store.
+//   bf16 rows (kind::f16, 2 products):  D += q_hi.x + q_lo.x with q split into bf16 hi + lo, so q is
+//     carried to ~16 mantissa bits and the scores are exact with respect to the stored rows.  CTAs run
+//     as PAIRS (cta_group::2): one M = 256 instruction stream issued by the leader CTA, each CTA holds
+//     its 128 queries, half of the corpus tile and its own 128 TMEM lanes (see the kernel comment).
+//     Accumulators are double-buffered in TMEM (2 x 256 columns).
+//   fp32 rows (fp32-faithful, "3xTF32" with the corrections moved to the bf16 pipe):
+//     main  D1 += x_hi.q_hi   kind::tf32; the raw fp32 tile IS x_hi (the tensor core ignores the low
+//                             13 mantissa bits of a tf32 operand), q_hi = tf32(q);
+//     corr  D2 += [x_lo | x_hi] . [q_hi | q_lo]   ONE kind::f16 MMA over a doubled K: eight transform
+//                             warps write, per K slice and row, bf16(x - trunc_tf32(x)) | bf16(x) in the
+//                             same swizzled layout; the correction terms are 2^-11 of the main term, so
+//                             bf16 operands cost 2^-20 relative.  (Plain 3xTF32, B2_GEMM_MIXED=0: 422 ms
+//                             vs 388 ms; a separate ring for the remainder tiles was slower still.)
+//     The tensor core adds each product into the fp32 accumulator with truncation, a bias that grows
+//     with the number of accumulation steps (measured: -1e-5 relative at d = 1536 with all three
+//     products in one accumulator), hence the separate accumulators: columns [0,256) main, [256,512)
+//     corrections, added in fp32 registers by the epilogue.  That uses all 512 TMEM columns, so the
+//     fp32 path is single-buffered (tile time ~33k cycles vs ~2k for the read-out).
+//   Epilogue: tcgen05.ld, one thread = one query = one TMEM lane; every score is compared with the
+//   thread's running threshold and the few survivors are pushed into (a) the query's sorted list of its
+//   k best keys in shared memory (warp-cooperative insertion; slot k-1 is the exact running k-th best =
+//   the threshold), and (b) a candidate log in global memory.
 //   Work item = (query tile, corpus segment); items are dealt round-robin to the CTAs with the
 //   query tile varying fastest, so the CTAs that run at the same time read the same corpus
 //   segment and the corpus is streamed from HBM about once.  A finished item publishes its
