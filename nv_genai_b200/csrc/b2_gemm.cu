@@ -28,7 +28,9 @@
 //                             warps write, per K slice and row, bf16(x - trunc_tf32(x)) | bf16(x) in the
 //                             same swizzled layout; the correction terms are 2^-11 of the main term, so
 //                             bf16 operands cost 2^-20 relative.  (Plain 3xTF32, B2_GEMM_MIXED=0: 422 ms
-//                             vs 388 ms; a separate ring for the remainder tiles was slower still.)
+//                             vs 388 ms.)  The correction tiles live in their own 2-slot ring, so a TMA
+//                             stage is only raw A + raw B and one more stage fits: the fp32 path is bound
+//                             by the depth of the TMA pipeline, not by the tensor pipe.
 //     The tensor core adds each product into the fp32 accumulator with truncation, a bias that grows
 //     with the number of accumulation steps (measured: -1e-5 relative at d = 1536 with all three
 //     products in one accumulator), hence the separate accumulators: columns [0,256) main, [256,512)
@@ -63,6 +65,7 @@ namespace {
 constexpr int kTileM = 128;                        // queries per tile
 constexpr int kTileN = 256;                        // corpus rows per tile
 constexpr int kMaxStages = 8;
+constexpr int kMaxCorrSlots = 4;                   // fp32 rows: ring of correction-operand tiles, decoupled from the TMA stages
 constexpr int kCandCap = 1024;                     // candidate log entries per query per CTA
 constexpr int kGemmMaxK = 128;                     // heap slots per query (k <= 128 on this path)
 constexpr int kEpiThreads = 128;
@@ -77,6 +80,7 @@ struct GemmParams {
     int metric;
     int n_qt, n_seg, tiles_per_seg, n_tiles, n_items;
     int num_stages;
+    int corr_slots;     // fp32 rows: correction tiles in the ring (2..4)
     int trunc_hi;       // fp32 rows: 1 = leave the raw tile as the hi operand (hardware truncation), 0 = round it in place
     int mixed;          // fp32 rows: 1 = correction products on the bf16 pipe (see kernel comment), 0 = plain 3xTF32
     const float* norms; // |x|^2 per stored row
@@ -193,10 +197,9 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     constexpr int kBRows = kTileN / CG;                   // corpus rows of the tile held by this CTA
     constexpr int kBTileBytes = kBRows * SWB;
     constexpr int KSLICE = kSwizzleBytes / ELEM;          // elements per stage along K
-    constexpr int STAGE_BYTES = NA * kAPartBytes + kBTileBytes + (KIND == 1 ? kBTileBytes : 0);
+    constexpr int STAGE_BYTES = NA * kAPartBytes + kBTileBytes;  // what TMA fills; fp32 rows add kCorrSlots correction tiles
     constexpr uint32_t STAGE_TX = NA * kAPartBytes + kBTileBytes;
     constexpr int B_OFF = NA * kAPartBytes;
-    constexpr int BLO_OFF = B_OFF + kBTileBytes;
     constexpr uint32_t NBUF = (KIND == 0) ? 2u : 1u;  // accumulator buffers (fp32 rows: main + correction, see above)
     // instruction descriptor: D fp32, A/B bf16 or tf32, both K-major, N = 256, M = 128
     constexpr uint32_t FMT = (KIND == 0) ? 1u : 2u;
@@ -213,7 +216,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint8_t* smem = smem_raw + pad;
     const int S = p.num_stages;
     uint8_t* stages = smem;
-    float* heap_s = reinterpret_cast<float*>(stages + (size_t)S * STAGE_BYTES);          // [128 queries][k] sorted keys
+    uint8_t* corr_tiles = stages + (size_t)S * STAGE_BYTES;                              // [kCorrSlots][B tile] (fp32 rows)
+    float* heap_s = reinterpret_cast<float*>(corr_tiles + (KIND == 1 ? p.corr_slots * kBTileBytes : 0));  // [128 queries][k] sorted keys
     float* nrm_s = heap_s + (size_t)p.k * kEpiThreads;                                    // [2][256]
     uint64_t* bars = reinterpret_cast<uint64_t*>(nrm_s + 2 * kTileN);
     uint64_t* full_bar = bars;                    // [S] TMA -> MMA / transform
@@ -221,7 +225,9 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint64_t* xf_bar = bars + 2 * kMaxStages;     // [S] transform -> MMA (fp32 rows)
     uint64_t* tfull_bar = bars + 3 * kMaxStages;  // [2] MMA -> epilogue
     uint64_t* tempty_bar = tfull_bar + 2;         // [2] epilogue -> MMA
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+    uint64_t* pxf_bar = tempty_bar + 2;           // [S] CTA pairs, fp32 rows: the peer's transform is done (leader's copy)
+    uint64_t* corr_empty_bar = pxf_bar + kMaxStages;  // [kCorrSlots] MMA -> transform (fp32 rows)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(corr_empty_bar + kMaxCorrSlots);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t cta_rank = (CG == 2) ? cluster_ctarank() : 0u;  // 0 = leader (issues the MMAs)
@@ -231,8 +237,10 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int s = 0; s < S; ++s) {
             mbar_init(smem_u32(full_bar + s), 1);
             mbar_init(smem_u32(empty_bar + s), 1);
-            mbar_init(smem_u32(xf_bar + s), CG * (kXfThreads / 32));
+            mbar_init(smem_u32(xf_bar + s), kXfThreads / 32);  // this CTA's transform warps
+            mbar_init(smem_u32(pxf_bar + s), 1);               // one forwarded arrival from the peer CTA
         }
+        for (int s = 0; s < kMaxCorrSlots; ++s) mbar_init(smem_u32(corr_empty_bar + s), 1);
         for (int b = 0; b < 2; ++b) {  // fp32 rows use only buffer 0
             mbar_init(smem_u32(tfull_bar + b), 1);
             mbar_init(smem_u32(tempty_bar + b), CG * 4);
@@ -300,6 +308,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         int stage = 0;
         uint32_t phase = 0;
         uint32_t tc = 0;
+        int cslot = 0;
         for (int item = unit; cta_rank == 0 && item < p.n_items; item += n_units) {
             const int seg = item / p.n_qt;
             const int t0 = seg * p.tiles_per_seg;
@@ -312,13 +321,14 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 const uint32_t c_tmem = tmem_base + kTileN;  // fp32 rows: correction accumulator
                 for (int ks = 0; ks < p.kstages; ++ks) {
                     mbar_wait(smem_u32((KIND == 1 ? xf_bar : full_bar) + stage), phase);
+                    if (CG == 2 && KIND == 1) mbar_wait(smem_u32(pxf_bar + stage), phase);
                     tcgen05_fence_after();
                     if (elect_one()) {
                         const uint32_t sb = smem_u32(stages + (size_t)stage * STAGE_BYTES);
                         const uint64_t a_hi0 = smem_desc<SWB>(sb);
                         const uint64_t a_lo0 = smem_desc<SWB>(sb + kAPartBytes);
                         const uint64_t b_hi0 = smem_desc<SWB>(sb + B_OFF);
-                        const uint64_t b_lo0 = smem_desc<SWB>(sb + BLO_OFF);
+                        const uint64_t b_lo0 = smem_desc<SWB>(smem_u32(corr_tiles + (size_t)cslot * kBTileBytes));
 #pragma unroll
                         for (int j = 0; j < kSwizzleBytes / 32; ++j) {
                             const uint32_t acc = (ks | j) ? 1u : 0u;
@@ -348,8 +358,13 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         }
                         if (CG == 2) tcgen05_commit_pair(smem_u32(empty_bar + stage));
                         else tcgen05_commit(smem_u32(empty_bar + stage));
+                        if (KIND == 1) {
+                            if (CG == 2) tcgen05_commit_pair(smem_u32(corr_empty_bar + cslot));
+                            else tcgen05_commit(smem_u32(corr_empty_bar + cslot));
+                        }
                     }
                     __syncwarp();
+                    if (KIND == 1 && ++cslot == p.corr_slots) cslot = 0;
                     if (++stage == S) {
                         stage = 0;
                         phase ^= 1u;
@@ -362,12 +377,37 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 __syncwarp();
             }
         }
+        // CTA pairs, fp32 rows: the peer's MMA warp has nothing to issue; it forwards "my transform warps are done with
+        // this K slice" to the leader with ONE cluster-scope arrival per slice (sixteen cluster-scope arrivals per
+        // slice, one per transform warp of both CTAs, made the paired fp32 path slower than the unpaired one)
+        if (CG == 2 && KIND == 1 && cta_rank != 0) {
+            int fstage = 0;
+            uint32_t fphase = 0;
+            for (int item = unit; item < p.n_items; item += n_units) {
+                const int seg = item / p.n_qt;
+                const int t0 = seg * p.tiles_per_seg;
+                const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
+                for (int t = t0; t < t1; ++t) {
+                    for (int ks = 0; ks < p.kstages; ++ks) {
+                        mbar_wait(smem_u32(xf_bar + fstage), fphase);
+                        if (elect_one()) mbar_arrive_cluster(map_to_cta(smem_u32(pxf_bar + fstage), 0));
+                        __syncwarp();
+                        if (++fstage == S) {
+                            fstage = 0;
+                            fphase ^= 1u;
+                        }
+                    }
+                }
+            }
+        }
     } else if (warp >= 6) {
         // ================= fp32 rows: split the landed B slice into tf32 hi (in place) + lo
         if (KIND == 1) {
             const int xt = tid - 192;  // 0..kXfThreads-1
             int stage = 0;
             uint32_t phase = 0;
+            int cslot = 0;
+            uint32_t cphase = 0;
             for (int item = unit; item < p.n_items; item += n_units) {
                 const int seg = item / p.n_qt;
                 const int t0 = seg * p.tiles_per_seg;
@@ -375,8 +415,9 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 for (int t = t0; t < t1; ++t) {
                     for (int ks = 0; ks < p.kstages; ++ks) {
                         mbar_wait(smem_u32(full_bar + stage), phase);
+                        mbar_wait(smem_u32(corr_empty_bar + cslot), cphase ^ 1u);
                         float4* b_hi = reinterpret_cast<float4*>(stages + (size_t)stage * STAGE_BYTES + B_OFF);
-                        float4* b_lo = reinterpret_cast<float4*>(stages + (size_t)stage * STAGE_BYTES + BLO_OFF);
+                        float4* b_lo = reinterpret_cast<float4*>(corr_tiles + (size_t)cslot * kBTileBytes);
                         if (p.mixed) {
                             // correction operand: per row, [bf16(x - trunc_tf32(x)) | bf16(x)] over this K slice, written
                             // in the same swizzled K-major layout (16-byte chunk index XOR a row-dependent mask)
@@ -433,9 +474,10 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         }
                         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                         __syncwarp();
-                        if (lane == 0) {
-                            if (CG == 2) mbar_arrive_cluster(map_to_cta(smem_u32(xf_bar + stage), 0));  // the leader waits
-                            else mbar_arrive(smem_u32(xf_bar + stage));
+                        if (lane == 0) mbar_arrive(smem_u32(xf_bar + stage));  // local; the peer's is forwarded (pxf_bar)
+                        if (++cslot == p.corr_slots) {
+                            cslot = 0;
+                            cphase ^= 1u;
                         }
                         if (++stage == S) {
                             stage = 0;
@@ -620,9 +662,11 @@ __global__ void prep_queries_kernel(const float* __restrict__ q, int nq, int d, 
     }
 }
 
-size_t gemm_smem_bytes(bool fp32_rows, int na, int swb, int stages, int k, int cg = 1) {
-    const size_t stage = (size_t)na * kTileM * swb + (size_t)(kTileN / cg) * swb * (fp32_rows ? 2 : 1);
-    return 1024 + stages * stage + (size_t)k * kEpiThreads * 4 + 2 * kTileN * 4 + (3 * kMaxStages + 4) * 8 + 16;
+size_t gemm_smem_bytes(bool fp32_rows, int na, int swb, int stages, int k, int cg = 1, int corr_slots = 2) {
+    const size_t stage = (size_t)na * kTileM * swb + (size_t)(kTileN / cg) * swb;
+    const size_t corr = fp32_rows ? (size_t)corr_slots * (kTileN / cg) * swb : 0;
+    return 1024 + stages * stage + corr + (size_t)k * kEpiThreads * 4 + 2 * kTileN * 4 +
+           (4 * kMaxStages + kMaxCorrSlots + 4) * 8 + 16;
 }
 
 template <int KIND, int NA, int SWB, int CG>
@@ -760,7 +804,26 @@ static int gemm_search_cg(const void* rows, int64_t n, size_t pitch_bytes, int d
     // pipeline depth from the shared-memory budget
     int stages = kMaxStages;
     while (stages > 2 && gemm_smem_bytes(!bf16, na, swb, stages, k, cg) > 227 * 1024) --stages;
-    const size_t smem = gemm_smem_bytes(!bf16, na, swb, stages, k, cg);
+    // fp32 rows: (TMA stages, correction tiles) from what was measured at 10M x 1024, nq = 4096: (4, 4) 352 ms,
+    // (4, 2) 366 ms, (3, 3) 398 ms, (5, 3) 420 ms - a fifth stage does not pay, a ring shorter than the stages does
+    int corr_slots = 2;
+    if (!bf16) {
+        static const int cand[5][2] = {{4, 4}, {4, 2}, {3, 3}, {3, 2}, {2, 2}};
+        for (int c = 0; c < 5; ++c) {
+            if (gemm_smem_bytes(true, na, swb, cand[c][0], k, cg, cand[c][1]) <= 227 * 1024) {
+                stages = cand[c][0];
+                corr_slots = cand[c][1];
+                break;
+            }
+        }
+        if (const char* e = getenv("B2_GEMM_CORR_SLOTS")) {
+            corr_slots = std::max(2, std::min(kMaxCorrSlots, atoi(e)));
+            stages = kMaxStages;
+            while (stages > 2 && gemm_smem_bytes(true, na, swb, stages, k, cg, corr_slots) > 227 * 1024) --stages;
+        }
+    }
+    const size_t smem = gemm_smem_bytes(!bf16, na, swb, stages, k, cg, corr_slots);
+    p.corr_slots = corr_slots;
     if (smem > 227 * 1024) {
         set_error("tensor-core search: k=%d does not fit shared memory", k);
         return B2_ERR_UNSUPPORTED;
