@@ -137,8 +137,17 @@ def measured_tensor_peak(fp32_rows):
     return peak, src
 
 
+def scan_tc_max_queries(k):
+    """Queries one tensor-core scan pass takes at this k (b2_scan_tc.cu: scan_tc_max_queries)."""
+    kpad = 32
+    while kpad < k:
+        kpad *= 2
+    return 0 if kpad > 128 else min(32, 2048 // kpad)
+
+
 def uses_tensor_path(batch, k, rows):
-    return batch >= 20 and k <= 128 and rows >= 4096
+    """True when b2_index_search sends this batch to the GEMM kernel (tensor-bound), not to a scan (HBM-bound)."""
+    return batch >= 20 and k <= 128 and rows >= 4096 and batch > scan_tc_max_queries(k)
 
 
 def ncu_traffic():
@@ -446,11 +455,12 @@ def run_b200(a):
         else:
             shard_bytes = (hi - lo) * pitch_c
             achieved = shard_bytes / (k_avg_ms * 1e-3) / 1e9 if k_n else None
-            per_step = -(-batch // 16)  # scan passes per step
+            per_step = 1 if batch <= max(16, scan_tc_max_queries(k)) else -(-batch // 16)  # scan passes per step
             roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": (achieved / peak) if achieved else None,
                     "traffic": ncu_traffic() if (batch == 1 and dtype == "float32" and world == 1) else None,
-                    "kernel": "scan_tc_kernel" if (3 if dtype == "bfloat16" else 5) <= batch <= 16 else "scan_topk_kernel",
+                    "kernel": ("scan_tc_kernel" if (3 if dtype == "bfloat16" else 5) <= batch <= max(16, scan_tc_max_queries(k))
+                               else "scan_topk_kernel"),
                     "algorithmic_bytes_per_launch": shard_bytes,
                     "avg_launch_ms": k_avg_ms, "launches_timed": k_n, "peak_source": peak_src,
                     "scan_share_of_step": (k_avg_ms * k_n / ms) if k_n else None, "scan_passes_per_step": per_step}

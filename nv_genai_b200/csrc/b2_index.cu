@@ -483,12 +483,12 @@ static int search_device(b2_index* h, int64_t nq, const float* q_dev, int k, flo
         B2_AFTER_LAUNCH();
         return B2_OK;
     }
-    if (gemm_path_supported(h->ntotal, h->d, h->dtype, k, nq))
-        return gemm_search(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, h->metric, h->norms, q_dev, nq, k,
-                           h->num_sms, D_dev, I_dev, stream, push);
     if (scan_tc_supported(h->ntotal, h->d, h->dtype, h->metric, k, nq))
         return scan_tc_search(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, q_dev, (int)nq, k, h->num_sms,
                               D_dev, I_dev, stream, push);
+    if (gemm_path_supported(h->ntotal, h->d, h->dtype, k, nq))
+        return gemm_search(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, h->metric, h->norms, q_dev, nq, k,
+                           h->num_sms, D_dev, I_dev, stream, push);
     const int kpad = next_pow2(k < 32 ? 32 : k);
     const int tmax = max_query_tile(h, kpad);
     if (tmax == 0) {

@@ -1,4 +1,5 @@
-// Small-batch exact scan on the tensor cores: 3..16 queries (fp32 rows: 5..16), inner product, one pass over the rows.
+// Small-batch exact scan on the tensor cores: 3..32 queries (fp32 rows: from 5; up to 32 queries for k <= 64,
+// 16 for k <= 128), inner product, one pass over the rows.
 //
 // Replaces faiss exhaustive_inner_product_seq + HeapResultHandler (faiss/utils/distances.cpp, the
 // nq < 20 path of IndexFlat::search), the same routine b2_scan.cu replaces, for the query counts
@@ -36,11 +37,10 @@ using namespace tc;
 namespace {
 
 constexpr int kTileRows = 128;
-constexpr int kNQ = 16;                          // queries per pass (padded)
+constexpr int kMaxNQ = 32;                       // queries per pass: 16 or 32 (padded; template parameter NQ).  A tile of 64 was
+                                                 // measured slower than the GEMM kernel (fp32 12.3 vs 11.0 ms, bf16 8.0 vs 6.3 ms)
 constexpr int kSlice = 128;                      // bytes of K per stage (swizzle width)
 constexpr int kATile = kTileRows * kSlice;       // 16 KB
-constexpr int kBTile = 2 * kNQ * kSlice;         // 4 KB: [q_hi; q_lo]
-constexpr int kStage = kATile + kBTile;          // 20 KB
 constexpr int kLoSlots = 4;                       // fp32 rows: A_lo slices resident in TMEM
 constexpr int kMaxStages = 10;
 constexpr int kEpi = 128;                        // epilogue threads
@@ -76,22 +76,26 @@ __device__ __forceinline__ void epi_bitonic_desc(uint64_t* buf, int n, int tid) 
     epi_sync();
 }
 
-// KIND 0: bf16 rows (kind::f16).  KIND 1: fp32 rows (kind::tf32, 3xTF32).
-template <int KIND>
+// KIND 0: bf16 rows (kind::f16).  KIND 1: fp32 rows (kind::tf32, 3xTF32).  NQ: queries per pass (16, 32, 64).
+template <int KIND, int NQ>
 __global__ void __launch_bounds__(KIND == 1 ? kThreadsFp32 : kThreadsBf16, 1)
 scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant__ CUtensorMap tmQ, const ScanTcParams p) {
     constexpr int ELEM = (KIND == 0) ? 2 : 4;
     constexpr int KSLICE = kSlice / ELEM;
     constexpr uint32_t FMT = (KIND == 0) ? 1u : 2u;
     constexpr uint32_t IDESC_BASE = (1u << 4) | (FMT << 7) | (FMT << 10) | ((uint32_t)(kTileRows >> 4) << 24);
-    constexpr uint32_t IDESC_N32 = IDESC_BASE | ((32u >> 3) << 17);
-    constexpr uint32_t IDESC_N16 = IDESC_BASE | ((16u >> 3) << 17);
+    constexpr int kNQ = NQ;
+    constexpr int kBTile = 2 * NQ * kSlice;          // [q_hi; q_lo]: 4 / 8 / 16 KB
+    constexpr int kStage = kATile + kBTile;
+    constexpr uint32_t IDESC_N32 = IDESC_BASE | (((uint32_t)(2 * NQ) >> 3) << 17);  // D1: N = 2 NQ
+    constexpr uint32_t IDESC_N16 = IDESC_BASE | (((uint32_t)NQ >> 3) << 17);        // D2: N = NQ
     // TMEM: 2 tile buffers x 4 accumulator chains x 48 columns (D1: 32, D2: 16), then 4 x 32 columns of A_lo
     // slices.  The four 32-byte K steps of a slice accumulate into four INDEPENDENT chains that the epilogue
     // adds up: back-to-back tcgen05.mma on one small accumulator serialise on the MMA latency (measured: the
     // MMA side, not HBM, paced the kernel with a single chain), and shorter chains also halve the truncation bias.
-    constexpr uint32_t kChains = kSlice / 32;
-    constexpr uint32_t kBufCols = kChains * 48u;  // 192
+    constexpr uint32_t kChains = (NQ == 16) ? kSlice / 32 : 1;  // more queries: one chain (TMEM has 512 columns)
+    constexpr uint32_t kChainCols = 3u * NQ;                    // D1 (2 NQ) + D2 (NQ)
+    constexpr uint32_t kBufCols = kChains * kChainCols;         // 192 / 96 / 192
     constexpr uint32_t kTmemCols = 512;
     constexpr uint32_t kLoCol0 = 2 * kBufCols;    // 384
 
@@ -183,10 +187,10 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
                     const uint64_t ad = smem_desc<kSlice>(a);
                     const uint64_t bd = smem_desc<kSlice>(a + kATile);
                     const uint32_t alo = tmem_base + kLoCol0 + (uint32_t)lo_slot * 32u;  // TMEM columns of this slice's A_lo
-                    const uint32_t acc = ks ? 1u : 0u;
 #pragma unroll
                     for (int j = 0; j < kSlice / 32; ++j) {
-                        const uint32_t d1 = dbase + j * 48u, d2 = d1 + 32u;
+                        const uint32_t acc = (kChains == 1 ? (ks | j) : ks) ? 1u : 0u;
+                        const uint32_t d1 = dbase + (kChains == 1 ? 0u : j * kChainCols), d2 = d1 + 2u * NQ;
                         umma<KIND>(d1, ad + (uint64_t)(j * 2), bd + (uint64_t)(j * 2), IDESC_N32, acc);  // +32 B in the address field
                         if (KIND == 1) umma_tf32_ts(d2, alo + j * 8, bd + (uint64_t)(j * 2), IDESC_N16, acc);
                     }
@@ -251,40 +255,47 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
             mbar_wait(smem_u32(tfull_bar + buf), par);
             tcgen05_fence_after();
             const uint32_t taddr = tmem_base + buf * kBufCols + ((uint32_t)(warp * 32) << 16);
-            float big[kNQ], small[kNQ];  // main products / correction products, summed over the four chains
-#pragma unroll
-            for (int j = 0; j < kNQ; ++j) big[j] = small[j] = 0.f;
-#pragma unroll
-            for (int c = 0; c < (int)kChains; ++c) {
-                uint32_t d1[32];
-                uint32_t d2[16];
-                tmem_ld32(taddr + c * 48u, d1);
-                if (KIND == 1) tmem_ld16(taddr + c * 48u + 32u, d2);
-                tmem_ld_wait();
-#pragma unroll
-                for (int j = 0; j < kNQ; ++j) {
-                    big[j] += __uint_as_float(d1[j]);
-                    small[j] += __uint_as_float(d1[kNQ + j]);
-                    if (KIND == 1) small[j] += __uint_as_float(d2[j]);
-                }
-            }
-            tcgen05_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(smem_u32(tempty_bar + buf));  // registers hold the tile: TMEM is free again
             const uint32_t row = (uint32_t)tile * kTileRows + warp * 32 + lane;
+            // queries in groups of 16: columns [g*16, +16) of the q_hi block, of the q_lo block and of D2
+#pragma unroll 1
+            for (int g = 0; g < NQ / 16; ++g) {
+                float big[16], small[16];  // main products / correction products, summed over the chains
 #pragma unroll
-            for (int j = 0; j < kNQ; ++j) {
-                if (j < p.nq) {  // warp-uniform
-                    const float key = (big[j] + small[j]) + 0.0f;
-                    const uint64_t cand = pack_cand(key, row);
-                    const int li = j * kEpiWarps + warp;
-                    const bool pass = row < p.n && key > -FLT_MAX && cand > worst_s[li];
-                    unsigned m = __ballot_sync(kFull, pass);
-                    while (m) {
-                        const int src = __ffs(m) - 1;
-                        m &= m - 1;
-                        const uint64_t c = shfl_u64(cand, src);
-                        warp_list_insert(lists + (size_t)li * p.kpad, p.k, c, worst_s + li, worstpos_s + li, lane);
+                for (int j = 0; j < 16; ++j) big[j] = small[j] = 0.f;
+#pragma unroll
+                for (int c = 0; c < (int)kChains; ++c) {
+                    uint32_t dh[16], dl[16], d2[16];
+                    tmem_ld16(taddr + c * kChainCols + g * 16u, dh);
+                    tmem_ld16(taddr + c * kChainCols + NQ + g * 16u, dl);
+                    if (KIND == 1) tmem_ld16(taddr + c * kChainCols + 2u * NQ + g * 16u, d2);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        big[j] += __uint_as_float(dh[j]);
+                        small[j] += __uint_as_float(dl[j]);
+                        if (KIND == 1) small[j] += __uint_as_float(d2[j]);
+                    }
+                }
+                if (g == NQ / 16 - 1) {
+                    tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(smem_u32(tempty_bar + buf));  // the last group is in registers: TMEM is free
+                }
+#pragma unroll
+                for (int jj = 0; jj < 16; ++jj) {
+                    const int j = g * 16 + jj;
+                    if (j < p.nq) {  // warp-uniform
+                        const float key = (big[jj] + small[jj]) + 0.0f;
+                        const uint64_t cand = pack_cand(key, row);
+                        const int li = j * kEpiWarps + warp;
+                        const bool pass = row < p.n && key > -FLT_MAX && cand > worst_s[li];
+                        unsigned m = __ballot_sync(kFull, pass);
+                        while (m) {
+                            const int src = __ffs(m) - 1;
+                            m &= m - 1;
+                            const uint64_t c = shfl_u64(cand, src);
+                            warp_list_insert(lists + (size_t)li * p.kpad, p.k, c, worst_s + li, worstpos_s + li, lane);
+                        }
                     }
                 }
             }
@@ -307,15 +318,23 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
     }
 }
 
-size_t scan_tc_smem_bytes(bool fp32_rows, int stages, int kpad) {
-    (void)fp32_rows;
-    return 1024 + (size_t)stages * kStage + (size_t)kNQ * kEpiWarps * kpad * 8 + (size_t)kNQ * kEpiWarps * 12 + (3 * kMaxStages + kLoSlots + 4) * 8 + 16;
+size_t scan_tc_smem_bytes(int nqt, int stages, int kpad) {
+    const size_t stage = (size_t)kATile + (size_t)2 * nqt * kSlice;
+    return 1024 + (size_t)stages * stage + (size_t)nqt * kEpiWarps * kpad * 8 + (size_t)nqt * kEpiWarps * 12 +
+           (3 * kMaxStages + kLoSlots + 4) * 8 + 16;
 }
 
-template <int KIND>
+// queries one pass can take at this k: the per-(warp, query) lists (4 x kpad x 8 B each) get at most 64 KB
+int scan_tc_max_queries(int k) {
+    const int kpad = next_pow2(k < 32 ? 32 : k);
+    if (kpad > 128) return 0;
+    return std::min(kMaxNQ, 2048 / kpad);  // kpad 32, 64 -> 32 queries, 128 -> 16
+}
+
+template <int KIND, int NQ>
 int launch_scan_tc(const CUtensorMap& tmRows, const CUtensorMap& tmQ, const ScanTcParams& p, int grid, size_t smem,
                    cudaStream_t stream) {
-    auto kern = scan_tc_kernel<KIND>;
+    auto kern = scan_tc_kernel<KIND, NQ>;
     static std::mutex mu;
     static size_t attr[64] = {0};
     int dev = 0;
@@ -343,8 +362,10 @@ bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t n
     // 6.7-7.3 ms for 3..16; bf16 rows, this kernel 3.1-3.6 ms for 3..16 (the FFMA scan needs 3.3 ms for ONE query)
     int min_nq = (dtype == B2_DTYPE_BF16) ? 3 : 5;
     if (const char* e = getenv("B2_SCAN_TC_MIN_NQ")) min_nq = atoi(e);
-    return metric == B2_METRIC_IP && nq >= min_nq && nq <= kNQ && k <= 128 && n >= 4096 && n < ((int64_t)1 << 31) &&
-           (int64_t)d * elem >= kSlice;
+    // up to 32 queries ride along in one pass when k is small (gemm path at 20..128 queries: 10-11.6 ms fp32,
+    // 5.9-6.7 ms bf16 at 10M x 1024, against the 5.8 / 3.1 ms it takes to stream the rows once)
+    return metric == B2_METRIC_IP && nq >= min_nq && nq <= scan_tc_max_queries(k) && n >= 4096 &&
+           n < ((int64_t)1 << 31) && (int64_t)d * elem >= kSlice;
 }
 
 int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, const float* q_dev, int nq, int k,
@@ -361,9 +382,10 @@ int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int d
     p.kpad = next_pow2(k < 32 ? 32 : k);
     p.kslices = (int)(kbytes / kSlice);
     p.n_tiles = (int)((n + kTileRows - 1) / kTileRows);
+    const int nqt = nq <= 16 ? 16 : 32;  // query tile of the pass
     int stages = kMaxStages;
-    while (stages > 2 && scan_tc_smem_bytes(!bf16, stages, p.kpad) > 227 * 1024) --stages;
-    const size_t smem = scan_tc_smem_bytes(!bf16, stages, p.kpad);
+    while (stages > 2 && scan_tc_smem_bytes(nqt, stages, p.kpad) > 227 * 1024) --stages;
+    const size_t smem = scan_tc_smem_bytes(nqt, stages, p.kpad);
     if (smem > 227 * 1024) {
         set_error("tensor-core scan: k=%d does not fit shared memory", k);
         return B2_ERR_UNSUPPORTED;
@@ -372,7 +394,7 @@ int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int d
     const int grid = (int)std::min<long long>(num_sms, p.n_tiles);
 
     auto al = [](size_t v) { return (v + 1023) / 1024 * 1024; };
-    const size_t q_bytes = al((size_t)2 * kNQ * kbytes);
+    const size_t q_bytes = al((size_t)2 * nqt * kbytes);
     const size_t part_bytes = al((size_t)nq * grid * k * 8);
     char* blk = nullptr;
     B2_CUDA_TRY(cudaMallocAsync(&blk, q_bytes + part_bytes, stream));
@@ -383,10 +405,16 @@ int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int d
     int promo = 256;  // consecutive K slices of a row are fetched back to back: let L2 bring in 256 B per miss
     if (const char* e = getenv("B2_SCAN_TC_L2PROMO")) promo = atoi(e);
     int rc = make_map(&tmRows, bf16, kSlice, rows, (uint64_t)(pitch_bytes / elem), (uint64_t)n, pitch_bytes, kTileRows, promo);
-    if (rc == B2_OK) rc = make_map(&tmQ, bf16, kSlice, Q, (uint64_t)kp, (uint64_t)2 * kNQ, kbytes, 2 * kNQ);
-    if (rc == B2_OK) rc = prep_queries(q_dev, nq, d, kNQ, kp, 2, bf16, Q, nullptr, nullptr, stream);
-    if (rc == B2_OK)
-        rc = bf16 ? launch_scan_tc<0>(tmRows, tmQ, p, grid, smem, stream) : launch_scan_tc<1>(tmRows, tmQ, p, grid, smem, stream);
+    if (rc == B2_OK) rc = make_map(&tmQ, bf16, kSlice, Q, (uint64_t)kp, (uint64_t)2 * nqt, kbytes, 2 * nqt);
+    if (rc == B2_OK) rc = prep_queries(q_dev, nq, d, nqt, kp, 2, bf16, Q, nullptr, nullptr, stream);
+    if (rc == B2_OK) {
+        switch ((bf16 ? 0 : 2) + (nqt == 16 ? 0 : 1)) {
+            case 0: rc = launch_scan_tc<0, 16>(tmRows, tmQ, p, grid, smem, stream); break;
+            case 1: rc = launch_scan_tc<0, 32>(tmRows, tmQ, p, grid, smem, stream); break;
+            case 2: rc = launch_scan_tc<1, 16>(tmRows, tmQ, p, grid, smem, stream); break;
+            default: rc = launch_scan_tc<1, 32>(tmRows, tmQ, p, grid, smem, stream); break;
+        }
+    }
     if (rc == B2_OK) rc = merge_partials(p.partial, nq, grid, k, B2_METRIC_IP, 0, D, I, (size_t)k, stream, nullptr, push);
     cudaFreeAsync(blk, stream);
     return rc;

@@ -191,6 +191,21 @@ def test_small_batch_tensor_scan_matches_sequential_oracle(dtype, nq, k):
     assert np.all(np.diff(D, axis=1) <= 0)
 
 
+@pytest.mark.parametrize("dtype", ["float32", "bfloat16"])
+@pytest.mark.parametrize("nq,k", [(17, 10), (32, 32), (33, 4), (64, 20), (20, 64), (32, 33)])
+def test_medium_batch_rides_one_tensor_scan_pass_when_k_is_small(dtype, nq, k):
+    """Up to 32 queries share one pass over the rows for k <= 64 (query tile of 32); beyond that the GEMM kernel."""
+    n, d = 50_003, 512
+    x, q = _data(n, d, nq, True, seed=200 + nq)
+    idx = _mk(flat.METRIC_IP, d, dtype)
+    idx.add(x)
+    (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, k))
+    assert launches == 3, launches
+    xr = flat.round_bf16(x) if dtype == "bfloat16" else x
+    Dr, Ir = flat.search_f64(xr, q, k, flat.METRIC_IP)
+    assert_parity(D, I, Dr.astype(np.float32), Ir, xr, q, metric_ip=True)
+
+
 def test_small_batch_tensor_scan_ties_and_dims():
     """Planted duplicates (lowest id first) and a dimension that is not a multiple of the 128-byte K slice."""
     n, d, nq, k = 30_000, 200, 7, 6
