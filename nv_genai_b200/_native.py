@@ -23,7 +23,7 @@ MAX_K = 2048
 SYMBOLS = [
     "b2_index_create", "b2_index_destroy", "b2_index_ntotal", "b2_index_d", "b2_index_metric", "b2_index_dtype",
     "b2_index_device", "b2_index_add", "b2_index_search", "b2_index_search_static", "b2_index_reconstruct_batch", "b2_index_remove_ids",
-    "b2_index_merge_from", "b2_index_reset", "b2_index_mmr", "b2_merge_shard_lists", "b2_merge_shard_lists_packed", "b2_index_search_push", "b2_merge_shard_lists_wait", "b2_normalize_l2",
+    "b2_index_merge_from", "b2_index_set_option", "b2_index_reset", "b2_index_mmr", "b2_merge_shard_lists", "b2_merge_shard_lists_packed", "b2_index_search_push", "b2_merge_shard_lists_wait", "b2_normalize_l2",
     "b2_synth_fill", "b2_launch_count", "b2_launch_count_reset", "b2_prof_enable", "b2_prof_read", "b2_prof_read_kernel", "b2_last_error",
     "b2_version",
 ]
@@ -57,6 +57,8 @@ def _load() -> ctypes.CDLL:
     L.b2_index_reconstruct_batch.argtypes = [vp, i64, vp, i32, vp, i32, vp]
     L.b2_index_remove_ids.argtypes = [vp, i64, vp, ctypes.POINTER(i64)]
     L.b2_index_merge_from.argtypes = [vp, vp]
+    L.b2_index_set_option.argtypes = [vp, ctypes.c_char_p, i64]
+    L.b2_index_set_option.restype = i32
     L.b2_index_reset.argtypes = [vp]
     L.b2_index_mmr.argtypes = [vp, i64, vp, i32, i32, i32, f32, vp, vp, i32, vp]
     L.b2_merge_shard_lists.argtypes = [i32, i64, i32, i32, vp, vp, vp, vp, i32, vp]
@@ -83,7 +85,7 @@ def _load() -> ctypes.CDLL:
     L.b2_version.argtypes = []
     L.b2_version.restype = ctypes.c_char_p
     for name in ("b2_index_create", "b2_index_destroy", "b2_index_add", "b2_index_search",
-                 "b2_index_reconstruct_batch", "b2_index_remove_ids", "b2_index_merge_from", "b2_index_reset",
+                 "b2_index_reconstruct_batch", "b2_index_remove_ids", "b2_index_merge_from", "b2_index_set_option", "b2_index_reset",
                  "b2_index_mmr", "b2_merge_shard_lists", "b2_merge_shard_lists_packed", "b2_index_search_push", "b2_merge_shard_lists_wait", "b2_normalize_l2", "b2_synth_fill"):
         getattr(L, name).restype = i32
     return L

@@ -737,30 +737,33 @@ bool gemm_path_supported(int64_t n, int d, int dtype, int k, int64_t nq) {
 
 static int gemm_search_cg(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric,
                           const float* norms, const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I,
-                          cudaStream_t stream, const PeerPush* push, int cg);
+                          cudaStream_t stream, const PeerPush* push, int cg, int query_parts);
 
 int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* norms,
                 const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream,
-                const PeerPush* push) {
+                const PeerPush* push, int query_parts) {
     // CTA pairs (cta_group::2) for bf16 rows when the SM count is even.  Measured at 10M x 1024, nq = 4096, k = 100:
     // bf16 rows 132.7 ms with pairs vs 141.0 ms without; fp32 rows 536 ms with pairs vs 388 ms without (every K slice
     // then needs 16 cluster-scope arrivals from the two CTAs' transform warps before the leader may issue), so fp32
     // rows keep one CTA per MMA.  B2_GEMM_CTA_GROUP overrides.
     int cg = (dtype == B2_DTYPE_BF16 && num_sms % 2 == 0) ? 2 : 1;
     if (const char* e = getenv("B2_GEMM_CTA_GROUP")) cg = (atoi(e) == 2 && num_sms % 2 == 0) ? 2 : 1;
-    int rc = gemm_search_cg(rows, n, pitch_bytes, d, dtype, metric, norms, q_dev, nq, k, num_sms, D, I, stream, push, cg);
+    int rc = gemm_search_cg(rows, n, pitch_bytes, d, dtype, metric, norms, q_dev, nq, k, num_sms, D, I, stream, push, cg,
+                           query_parts);
     if (rc == B2_ERR_UNSUPPORTED && cg == 2)  // no cluster launch here (e.g. a partitioned GPU): one CTA per MMA
-        rc = gemm_search_cg(rows, n, pitch_bytes, d, dtype, metric, norms, q_dev, nq, k, num_sms, D, I, stream, push, 1);
+        rc = gemm_search_cg(rows, n, pitch_bytes, d, dtype, metric, norms, q_dev, nq, k, num_sms, D, I, stream, push, 1,
+                            query_parts);
     return rc;
 }
 
 static int gemm_search_cg(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric,
                           const float* norms, const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I,
-                          cudaStream_t stream, const PeerPush* push, int cg) {
+                          cudaStream_t stream, const PeerPush* push, int cg, int query_parts) {
     const bool bf16 = dtype == B2_DTYPE_BF16;
     const int elem = bf16 ? 2 : 4;
     int na = 2;
     if (const char* e = getenv("B2_GEMM_QUERY_PARTS")) na = (atoi(e) == 1) ? 1 : 2;
+    if (query_parts == 1 || query_parts == 2) na = query_parts;  // b2_index_set_option("gemm_query_parts")
     // stage width: 128-byte swizzle when at least three stages of it fit beside the k-slot heaps, else 64
     int swb = (gemm_smem_bytes(!bf16, na, 128, 3, k, cg) <= 227 * 1024) ? 128 : 64;
     if (const char* e = getenv("B2_GEMM_SWIZZLE")) swb = (atoi(e) == 128) ? 128 : 64;  // tuning override

@@ -231,6 +231,7 @@ struct b2_index {
     RowStore store;
     float* norms = nullptr;  // squared norm of each stored row
     int64_t norms_cap = 0;
+    int gemm_query_parts = 0;  // 0 = default (2: scores exact w.r.t. the stored rows), 1 = single part (faster, approximate)
     std::shared_mutex mu;
 };
 
@@ -488,7 +489,7 @@ static int search_device(b2_index* h, int64_t nq, const float* q_dev, int k, flo
                               D_dev, I_dev, stream, push);
     if (gemm_path_supported(h->ntotal, h->d, h->dtype, k, nq))
         return gemm_search(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, h->metric, h->norms, q_dev, nq, k,
-                           h->num_sms, D_dev, I_dev, stream, push);
+                           h->num_sms, D_dev, I_dev, stream, push, h->gemm_query_parts);
     const int kpad = next_pow2(k < 32 ? 32 : k);
     const int tmax = max_query_tile(h, kpad);
     if (tmax == 0) {
@@ -705,6 +706,25 @@ int b2_index_merge_from(b2_index* dst, b2_index* src) {
     dst->ntotal += n;
     src->ntotal = 0;  // faiss: other.reset()
     return B2_OK;
+}
+
+int b2_index_set_option(b2_index* h, const char* name, int64_t value) {
+    B2_TRY(check_handle(h));
+    if (name == nullptr) {
+        set_error("b2_index_set_option: null option name");
+        return B2_ERR_INVALID;
+    }
+    std::unique_lock<std::shared_mutex> lk(h->mu);
+    if (strcmp(name, "gemm_query_parts") == 0) {
+        if (value != 0 && value != 1 && value != 2) {
+            set_error("b2_index_set_option: gemm_query_parts must be 0 (default), 1 or 2");
+            return B2_ERR_INVALID;
+        }
+        h->gemm_query_parts = (int)value;
+        return B2_OK;
+    }
+    set_error("b2_index_set_option: unknown option '%s'", name);
+    return B2_ERR_INVALID;
 }
 
 int b2_index_reset(b2_index* h) {

@@ -65,7 +65,7 @@ int prep_queries(const float* q_dev, int nq, int d, int nq_pad, int kp, int na, 
 bool gemm_path_supported(int64_t n, int d, int dtype, int k, int64_t nq);
 int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* norms,
                 const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream,
-                const PeerPush* push = nullptr);
+                const PeerPush* push = nullptr, int query_parts = 0);
 // (D_parts, I_parts): [nparts][nq][k] -> [nq][k]
 // part g's lists start d_stride_bytes / i_stride_bytes after part g-1's (0 = natural [nparts][nq][k] arrays);
 // id_bases (host, nparts entries, optional): ids in the lists are local to their part, global = base + local.

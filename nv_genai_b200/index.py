@@ -215,6 +215,11 @@ class IndexFlat:
     def reset(self) -> None:
         N.check(N.lib.b2_index_reset(self._h))
 
+    def set_option(self, name: str, value: int) -> None:
+        """Engine options (no faiss counterpart), e.g. ("gemm_query_parts", 1) for the faster single-part query
+        operand of the tensor-core kernel; see b2_index_set_option in include/b2_flat.h."""
+        N.check(N.lib.b2_index_set_option(self._h, name.encode(), int(value)))
+
     # ---- batched MMR on the device (langchain's maximal_marginal_relevance over index.search hits)
     def mmr(self, x, k: int = 4, fetch_k: int = 20, lambda_mult: float = 0.5):
         """For each query: search fetch_k, reconstruct the hits, greedy MMR pick of k.

@@ -232,3 +232,23 @@ def test_small_batch_l2_keeps_the_direct_form():
     (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, 4))
     assert launches == 2
     assert I[2, 0] == 77 and D[2, 0] == 0.0
+
+
+def test_set_option_single_query_part_is_approximate_but_close():
+    n, d, nq, k = 60_000, 1024, 128, 100
+    x, q = _data(n, d, nq, True, seed=41)
+    idx = _mk(flat.METRIC_IP, d, "bfloat16")
+    idx.add(x)
+    D2, I2 = idx.search(q, k)
+    idx.set_option("gemm_query_parts", 1)
+    D1, I1 = idx.search(q, k)
+    idx.set_option("gemm_query_parts", 0)
+    D0, I0 = idx.search(q, k)
+    assert np.array_equal(I0, I2) and np.array_equal(D0, D2)  # 0 restores the default
+    assert recall_at_k(I1, I2) >= 0.97
+    assert np.allclose(D1, D2, rtol=5e-3)
+    assert not np.array_equal(D1, D2)  # it really is a different operand
+    with pytest.raises(ValueError):
+        idx.set_option("gemm_query_parts", 3)
+    with pytest.raises(ValueError):
+        idx.set_option("no_such_option", 1)
