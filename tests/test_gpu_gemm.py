@@ -252,3 +252,20 @@ def test_set_option_single_query_part_is_approximate_but_close():
         idx.set_option("gemm_query_parts", 3)
     with pytest.raises(ValueError):
         idx.set_option("no_such_option", 1)
+
+
+def test_concurrent_readers_across_all_three_kernels():
+    """Many host threads searching one index at once with batch sizes that take the FFMA scan, the tensor-core scan
+    and the GEMM kernel (each call has its own scratch; static launch state is guarded)."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    n, d = 40_000, 256
+    x, q = _data(n, d, 96, True, seed=51)
+    idx = _mk(flat.METRIC_IP, d)
+    idx.add(x)
+    jobs = [(0, 1, 5), (1, 16, 10), (17, 24, 10), (41, 40, 100), (2, 3, 7), (50, 33, 100), (10, 12, 50), (30, 64, 128)] * 3
+    serial = [idx.search(q[a:a + m], k) for a, m, k in jobs]
+    with ThreadPoolExecutor(8) as ex:
+        par = list(ex.map(lambda j: idx.search(q[j[0]:j[0] + j[1]], j[2]), jobs))
+    for (Ds, Is), (Dp, Ip) in zip(serial, par):
+        assert np.array_equal(Is, Ip) and np.array_equal(Ds, Dp)
