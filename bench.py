@@ -313,6 +313,45 @@ def cfg5(a, device, idx, peak, peak_src):
     return out
 
 
+def cfg1(a, device):
+    """BASELINE configs[0]: IndexFlatL2 over 100k x 1024 un-normalised rows, one query, k = 4 (the 5_mins_rag_no_gpu
+    shape): the launch-latency regime, reported as latency."""
+    import torch
+
+    from nv_genai_b200 import IndexFlatL2, synth_fill
+    from oracle import flat  # seeds only
+
+    n = 100_000
+    idx = IndexFlatL2(a.dim, device=device)
+    buf = torch.empty((n, a.dim), dtype=torch.float32, device=f"cuda:{device}")
+    synth_fill(buf, 0, flat.CORPUS_SEED)
+    idx.add(buf)
+    q = torch.empty((256, a.dim), dtype=torch.float32, device=f"cuda:{device}")
+    synth_fill(q, 0, flat.QUERY_SEED)
+    qh = q.cpu().numpy()
+    for i in range(10):
+        idx.search(q[i:i + 1], 4)
+        idx.search(qh[i:i + 1], 4)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 200
+    e0.record()
+    for i in range(reps):
+        idx.search(q[i:i + 1], 4)
+    e1.record()
+    torch.cuda.synchronize()
+    dev_us = e0.elapsed_time(e1) * 1e3 / reps
+    lat = []
+    for i in range(reps):
+        t0 = time.perf_counter()
+        idx.search(qh[i:i + 1], 4)  # host buffers in and out, synchronous
+        lat.append((time.perf_counter() - t0) * 1e6)
+    return {"rows": n, "device_resident_us_per_query": dev_us, "e2e_host_median_us": statistics.median(lat),
+            "e2e_host_p99_us": sorted(lat)[int(0.99 * len(lat)) - 1],
+            "hbm_floor_us": n * a.dim * 4 / (measured_peak()[0] * 1e9) * 1e6,
+            "note": "409.6 MB per query: 62.6 us at the measured copy peak; scan + merge launches and the host call on top"}
+
+
 def make_queries(a, device, count, batch):
     import torch
 
@@ -493,6 +532,7 @@ def run_b200(a):
             torch.cuda.empty_cache()
         if world == 1:
             extra["cfg5_ingest_and_mmr"] = cfg5(a, local, idx, peak, peak_src)
+            extra["cfg1_100k_l2_k4_latency"] = cfg1(a, local)
     if sampler is not None:
         sampler.stop()
 
