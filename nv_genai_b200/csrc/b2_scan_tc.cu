@@ -30,6 +30,10 @@
 #include "b2_kernels.h"
 #include "b2_tc.cuh"
 
+#ifndef B2_SCAN_TC_CHAINS4
+#define B2_SCAN_TC_CHAINS4 0
+#endif
+
 namespace b2 {
 
 using namespace tc;
@@ -89,11 +93,11 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
     constexpr int kStage = kATile + kBTile;
     constexpr uint32_t IDESC_N32 = IDESC_BASE | (((uint32_t)(2 * NQ) >> 3) << 17);  // D1: N = 2 NQ
     constexpr uint32_t IDESC_N16 = IDESC_BASE | (((uint32_t)NQ >> 3) << 17);        // D2: N = NQ
-    // TMEM: 2 tile buffers x 4 accumulator chains x 48 columns (D1: 32, D2: 16), then 4 x 32 columns of A_lo
-    // slices.  The four 32-byte K steps of a slice accumulate into four INDEPENDENT chains that the epilogue
-    // adds up: back-to-back tcgen05.mma on one small accumulator serialise on the MMA latency (measured: the
-    // MMA side, not HBM, paced the kernel with a single chain), and shorter chains also halve the truncation bias.
-    constexpr uint32_t kChains = (NQ == 16) ? kSlice / 32 : 1;  // more queries: one chain (TMEM has 512 columns)
+    // TMEM: 2 tile buffers x kChains accumulator chains x 3 NQ columns (D1: 2 NQ, D2: NQ), then 4 x 32 columns of A_lo
+    // slices.  With -DB2_SCAN_TC_CHAINS4=1 the four 32-byte K steps of a slice accumulate into four independent
+    // chains that the epilogue adds up (shorter chains halve the truncation bias); measured speed is the same
+    // (7.35 / 3.57 ms at 16 queries either way), so the default is one chain and three TMEM loads per tile.
+    constexpr uint32_t kChains = (NQ == 16 && B2_SCAN_TC_CHAINS4) ? kSlice / 32 : 1;  // more queries: one chain (TMEM has 512 columns)
     constexpr uint32_t kChainCols = 3u * NQ;                    // D1 (2 NQ) + D2 (NQ)
     constexpr uint32_t kBufCols = kChains * kChainCols;         // 192 / 96 / 192
     constexpr uint32_t kTmemCols = 512;
