@@ -51,7 +51,10 @@
 //
 // Algorithmic work per launch: 2 * nq_pad * ntotal * K flop per product (x2 bf16, x3 fp32);
 // corpus bytes ntotal * pitch read ~once from HBM, query tile re-read from L2 per corpus tile.
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "b2_kernels.h"
 #include "b2_tc.cuh"
@@ -83,6 +86,12 @@ struct GemmParams {
     int corr_slots;     // fp32 rows: correction tiles in the ring (2..4)
     int trunc_hi;       // fp32 rows: 1 = leave the raw tile as the hi operand (hardware truncation), 0 = round it in place
     int mixed;          // fp32 rows: 1 = correction products on the bf16 pipe (see kernel comment), 0 = plain 3xTF32
+    int refine;         // 1 = single approximate product; log everything within `band` of the running k-th, exact
+                        //     re-scoring happens in merge_rescore_kernel (see "Filter and refine" above)
+    int list_len;       // entries emitted per (query, segment): k, or k + slack when refine
+    int only_flagged;   // fix-up launch: process only query groups whose flag is set
+    const float* band;  // [nq_pad] refine: 2 x (bound on |approximate key - exact key|), per query
+    uint32_t* flags;    // [n_qt] refine: set when a query of the group had more in-band candidates than fit
     const float* norms; // |x|^2 per stored row
     uint64_t* cand;     // [grid][kCandCap][128]
     uint64_t* partial;  // [nq_pad][n_seg][k]
@@ -180,8 +189,34 @@ __device__ __forceinline__ void compact_log(uint64_t* __restrict__ log, int& cnt
     if (active) cnt = w;
 }
 
+// Refine mode: keep the log entries whose approximate key is above `thr_log` (arrival order preserved).  Called by
+// all lanes of a warp together, like compact_log.
+__device__ __forceinline__ void compact_band(uint64_t* __restrict__ log, int& cnt, float thr_log, bool active) {
+    int cmax = active ? cnt : 0;
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) cmax = max(cmax, __shfl_xor_sync(kFull, cmax, s));
+    const uint32_t to = f2ord(thr_log);
+    const int n = active ? cnt : 0;
+    int w = 0;
+    for (int j0 = 0; j0 < cmax; j0 += 8) {
+        uint64_t e[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) e[u] = (j0 + u < n) ? log[(size_t)(j0 + u) * kEpiThreads] : 0ull;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            if (j0 + u < n && (uint32_t)(e[u] >> 32) > to) {
+                log[(size_t)w * kEpiThreads] = e[u];
+                ++w;
+            }
+        }
+    }
+    if (active) cnt = w;
+}
+
 // ------------------------------------------------------------------ the kernel
-// KIND 0: bf16 rows, kind::f16.  KIND 1: fp32 rows, kind::tf32 (3xTF32).  NA: query parts (1 = hi only, 2 = hi + lo).
+// KIND 0: bf16 rows, kind::f16.  KIND 1: fp32 rows, fp32-faithful (tf32 main + bf16 correction, transform warps).
+// KIND 2: fp32 rows, ONE tf32 product straight from the raw tile (approximate; only with refine).
+// NA: query parts (1 = hi only, 2 = hi + lo).
 // SWB: bytes of K per pipeline stage = the shared-memory swizzle width (64 or 128).
 // CG: CTAs per MMA (tcgen05 cta_group).  CG = 2 launches clusters of two CTAs on the two SMs of a TPC: the pair
 // computes a 256-query x 256-row tile with ONE M = 256 instruction stream issued by the leader CTA; each CTA holds its
@@ -200,7 +235,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     constexpr int STAGE_BYTES = NA * kAPartBytes + kBTileBytes;  // what TMA fills; fp32 rows add kCorrSlots correction tiles
     constexpr uint32_t STAGE_TX = NA * kAPartBytes + kBTileBytes;
     constexpr int B_OFF = NA * kAPartBytes;
-    constexpr uint32_t NBUF = (KIND == 0) ? 2u : 1u;  // accumulator buffers (fp32 rows: main + correction, see above)
+    constexpr uint32_t NBUF = (KIND == 1) ? 1u : 2u;  // accumulator buffers (KIND 1: main + correction use all of TMEM)
+    constexpr int MK = (KIND == 0) ? 0 : 1;          // MMA kind: f16 or tf32
     // instruction descriptor: D fp32, A/B bf16 or tf32, both K-major, N = 256, M = 128
     constexpr uint32_t FMT = (KIND == 0) ? 1u : 2u;
     constexpr uint32_t IDESC = (1u << 4) | (FMT << 7) | (FMT << 10) | ((uint32_t)(kTileN >> 3) << 17) |
@@ -208,7 +244,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     constexpr uint32_t IDESC_BF16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kTileN >> 3) << 17) |
                                     ((uint32_t)((kTileM * CG) >> 4) << 24);
     // bf16 rows, CG = 2: both CTAs' TMA loads complete on the LEADER's full barrier (no transform stage in between)
-    constexpr bool PAIR_FULL = (CG == 2 && KIND == 0);
+    constexpr bool PAIR_FULL = (CG == 2 && KIND != 1);
 
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
@@ -271,6 +307,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         int stage = 0;
         uint32_t phase = 0;
         for (int item = unit; item < p.n_items; item += n_units) {
+            if (p.only_flagged && __ldcg(p.flags + item % p.n_qt) == 0u) continue;  // fix-up launch: flagged groups only
             const int qt = (item % p.n_qt) * CG + (int)cta_rank, seg = item / p.n_qt;
             const int t0 = seg * p.tiles_per_seg;
             const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
@@ -310,6 +347,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint32_t tc = 0;
         int cslot = 0;
         for (int item = unit; cta_rank == 0 && item < p.n_items; item += n_units) {
+            if (p.only_flagged && __ldcg(p.flags + item % p.n_qt) == 0u) continue;  // fix-up launch: flagged groups only
             const int seg = item / p.n_qt;
             const int t0 = seg * p.tiles_per_seg;
             const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
@@ -334,26 +372,26 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             const uint32_t acc = (ks | j) ? 1u : 0u;
                             const uint64_t dj = (uint64_t)(j * 2);  // +32 bytes in the descriptor's address field
                             if (CG == 2) {
-                                umma_pair<KIND>(d_tmem, a_hi0 + dj, b_hi0 + dj, IDESC, acc);
-                                if (KIND == 0) {
-                                    if (NA == 2) umma_pair<KIND>(d_tmem, a_lo0 + dj, b_hi0 + dj, IDESC, 1u);
+                                umma_pair<MK>(d_tmem, a_hi0 + dj, b_hi0 + dj, IDESC, acc);
+                                if (KIND != 1) {
+                                    if (NA == 2) umma_pair<MK>(d_tmem, a_lo0 + dj, b_hi0 + dj, IDESC, 1u);
                                 } else if (p.mixed) {
                                     if (NA == 2) umma_pair<0>(c_tmem, a_lo0 + dj, b_lo0 + dj, IDESC_BF16, acc);
                                 } else {
-                                    umma_pair<KIND>(c_tmem, a_hi0 + dj, b_lo0 + dj, IDESC, acc);
-                                    if (NA == 2) umma_pair<KIND>(c_tmem, a_lo0 + dj, b_hi0 + dj, IDESC, 1u);
+                                    umma_pair<MK>(c_tmem, a_hi0 + dj, b_lo0 + dj, IDESC, acc);
+                                    if (NA == 2) umma_pair<MK>(c_tmem, a_lo0 + dj, b_hi0 + dj, IDESC, 1u);
                                 }
                                 continue;
                             }
-                            umma<KIND>(d_tmem, a_hi0 + dj, b_hi0 + dj, IDESC, acc);
-                            if (KIND == 0) {
-                                if (NA == 2) umma<KIND>(d_tmem, a_lo0 + dj, b_hi0 + dj, IDESC, 1u);
+                            umma<MK>(d_tmem, a_hi0 + dj, b_hi0 + dj, IDESC, acc);
+                            if (KIND != 1) {
+                                if (NA == 2) umma<MK>(d_tmem, a_lo0 + dj, b_hi0 + dj, IDESC, 1u);
                             } else if (p.mixed) {
                                 // both correction products in ONE bf16 MMA: [q_hi | q_lo] . [x_lo | x_hi] over a doubled K
                                 if (NA == 2) umma<0>(c_tmem, a_lo0 + dj, b_lo0 + dj, IDESC_BF16, acc);
                             } else {
-                                umma<KIND>(c_tmem, a_hi0 + dj, b_lo0 + dj, IDESC, acc);
-                                if (NA == 2) umma<KIND>(c_tmem, a_lo0 + dj, b_hi0 + dj, IDESC, 1u);
+                                umma<MK>(c_tmem, a_hi0 + dj, b_lo0 + dj, IDESC, acc);
+                                if (NA == 2) umma<MK>(c_tmem, a_lo0 + dj, b_hi0 + dj, IDESC, 1u);
                             }
                         }
                         if (CG == 2) tcgen05_commit_pair(smem_u32(empty_bar + stage));
@@ -384,6 +422,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             int fstage = 0;
             uint32_t fphase = 0;
             for (int item = unit; item < p.n_items; item += n_units) {
+                if (p.only_flagged && __ldcg(p.flags + item % p.n_qt) == 0u) continue;  // fix-up launch: flagged groups only
                 const int seg = item / p.n_qt;
                 const int t0 = seg * p.tiles_per_seg;
                 const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
@@ -409,6 +448,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             int cslot = 0;
             uint32_t cphase = 0;
             for (int item = unit; item < p.n_items; item += n_units) {
+                if (p.only_flagged && __ldcg(p.flags + item % p.n_qt) == 0u) continue;  // fix-up launch: flagged groups only
                 const int seg = item / p.n_qt;
                 const int t0 = seg * p.tiles_per_seg;
                 const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
@@ -497,6 +537,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const bool l2 = p.metric == B2_METRIC_L2;
         uint32_t tc = 0;
         for (int item = unit; item < p.n_items; item += n_units) {
+            if (p.only_flagged && __ldcg(p.flags + item % p.n_qt) == 0u) continue;  // fix-up launch: flagged groups only
             const int qt = (item % p.n_qt) * CG + (int)cta_rank, seg = item / p.n_qt;
             const int t0 = seg * p.tiles_per_seg;
             const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
@@ -504,7 +545,13 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const bool active = q < p.nq;
             // bound imported from finished items of this query (exclusive); +inf parks padding lanes
             const float thr0 = active ? ord2f(__ldcg(p.tau + q)) : -kNegInf;
-            float thr = thr0;
+            float thr = thr0;      // a key enters the sorted list if it is above this
+            // refine: approximate keys; everything within `band` below the running k-th is logged as well, and the
+            // imported bound is already such a log threshold
+            const bool refine = p.refine != 0;
+            const float band = (refine && active) ? __ldg(p.band + q) : 0.f;
+            float thr_log = thr0;  // a key is logged if it is above this (== thr unless refine)
+            bool overflow = false;
             int cnt = 0;
             for (int i = lane; i < 32 * k; i += 32) keys_w[i] = kNegInf;
             __syncwarp();
@@ -520,8 +567,17 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     asm volatile("bar.sync 1, 128;" ::: "memory");
                 }
                 // a whole tile of survivors must fit behind cnt: compact first if any lane is close (warp-uniform)
-                if (__any_sync(kFull, cnt > kCandCap - kTileN))
-                    compact_log(log, cnt, keys_w[(size_t)lane * k + (k - 1)], k, cnt > k);
+                if (__any_sync(kFull, cnt > kCandCap - kTileN)) {
+                    if (refine) {
+                        compact_band(log, cnt, thr_log, active);
+                        if (cnt > kCandCap - kTileN && !overflow) {  // too many in-band candidates: leave it to the fix-up pass
+                            overflow = true;
+                            atomicOr(p.flags + item % p.n_qt, 1u);
+                        }
+                    } else {
+                        compact_log(log, cnt, keys_w[(size_t)lane * k + (k - 1)], k, cnt > k);
+                    }
+                }
                 mbar_wait(smem_u32(tfull_bar + buf), par);
                 tcgen05_fence_after();
                 const int limit = (int)min((uint32_t)kTileN, p.n - row0);
@@ -556,10 +612,29 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         for (int c = 0; c < 32; ++c) key[c] = __uint_as_float(raw32[c]) + 0.0f;
                     }
                     uint32_t m = 0;
-#pragma unroll
-                    for (int c = 0; c < 32; ++c) m |= (key[c] > thr) ? (1u << c) : 0u;
                     const int left = limit - ch * 32;
-                    if (left < 32) m &= (left <= 0) ? 0u : ((1u << left) - 1u);
+                    const uint32_t valid = (left >= 32) ? 0xffffffffu : ((left <= 0) ? 0u : ((1u << left) - 1u));
+                    if (refine) {
+                        uint32_t ml = 0;
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) {
+                            ml |= (key[c] > thr_log) ? (1u << c) : 0u;
+                            m |= (key[c] > thr) ? (1u << c) : 0u;
+                        }
+                        ml &= valid;
+                        while (ml) {  // lane-local: log every in-band candidate of this chunk, in row order
+                            const int c = __ffs(ml) - 1;
+                            ml &= ml - 1u;
+                            if (cnt < kCandCap) {
+                                log[(size_t)cnt * kEpiThreads] = pack_cand(select32(key, c), row0 + ch * 32 + c);
+                                ++cnt;
+                            }
+                        }
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) m |= (key[c] > thr) ? (1u << c) : 0u;
+                    }
+                    m &= valid;
                     // survivors, one (query, column) at a time, each inserted by the whole warp
                     unsigned pending = __ballot_sync(kFull, m != 0u);
                     while (pending) {
@@ -571,9 +646,12 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         if (xs > ts) {  // the threshold may have risen since the mask was built
                             const float kth = coop_insert(keys_w + (size_t)src * k, k, xs, lane);
                             if (lane == src) {
-                                log[(size_t)cnt * kEpiThreads] = pack_cand(kv, row0 + ch * 32 + c);
-                                ++cnt;
+                                if (!refine) {
+                                    log[(size_t)cnt * kEpiThreads] = pack_cand(kv, row0 + ch * 32 + c);
+                                    ++cnt;
+                                }
                                 thr = fmaxf(thr0, kth);
+                                thr_log = fmaxf(thr0, kth - band);
                             }
                         }
                         if (lane == src) m &= m - 1u;
@@ -590,18 +668,25 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             // ---- item done: emit this query's k best of the segment, publish the bound
             const float tau = keys_w[(size_t)lane * k + (k - 1)];
             const bool full = active && tau > kNegInf;
-            compact_log(log, cnt, tau, k, full);
-            if (full) atomicMax(p.tau + q, f2ord(tau) - 1u);
+            const int L = p.list_len;
+            if (refine) {
+                compact_band(log, cnt, thr_log, active);  // everything that can still be in the exact top-k
+                if (active && (cnt > L || overflow)) atomicOr(p.flags + item % p.n_qt, 1u);
+                if (full) atomicMax(p.tau + q, f2ord(tau - band) - 1u);  // a log threshold for the other segments
+            } else {
+                compact_log(log, cnt, tau, k, full);
+                if (full) atomicMax(p.tau + q, f2ord(tau) - 1u);
+            }
             if (active) {
-                uint64_t* out = p.partial + ((size_t)q * p.n_seg + seg) * k;
-                for (int i0 = 0; i0 < k; i0 += 8) {
+                uint64_t* out = p.partial + ((size_t)q * p.n_seg + seg) * L;
+                for (int i0 = 0; i0 < L; i0 += 8) {
                     uint64_t e[8];
 #pragma unroll
                     for (int u = 0; u < 8; ++u)
                         e[u] = (i0 + u < cnt) ? log[(size_t)(i0 + u) * kEpiThreads] : B2_SENTINEL;
 #pragma unroll
                     for (int u = 0; u < 8; ++u)
-                        if (i0 + u < k) out[i0 + u] = e[u];
+                        if (i0 + u < L) out[i0 + u] = e[u];
                 }
             }
             __syncwarp();
@@ -662,6 +747,50 @@ __global__ void prep_queries_kernel(const float* __restrict__ q, int nq, int d, 
     }
 }
 
+// Refine mode: band[q] = 2 x (a rigorous bound on |approximate key - exact key| over all stored rows), per query.
+//   bf16 rows:  approximate = bf16(q) . x         -> |error| <= |q - bf16(q)| |x|
+//   fp32 rows:  approximate = tf32(q) . trunc(x)   -> |error| <= (|q - tf32(q)| + 2^-10 |tf32(q)|) |x|
+// plus the tensor core's truncating accumulation (<= steps x 2^-21 |q||x|, measured ~2^-24 per step), with |x| <=
+// sqrt(max_norm) from the ingest side array; x2 again for L2 keys (2 q.x - |x|^2).
+template <int KIND>
+__global__ void band_kernel(const float* __restrict__ q, int nq, int d, int nq_pad, int steps, int l2,
+                            const uint32_t* __restrict__ max_norm_ord, float* __restrict__ band) {
+    const int lane = threadIdx.x & 31;
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= nq_pad) return;
+    float ss = 0.f, se = 0.f;
+    if (row < nq) {
+        for (int c = lane; c < d; c += 32) {
+            const float x = q[(size_t)row * d + c];
+            float h;
+            if (KIND == 0) {
+                h = __bfloat162float(__float2bfloat16_rn(x));
+            } else {
+                uint32_t u;
+                asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+                h = __uint_as_float(u);
+            }
+            ss = fmaf(h, h, ss);
+            se = fmaf(x - h, x - h, se);
+        }
+    }
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) {
+        ss += __shfl_xor_sync(kFull, ss, s);
+        se += __shfl_xor_sync(kFull, se, s);
+    }
+    if (lane == 0) {
+        const float xn = sqrtf(fmaxf(ord2f(*max_norm_ord), 0.f)) * 1.0001f;
+        const float qn = sqrtf(ss) * 1.0001f, qe = sqrtf(se) * 1.0001f;
+        float err = qe * xn;
+        if (KIND != 0) err += qn * xn * 0.0009765625f;               // the row operand is truncated to tf32: 2^-10
+        err += (float)steps * 4.76837158e-7f * qn * xn;              // accumulation: steps x 2^-21
+        float b = 2.f * err * 1.001f + 1e-30f;
+        if (l2) b *= 2.f;
+        band[row] = b;
+    }
+}
+
 size_t gemm_smem_bytes(bool fp32_rows, int na, int swb, int stages, int k, int cg = 1, int corr_slots = 2) {
     const size_t stage = (size_t)na * kTileM * swb + (size_t)(kTileN / cg) * swb;
     const size_t corr = fp32_rows ? (size_t)corr_slots * (kTileN / cg) * swb : 0;
@@ -684,7 +813,7 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
             attr[dev & 63] = smem;
         }
     }
-    void* tok = prof_begin(stream);
+    void* tok = p.only_flagged ? nullptr : prof_begin(stream);  // the fix-up launch is not the profiled kernel
     if (CG == 2) {
         cudaLaunchConfig_t cfg;
         memset(&cfg, 0, sizeof(cfg));
@@ -738,10 +867,28 @@ bool gemm_path_supported(int64_t n, int d, int dtype, int k, int64_t nq) {
 static int gemm_search_cg(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric,
                           const float* norms, const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I,
                           cudaStream_t stream, const PeerPush* push, int cg, int query_parts);
+static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric,
+                              const float* norms, const uint32_t* max_norm_ord, const float* q_dev, int64_t nq, int k,
+                              int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push, int cg);
 
 int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* norms,
                 const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream,
-                const PeerPush* push, int query_parts) {
+                const PeerPush* push, int query_parts, const uint32_t* max_norm_ord) {
+    // Filter and refine (default): one approximate product on the tensor cores, exact re-scoring of the few
+    // candidates near the cut.  An explicit number of query parts (option / environment) selects the all-exact
+    // tensor-core arithmetic instead, as does B2_GEMM_REFINE=0.
+    bool refine = max_norm_ord != nullptr && query_parts == 0 && getenv("B2_GEMM_QUERY_PARTS") == nullptr;
+    if (const char* e = getenv("B2_GEMM_REFINE")) refine = refine && atoi(e) != 0;
+    if (refine) {
+        int cgr = (num_sms % 2 == 0) ? 2 : 1;
+        if (const char* e = getenv("B2_GEMM_CTA_GROUP")) cgr = (atoi(e) == 2 && num_sms % 2 == 0) ? 2 : 1;
+        int rc = gemm_search_refine(rows, n, pitch_bytes, d, dtype, metric, norms, max_norm_ord, q_dev, nq, k, num_sms, D,
+                                    I, stream, push, cgr);
+        if (rc == B2_ERR_UNSUPPORTED && cgr == 2)
+            rc = gemm_search_refine(rows, n, pitch_bytes, d, dtype, metric, norms, max_norm_ord, q_dev, nq, k, num_sms,
+                                    D, I, stream, push, 1);
+        return rc;
+    }
     // CTA pairs (cta_group::2) for bf16 rows when the SM count is even.  Measured at 10M x 1024, nq = 4096, k = 100:
     // bf16 rows 132.7 ms with pairs vs 141.0 ms without; fp32 rows 536 ms with pairs vs 388 ms without (every K slice
     // then needs 16 cluster-scope arrivals from the two CTAs' transform warps before the leader may issue), so fp32
@@ -836,6 +983,11 @@ static int gemm_search_cg(const void* rows, int64_t n, size_t pitch_bytes, int d
     if (const char* e = getenv("B2_GEMM_TRUNC")) p.trunc_hi = atoi(e) ? 1 : 0;
     p.mixed = (!bf16 && na == 2) ? 1 : 0;
     if (const char* e = getenv("B2_GEMM_MIXED")) p.mixed = (!bf16 && na == 2 && atoi(e)) ? 1 : 0;
+    p.refine = 0;
+    p.only_flagged = 0;
+    p.list_len = k;
+    p.band = nullptr;
+    p.flags = nullptr;
 
     // scratch: [A parts][qn][tau][partial][candidate logs]
     auto al = [](size_t v) { return (v + 1023) / 1024 * 1024; };
@@ -881,6 +1033,221 @@ static int gemm_search_cg(const void* rows, int64_t n, size_t pitch_bytes, int d
     if (rc == B2_OK)
         rc = merge_partials(p.partial, (int)nq, p.n_seg, k, metric, 0, D, I, (size_t)k, stream,
                             metric == B2_METRIC_L2 ? qn : nullptr, push);
+    cudaFreeAsync(blk, stream);
+    return rc;
+}
+
+// ------------------------------------------------------------------ filter and refine
+// One approximate product per score on the tensor cores (bf16 rows: bf16(q) . x; fp32 rows: tf32(q) . trunc_tf32(x)
+// straight from the raw tile, no transform warps), every candidate within a rigorous error band of the running k-th
+// is kept, and merge_rescore_kernel re-scores the handful of candidates near the final cut exactly (fp32 FMA, the
+// small-batch scan's arithmetic) before it selects the top k.  Exactness does not depend on the data: the band
+// comes from |q - q~| |x| (Cauchy-Schwarz) with |x| <= the largest stored norm.  If a query collects more in-band
+// candidates than its list holds (dense score ties), its query group is flagged and a second launch of the
+// all-exact kernel (2 query parts / tf32 + bf16 correction) redoes exactly those groups.
+template <int KIND, int NA, int SWB>
+static int launch_gemm_cg(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int grid, size_t smem,
+                          cudaStream_t stream, int cg) {
+    return cg == 2 ? launch_gemm<KIND, NA, SWB, 2>(tmA, tmB, p, grid, smem, stream)
+                   : launch_gemm<KIND, NA, SWB, 1>(tmA, tmB, p, grid, smem, stream);
+}
+
+static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric,
+                              const float* norms, const uint32_t* max_norm_ord, const float* q_dev, int64_t nq, int k,
+                              int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push, int cg) {
+    const bool bf16 = dtype == B2_DTYPE_BF16;
+    const int elem = bf16 ? 2 : 4;
+    auto fits = [&](bool fp32_exact, int na, int swb, int stages, int corr) {
+        return gemm_smem_bytes(fp32_exact, na, swb, stages, k, cg, corr) <= 227 * 1024;
+    };
+    // ---- the approximate launch: one query part, no correction tiles
+    int swb = fits(false, 1, 128, 3, 0) ? 128 : 64;
+    if (const char* e = getenv("B2_GEMM_SWIZZLE")) swb = (atoi(e) == 128 && fits(false, 1, 128, 2, 0)) ? 128 : 64;
+    const size_t kbytes = (((size_t)d * elem + swb - 1) / swb) * swb;
+    const int kp = (int)(kbytes / elem);
+    int stages = kMaxStages;
+    while (stages > 2 && !fits(false, 1, swb, stages, 0)) --stages;
+    if (!fits(false, 1, swb, stages, 0)) {
+        set_error("tensor-core search: k=%d does not fit shared memory", k);
+        return B2_ERR_UNSUPPORTED;
+    }
+    // ---- the exact fix-up launch (same grid, same items): two query parts
+    const int swb_x = 64;
+    int stages_x = kMaxStages, corr_x = 2;
+    if (bf16) {
+        while (stages_x > 2 && !fits(false, 2, swb_x, stages_x, 0)) --stages_x;
+    } else {
+        static const int cand[5][2] = {{4, 4}, {4, 2}, {3, 3}, {3, 2}, {2, 2}};
+        stages_x = 2;
+        for (int c = 0; c < 5; ++c)
+            if (fits(true, 2, swb_x, cand[c][0], cand[c][1])) {
+                stages_x = cand[c][0];
+                corr_x = cand[c][1];
+                break;
+            }
+    }
+    const size_t kbytes_x = (((size_t)d * elem + swb_x - 1) / swb_x) * swb_x;
+    const int kp_x = (int)(kbytes_x / elem);
+    const size_t smem_x = gemm_smem_bytes(!bf16, 2, swb_x, stages_x, k, cg, corr_x);
+    if (smem_x > 227 * 1024) {
+        set_error("tensor-core search: k=%d does not fit shared memory", k);
+        return B2_ERR_UNSUPPORTED;
+    }
+
+    GemmParams p;
+    p.nq = (int)nq;
+    p.nq_pad = (int)((nq + kTileM * cg - 1) / (kTileM * cg)) * kTileM * cg;
+    p.n = (uint32_t)n;
+    p.k = k;
+    p.kstages = (int)(kbytes / swb);
+    p.metric = metric;
+    p.n_qt = p.nq_pad / (kTileM * cg);
+    p.n_tiles = (int)((n + kTileN - 1) / kTileN);
+    p.norms = norms;
+    const int grid_max = num_sms / cg;
+    int best_s = 1;
+    double best_cost = 1e30;
+    const int max_s = std::max(1, std::min(p.n_tiles / 8, 4 * grid_max));
+    for (int s = 1; s <= max_s; ++s) {
+        const int tps = (p.n_tiles + s - 1) / s;
+        const int s_eff = (p.n_tiles + tps - 1) / tps;
+        const long long items = (long long)p.n_qt * s_eff;
+        const long long waves = (items + grid_max - 1) / grid_max;
+        const double cost = (double)waves * (tps + 6.0);
+        if (cost < best_cost * 0.995) {
+            best_cost = cost;
+            best_s = s_eff;
+        }
+    }
+    p.tiles_per_seg = (p.n_tiles + best_s - 1) / best_s;
+    p.n_seg = (p.n_tiles + p.tiles_per_seg - 1) / p.tiles_per_seg;
+    p.n_items = p.n_qt * p.n_seg;
+    const int grid = (int)std::min<long long>(grid_max, p.n_items) * cg;
+    p.num_stages = stages;
+    p.corr_slots = 2;
+    p.trunc_hi = 1;
+    p.mixed = 0;
+    p.refine = 1;
+    p.only_flagged = 0;
+    // Room for the in-band candidates of a segment beyond its k best.  Their number grows with k (about
+    // k * z * band / sigma for scores with a Gaussian tail: ~0.4 k on 1024-d unit vectors with bf16 queries); a
+    // segment that overflows the list is flagged and redone by the exact fix-up launch, so this is a speed knob only.
+    int slack = std::max(48, 32 + 5 * k / 4);
+    if (const char* e = std::getenv("B2_GEMM_LIST_SLACK")) slack = std::max(8, std::min(1024 - k - 8, atoi(e)));
+    p.list_len = ((k + slack) + 7) / 8 * 8;
+
+    // scratch: [A (1 part)][A exact (2 parts)][qn][tau][band][flags][partial][candidate logs]
+    auto al = [](size_t v) { return (v + 1023) / 1024 * 1024; };
+    const size_t a_bytes = al((size_t)p.nq_pad * kbytes);
+    const size_t ax_bytes = al((size_t)2 * p.nq_pad * kbytes_x);
+    const size_t qn_bytes = al((size_t)p.nq_pad * 4);
+    const size_t fl_bytes = al((size_t)p.n_qt * 4);
+    const size_t part_bytes = al((size_t)p.nq_pad * p.n_seg * p.list_len * 8);
+    const size_t cand_bytes = al((size_t)grid * kCandCap * kEpiThreads * 8);
+    char* blk = nullptr;
+    B2_CUDA_TRY(cudaMallocAsync(&blk, a_bytes + ax_bytes + 3 * qn_bytes + fl_bytes + part_bytes + cand_bytes, stream));
+    char* cur = blk;
+    void* A = cur;
+    cur += a_bytes;
+    void* Ax = cur;
+    cur += ax_bytes;
+    float* qn = reinterpret_cast<float*>(cur);
+    cur += qn_bytes;
+    p.tau = reinterpret_cast<uint32_t*>(cur);
+    cur += qn_bytes;
+    float* band = reinterpret_cast<float*>(cur);
+    cur += qn_bytes;
+    p.flags = reinterpret_cast<uint32_t*>(cur);
+    cur += fl_bytes;
+    p.partial = reinterpret_cast<uint64_t*>(cur);
+    cur += part_bytes;
+    p.cand = reinterpret_cast<uint64_t*>(cur);
+    p.band = band;
+
+    int rc = B2_OK;
+    CUtensorMap tmA, tmB, tmAx, tmBx;
+    rc = make_map(&tmA, bf16, swb, A, (uint64_t)kp, (uint64_t)p.nq_pad, kbytes, kTileM);
+    if (rc == B2_OK) rc = make_map(&tmB, bf16, swb, rows, (uint64_t)(pitch_bytes / elem), (uint64_t)n, pitch_bytes, kTileN / cg);
+    if (rc == B2_OK) rc = make_map(&tmAx, bf16, swb_x, Ax, (uint64_t)kp_x, (uint64_t)2 * p.nq_pad, kbytes_x, kTileM);
+    if (rc == B2_OK) rc = make_map(&tmBx, bf16, swb_x, rows, (uint64_t)(pitch_bytes / elem), (uint64_t)n, pitch_bytes, kTileN / cg);
+    if (rc == B2_OK && cudaMemsetAsync(p.flags, 0, (size_t)p.n_qt * 4, stream) != cudaSuccess) {
+        set_error("tensor-core search: cudaMemsetAsync failed");
+        rc = B2_ERR_CUDA;
+    }
+    if (rc == B2_OK) rc = prep_queries(q_dev, (int)nq, d, p.nq_pad, kp, 1, bf16, A, qn, p.tau, stream, 0);
+    if (rc == B2_OK) rc = prep_queries(q_dev, (int)nq, d, p.nq_pad, kp_x, 2, bf16, Ax, nullptr, nullptr, stream, bf16 ? 0 : swb_x / 4);
+    if (rc == B2_OK) {
+        const int blocks = (p.nq_pad + 7) / 8;
+        const int steps = bf16 ? kp / 16 : kp / 8;
+        if (bf16)
+            band_kernel<0><<<blocks, 256, 0, stream>>>(q_dev, (int)nq, d, p.nq_pad, steps, metric == B2_METRIC_L2, max_norm_ord, band);
+        else
+            band_kernel<1><<<blocks, 256, 0, stream>>>(q_dev, (int)nq, d, p.nq_pad, steps, metric == B2_METRIC_L2, max_norm_ord, band);
+        B2_COUNT_LAUNCH();
+        if (cudaGetLastError() != cudaSuccess) {
+            set_error("band kernel launch failed");
+            rc = B2_ERR_CUDA;
+        }
+    }
+    const size_t smem = gemm_smem_bytes(false, 1, swb, stages, k, cg, 0);
+    static const bool debug_t = std::getenv("B2_GEMM_DEBUG") != nullptr;
+    cudaEvent_t dbg_ev0 = nullptr;
+    if (debug_t) {
+        cudaEventCreate(&dbg_ev0);
+        cudaEventRecord(dbg_ev0, stream);
+    }
+    if (rc == B2_OK) {
+        if (bf16)
+            rc = swb == 128 ? launch_gemm_cg<0, 1, 128>(tmA, tmB, p, grid, smem, stream, cg)
+                            : launch_gemm_cg<0, 1, 64>(tmA, tmB, p, grid, smem, stream, cg);
+        else
+            rc = swb == 128 ? launch_gemm_cg<2, 1, 128>(tmA, tmB, p, grid, smem, stream, cg)
+                            : launch_gemm_cg<2, 1, 64>(tmA, tmB, p, grid, smem, stream, cg);
+    }
+    static const bool debug = std::getenv("B2_GEMM_DEBUG") != nullptr;
+    cudaEvent_t dbg_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    if (debug) {
+        for (auto& e : dbg_ev) cudaEventCreate(&e);
+        cudaEventRecord(dbg_ev[1], stream);
+    }
+    if (rc == B2_OK && debug) {  // diagnostics only: how many query groups the approximate pass handed to the fix-up
+        std::vector<uint32_t> fl(p.n_qt);
+        std::vector<float> bd(std::min(p.nq, 4));
+        cudaStreamSynchronize(stream);
+        cudaMemcpy(fl.data(), p.flags, fl.size() * 4, cudaMemcpyDeviceToHost);
+        cudaMemcpy(bd.data(), band, bd.size() * 4, cudaMemcpyDeviceToHost);
+        int nf = 0;
+        for (uint32_t f : fl) nf += f != 0u;
+        std::fprintf(stderr, "[b2 gemm refine] k=%d list_len=%d n_seg=%d n_qt=%d flagged=%d band[0]=%g\n", k, p.list_len,
+                     p.n_seg, p.n_qt, nf, bd.empty() ? 0.0 : (double)bd[0]);
+    }
+    if (rc == B2_OK) {  // fix-up: the all-exact kernel over the flagged query groups only (normally none)
+        GemmParams px = p;
+        px.refine = 0;
+        px.only_flagged = 1;
+        px.kstages = (int)(kbytes_x / swb_x);
+        px.num_stages = stages_x;
+        px.corr_slots = corr_x;
+        px.mixed = bf16 ? 0 : 1;
+        rc = bf16 ? launch_gemm_cg<0, 2, 64>(tmAx, tmBx, px, grid, smem_x, stream, cg)
+                  : launch_gemm_cg<1, 2, 64>(tmAx, tmBx, px, grid, smem_x, stream, cg);
+    }
+    if (debug) cudaEventRecord(dbg_ev[2], stream);
+    if (rc == B2_OK)
+        rc = merge_rescore(p.partial, (int)nq, p.n_seg, p.list_len, k, metric, D, I, (size_t)k, stream,
+                           metric == B2_METRIC_L2 ? qn : nullptr, q_dev, d, rows, pitch_bytes, dtype, norms, band, push);
+    if (debug) {
+        cudaEventRecord(dbg_ev[3], stream);
+        cudaStreamSynchronize(stream);
+        float t_approx = 0.f, t_fix = 0.f, t_merge = 0.f;
+        cudaEventElapsedTime(&t_approx, dbg_ev0, dbg_ev[1]);
+        cudaEventElapsedTime(&t_fix, dbg_ev[1], dbg_ev[2]);
+        cudaEventElapsedTime(&t_merge, dbg_ev[2], dbg_ev[3]);
+        std::fprintf(stderr, "[b2 gemm refine] approx %.2f ms (stages %d, swizzle %d), fix-up %.2f ms (incl. the flag read-back), merge %.2f ms\n",
+                     t_approx, stages, swb, t_fix, t_merge);
+        for (auto& e : dbg_ev) cudaEventDestroy(e);
+        cudaEventDestroy(dbg_ev0);
+    }
     cudaFreeAsync(blk, stream);
     return rc;
 }

@@ -231,6 +231,7 @@ struct b2_index {
     RowStore store;
     float* norms = nullptr;  // squared norm of each stored row
     int64_t norms_cap = 0;
+    uint32_t* max_norm_ord = nullptr;  // device: ordered image of the largest squared row norm seen so far
     int gemm_query_parts = 0;  // 0 = default (2: scores exact w.r.t. the stored rows), 1 = single part (faster, approximate)
     std::shared_mutex mu;
 };
@@ -361,6 +362,13 @@ int b2_index_create(int d, int metric, int dtype, int device, b2_index** out) {
     h->num_sms = sms;
     h->pitch = row_pitch_bytes(d, dtype);
     h->store.init(device);
+    if (cudaMalloc(&h->max_norm_ord, sizeof(uint32_t)) != cudaSuccess ||
+        cudaMemset(h->max_norm_ord, 0, sizeof(uint32_t)) != cudaSuccess) {  // 0 orders below every float
+        cudaGetLastError();
+        delete h;
+        set_error("out of device memory");
+        return B2_ERR_OOM;
+    }
     *out = h;
     return B2_OK;
 }
@@ -372,6 +380,7 @@ int b2_index_destroy(b2_index* h) {
         cudaDeviceSynchronize();
         h->store.release();
         if (h->norms) cudaFree(h->norms);
+        if (h->max_norm_ord) cudaFree(h->max_norm_ord);
         cudaGetLastError();
     }
     delete h;
@@ -445,6 +454,7 @@ int b2_index_add(b2_index* h, int64_t n, const float* x, int x_where, unsigned f
         // the caller may reuse its host buffer as soon as we return
         B2_CUDA_TRY(cudaStreamSynchronize(stream));
     }
+    B2_TRY(update_max_norm(nrm, n, h->max_norm_ord, stream));
     h->ntotal += n;
     return B2_OK;
 }
@@ -489,7 +499,7 @@ static int search_device(b2_index* h, int64_t nq, const float* q_dev, int k, flo
                               D_dev, I_dev, stream, push);
     if (gemm_path_supported(h->ntotal, h->d, h->dtype, k, nq))
         return gemm_search(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, h->metric, h->norms, q_dev, nq, k,
-                           h->num_sms, D_dev, I_dev, stream, push, h->gemm_query_parts);
+                           h->num_sms, D_dev, I_dev, stream, push, h->gemm_query_parts, h->max_norm_ord);
     const int kpad = next_pow2(k < 32 ? 32 : k);
     const int tmax = max_query_tile(h, kpad);
     if (tmax == 0) {
@@ -702,6 +712,7 @@ int b2_index_merge_from(b2_index* dst, b2_index* src) {
         B2_CUDA_TRY(cudaMemcpyPeerAsync(to, dst->device, src->store.base(), src->device, (size_t)n * dst->pitch, stream));
         B2_CUDA_TRY(cudaMemcpyPeerAsync(dst->norms + dst->ntotal, dst->device, src->norms, src->device, (size_t)n * 4, stream));
     }
+    B2_TRY(update_max_norm(dst->norms + dst->ntotal, n, dst->max_norm_ord, stream));
     B2_CUDA_TRY(cudaStreamSynchronize(stream));
     dst->ntotal += n;
     src->ntotal = 0;  // faiss: other.reset()

@@ -12,6 +12,8 @@
 //
 // gather_rows replaces index.reconstruct (IndexFlatCodes::reconstruct); copy_rows_indexed is
 // the mover behind index.remove_ids (IndexFlatCodes::remove_ids compaction).
+#include <algorithm>
+
 #include "b2_common.cuh"
 #include "b2_kernels.h"
 
@@ -257,6 +259,27 @@ int compact_rows(void* rows, size_t pitch_bytes, float* norms, const int64_t* sr
     cudaFreeAsync(tmp, stream);
     cudaFreeAsync(tmpn, stream);
     return rc;
+}
+
+// ------------------------------------------------------------------ running maximum of the squared row norms
+// (ordered-uint image, atomicMax): the refine mode of the tensor-core search bounds its scoring error with it.
+__global__ void max_norm_kernel(const float* __restrict__ norms, int64_t n, uint32_t* __restrict__ out) {
+    float m = 0.f;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float v = norms[i];
+        m = (v > m) ? v : m;  // NaN norms are ignored here: such rows never enter a result anyway
+    }
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) m = fmaxf(m, __shfl_xor_sync(kFull, m, s));
+    if ((threadIdx.x & 31) == 0) atomicMax(out, f2ord(m));
+}
+
+int update_max_norm(const float* norms, int64_t n, uint32_t* max_norm_ord, cudaStream_t stream) {
+    if (n <= 0) return B2_OK;
+    const int blocks = (int)std::min<int64_t>((n + 255) / 256, 148 * 8);
+    max_norm_kernel<<<blocks, 256, 0, stream>>>(norms, n, max_norm_ord);
+    B2_AFTER_LAUNCH();
+    return B2_OK;
 }
 
 }  // namespace b2

@@ -49,6 +49,11 @@ struct PeerPush {
 int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metric, int64_t id_base, float* D,
                    int64_t* I, size_t out_stride, cudaStream_t stream, const float* qnorm = nullptr,
                    const PeerPush* push = nullptr);
+// refine mode of the tensor-core kernel: merge by approximate key, re-score the candidates near the cut exactly
+// (fp32 FMA dot of q_dev[q] with the stored row), emit the exact top-k.  partial: [nq][nlists][list_len].
+int merge_rescore(const uint64_t* partial, int nq, int nlists, int list_len, int k, int metric, float* D, int64_t* I,
+                  size_t out_stride, cudaStream_t stream, const float* qnorm, const float* q_dev, int d, const void* rows,
+                  size_t pitch_bytes, int dtype, const float* norms, const float* band, const PeerPush* push = nullptr);
 // merge of exchanged blocks that first waits (per query) for every part's flag to reach `epoch`
 int merge_shards_wait(int metric, int nq, int k, int nparts, const char* blocks, size_t part_stride_bytes,
                       const uint32_t* flags, size_t flag_stride_elems, uint32_t epoch, const int64_t* id_bases, float* D,
@@ -65,7 +70,7 @@ int prep_queries(const float* q_dev, int nq, int d, int nq_pad, int kp, int na, 
 bool gemm_path_supported(int64_t n, int d, int dtype, int k, int64_t nq);
 int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* norms,
                 const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream,
-                const PeerPush* push = nullptr, int query_parts = 0);
+                const PeerPush* push = nullptr, int query_parts = 0, const uint32_t* max_norm_ord = nullptr);
 // (D_parts, I_parts): [nparts][nq][k] -> [nq][k]
 // part g's lists start d_stride_bytes / i_stride_bytes after part g-1's (0 = natural [nparts][nq][k] arrays);
 // id_bases (host, nparts entries, optional): ids in the lists are local to their part, global = base + local.
@@ -85,6 +90,9 @@ int gather_rows(const void* rows, int64_t ntotal, size_t pitch_bytes, int d, int
 // keep[i] != 0 rows are compacted to the front preserving order; dst_index = exclusive prefix of keep
 int compact_rows(void* rows, size_t pitch_bytes, float* norms, const int64_t* src_of_dst, int64_t n_dst,
                  int64_t first_moved, cudaStream_t stream);
+
+// max_norm_ord = max(max_norm_ord, ordered image of max(norms[0..n)))
+int update_max_norm(const float* norms, int64_t n, uint32_t* max_norm_ord, cudaStream_t stream);
 
 // b2_mmr.cu ----------------------------------------------------------------
 int mmr_select(const float* q, int d, int nq, const float* cand_rows /*[nq][fetch_k][d]*/, const int64_t* cand_ids,

@@ -182,6 +182,139 @@ int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metri
     return B2_OK;
 }
 
+// ---------------------------------------------------------------- merge + exact re-scoring (filter and refine)
+// The tensor-core kernel in refine mode scores with ONE approximate product and emits, per (query, segment), every
+// candidate whose approximate key is within `band` of the segment's k-th best approximate key, where band = 2 x a
+// rigorous bound on |approximate - exact|.  The exact top-k of a query is then contained in
+//     { candidates with approximate key > (k-th best approximate key over all segments) - band },
+// typically k + a dozen entries.  One CTA per query: pass A finds the k-th best approximate key (chunked bitonic
+// sort as above); pass B re-scores exactly the candidates above the cut - one warp per candidate: fp32 FMA dot of
+// the fp32 query with the stored row, the arithmetic of the small-batch scan - and keeps the best k exact keys.
+// Replaces the same faiss routines as merge_partials_kernel; the scores it returns are fp32-exact with respect to
+// the stored rows on both row types.
+struct RescoreCtx {
+    const float* q;        // [nq][d] fp32 queries (device)
+    const char* rows;      // row store
+    const float* norms;    // |x|^2 per row (L2 keys)
+    const float* band;     // [nq]
+    size_t pitch_bytes;
+    int d;
+    int bf16;
+};
+
+__device__ __forceinline__ float warp_exact_dot(const RescoreCtx& c, const float* __restrict__ qrow, uint32_t row, int lane) {
+    const char* r = c.rows + (size_t)row * c.pitch_bytes;
+    float acc = 0.f;
+    if (c.bf16) {
+        for (int e0 = lane * 8; e0 < c.d; e0 += 256) {
+            const uint4 w = *reinterpret_cast<const uint4*>(r + (size_t)e0 * 2);  // 8 bf16; padding columns are zero
+            const float x[8] = {bf16lo(w.x), bf16hi(w.x), bf16lo(w.y), bf16hi(w.y),
+                                bf16lo(w.z), bf16hi(w.z), bf16lo(w.w), bf16hi(w.w)};
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+                if (e0 + e < c.d) acc = fmaf(x[e], __ldg(qrow + e0 + e), acc);
+        }
+    } else {
+        for (int e0 = lane * 4; e0 < c.d; e0 += 128) {
+            const float4 w = *reinterpret_cast<const float4*>(r + (size_t)e0 * 4);
+            const float x[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if (e0 + e < c.d) acc = fmaf(x[e], __ldg(qrow + e0 + e), acc);
+        }
+    }
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) acc += __shfl_xor_sync(kFull, acc, s);
+    return acc;
+}
+
+__global__ void __launch_bounds__(kMergeThreads) merge_rescore_kernel(const uint64_t* __restrict__ partial, int total,
+                                                                     int k, int kpad, int sort_n, int metric,
+                                                                     float* D, int64_t* I, size_t out_stride,
+                                                                     const float* __restrict__ qnorm,
+                                                                     const RescoreCtx ctx, const PeerPush push) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw);
+    const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint64_t* in = partial + (size_t)q * total;
+    const int cap = sort_n - kpad;
+    // ---- pass A: the k-th best APPROXIMATE key
+    for (int i = tid; i < kpad; i += kMergeThreads) buf[i] = B2_SENTINEL;
+    for (int off = 0; off < total; off += cap) {
+        for (int i = tid; i < cap; i += kMergeThreads) buf[kpad + i] = (off + i < total) ? in[off + i] : B2_SENTINEL;
+        block_bitonic_desc(buf, sort_n, tid, kMergeThreads);
+    }
+    __syncthreads();
+    const uint64_t kth = buf[k - 1];
+    // fewer than k candidates: everything is re-scored
+    const float cut = (cand_pos(kth) == kNoPos) ? -__builtin_huge_valf() : cand_key(kth) - ctx.band[q];
+    __syncthreads();
+    // ---- pass B: exact keys for the candidates above the cut, running best k of those
+    const float* qrow = ctx.q + (size_t)q * ctx.d;
+    for (int i = tid; i < kpad; i += kMergeThreads) buf[i] = B2_SENTINEL;
+    for (int off = 0; off < total; off += cap) {
+        __syncthreads();
+        for (int base = warp * 32; base < cap; base += kMergeThreads) {
+            const int i = base + lane;
+            const uint64_t c = (off + i < total) ? in[off + i] : B2_SENTINEL;
+            const uint32_t row = cand_pos(c);
+            const bool need = row != kNoPos && cand_key(c) > cut;
+            uint64_t outc = B2_SENTINEL;
+            unsigned m = __ballot_sync(kFull, need);
+            while (m) {
+                const int src = __ffs(m) - 1;
+                m &= m - 1;
+                const uint32_t r = __shfl_sync(kFull, row, src);
+                const float s = warp_exact_dot(ctx, qrow, r, lane);
+                if (lane == src) {
+                    const float key = (metric == B2_METRIC_IP) ? (s + 0.0f) : fmaf(2.f, s, -ctx.norms[r]);
+                    if (key > -FLT_MAX) outc = pack_cand(key, r);  // NaN / -FLT_MAX never enter, as everywhere else
+                }
+            }
+            buf[kpad + i] = outc;
+        }
+        block_bitonic_desc(buf, sort_n, tid, kMergeThreads);
+    }
+    __syncthreads();
+    for (int i = tid; i < k; i += kMergeThreads) emit_out(buf[i], q, i, k, metric, 0, D, I, out_stride, qnorm, push);
+    push_signal(q, push);
+}
+
+int merge_rescore(const uint64_t* partial, int nq, int nlists, int list_len, int k, int metric, float* D, int64_t* I,
+                  size_t out_stride, cudaStream_t stream, const float* qnorm, const float* q_dev, int d, const void* rows,
+                  size_t pitch_bytes, int dtype, const float* norms, const float* band, const PeerPush* push_in) {
+    const int kpad = next_pow2(k < 32 ? 32 : k);
+    const int total = nlists * list_len;
+    PeerPush push;
+    if (push_in != nullptr) {
+        push = *push_in;
+    } else {
+        push.nparts = 0;
+        push.epoch = 0;
+        push.nq_total = push.q_offset = 0;
+        for (int g = 0; g < kMaxPushPeers; ++g) {
+            push.block[g] = nullptr;
+            push.flag[g] = nullptr;
+        }
+    }
+    RescoreCtx ctx;
+    ctx.q = q_dev;
+    ctx.rows = static_cast<const char*>(rows);
+    ctx.norms = norms;
+    ctx.band = band;
+    ctx.pitch_bytes = pitch_bytes;
+    ctx.d = d;
+    ctx.bf16 = dtype == B2_DTYPE_BF16;
+    int sort_n = 2 * kpad;
+    const int want = next_pow2(total + kpad);
+    while (sort_n < want && sort_n < 4096) sort_n <<= 1;
+    const size_t smem = (size_t)sort_n * sizeof(uint64_t);
+    merge_rescore_kernel<<<nq, kMergeThreads, smem, stream>>>(partial, total, k, kpad, sort_n, metric, D, I, out_stride,
+                                                              qnorm, ctx, push);
+    B2_AFTER_LAUNCH();
+    return B2_OK;
+}
+
 // ---------------------------------------------------------------- shard lists
 // Candidate position = part * k + rank: parts are in global id order and each part's list
 // is already ordered lowest-id-first among equal keys, so "lower position first" is exactly

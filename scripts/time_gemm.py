@@ -67,7 +67,9 @@ def run_one(a, idx, q, torch):
         torch.cuda.synchronize()
         times.append(e0.elapsed_time(e1))
     ms = min(times)
-    products = int(os.environ.get("B2_GEMM_QUERY_PARTS", "2")) + (1 if a.dtype == "float32" else 0)
+    # tensor-core products issued per score: 1 under filter-and-refine (the default), else query parts (+1 on fp32 rows)
+    refine = os.environ.get("B2_GEMM_REFINE", "1") != "0" and "B2_GEMM_QUERY_PARTS" not in os.environ
+    products = 1 if refine else int(os.environ.get("B2_GEMM_QUERY_PARTS", "2")) + (1 if a.dtype == "float32" else 0)
     nq_pad = (a.nq + 127) // 128 * 128
     useful = 2.0 * a.nq * a.rows * a.dim / (ms * 1e-3) / 1e12
     mma = 2.0 * nq_pad * a.rows * a.dim * products / (ms * 1e-3) / 1e12
@@ -81,7 +83,7 @@ def run_one(a, idx, q, torch):
     maxrel = float(((Ds - D[s]).abs() / Ds.abs().clamp_min(1e-6)).max().item())
     print(json.dumps({"rows": a.rows, "dim": a.dim, "nq": a.nq, "k": a.k, "dtype": a.dtype, "metric": a.metric,
                       "ms": ms, "all_ms": times, "qps": a.nq / (ms * 1e-3), "useful_tflops": useful,
-                      "mma_tflops": mma, "products": products, "swizzle": os.environ.get("B2_GEMM_SWIZZLE", "auto"), "mixed": os.environ.get("B2_GEMM_MIXED", "default"), "cta_group": os.environ.get("B2_GEMM_CTA_GROUP", "default"), "ids_equal_scan_sample": same,
+                      "mma_tflops": mma, "products": products, "refine": refine, "swizzle": os.environ.get("B2_GEMM_SWIZZLE", "auto"), "mixed": os.environ.get("B2_GEMM_MIXED", "default"), "cta_group": os.environ.get("B2_GEMM_CTA_GROUP", "default"), "ids_equal_scan_sample": same,
                       "max_rel_score_diff_vs_scan": maxrel}), flush=True)
 
 

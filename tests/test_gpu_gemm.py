@@ -32,7 +32,9 @@ def _data(n, d, nq, normalize, seed=0):
 
 
 def _launched_tensor_kernel(fn):
-    """Run fn() and return (result, kernel launches): the tensor path is prep + gemm + merge = 3 launches."""
+    """Run fn() and return (result, kernel launches).  One pass for the whole batch: the tensor-core scan is prep +
+    scan + merge = 3 launches, the GEMM path in its default filter-and-refine mode 2 x prep + band + gemm + fix-up +
+    merge = 6 (3 with an explicit number of query parts); ceil(nq/16) FFMA scan passes would be 2 per pass."""
     from nv_genai_b200 import _native
 
     _native.launch_count_reset()
@@ -48,7 +50,7 @@ def test_fp32_store_matches_blas_oracle(metric, nq, k):
     idx = _mk(metric, d)
     idx.add(x)
     (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, k))
-    assert launches == 3, launches  # one pass for the whole batch, not ceil(nq/16) scan passes
+    assert launches in (3, 6), launches  # one pass for the whole batch, not ceil(nq/16) scan passes
     Dr, Ir = flat.search_blas(x, q, k, metric)
     assert_parity(D, I, Dr, Ir, x, q, metric_ip=(metric == flat.METRIC_IP))
     D64, I64 = flat.search_f64(x, q, k, metric)
@@ -78,7 +80,7 @@ def test_bf16_store_matches_oracle_on_rounded_rows(metric):
     idx = _mk(metric, d, "bfloat16")
     idx.add(x)
     (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, k))
-    assert launches == 3
+    assert launches in (3, 6)
     xr = flat.round_bf16(x)
     Dr, Ir = flat.search_blas(xr, q, k, metric)
     assert_parity(D, I, Dr, Ir, xr, q, metric_ip=(metric == flat.METRIC_IP))
@@ -200,7 +202,7 @@ def test_medium_batch_rides_one_tensor_scan_pass_when_k_is_small(dtype, nq, k):
     idx = _mk(flat.METRIC_IP, d, dtype)
     idx.add(x)
     (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, k))
-    assert launches == 3, launches
+    assert launches in (3, 6), launches
     xr = flat.round_bf16(x) if dtype == "bfloat16" else x
     Dr, Ir = flat.search_f64(xr, q, k, flat.METRIC_IP)
     assert_parity(D, I, Dr.astype(np.float32), Ir, xr, q, metric_ip=True)
