@@ -140,10 +140,47 @@ B2_API int b2_index_remove_ids(b2_index* h, int64_t n, const int64_t* ids, int64
  * appends other's rows, then empties other. */
 B2_API int b2_index_merge_from(b2_index* dst, b2_index* src);
 
+/* Relevance-score functions of langchain's FAISS (_euclidean_relevance_score_fn,
+ * _cosine_relevance_score_fn, _max_inner_product_relevance_score_fn), selected there by distance_strategy. */
+#define B2_REL_NONE 0
+#define B2_REL_EUCLIDEAN 1         /* 1 - d / sqrt(2), d = squared L2 distance as returned */
+#define B2_REL_COSINE 2            /* 1 - d */
+#define B2_REL_MAX_INNER_PRODUCT 3 /* d > 0 ? 1 - d : -d */
+
+/* Replaces the selection langchain's FAISS.similarity_search_with_score_by_vector and
+ * similarity_search_with_relevance_scores run on the host after index.search (thresholded retrievers:
+ * RetrievalAugmentedGeneration/examples/nvidia_api_catalog/chains.py:122,162,
+ * examples/multi_turn_rag/chains.py:160-165, experimental/oran-chatbot-multimodal/retriever/retriever.py:69-71;
+ * the threshold comes from RetrievalAugmentedGeneration/common/configuration.py:146):
+ * searches fetch_k results per query (the caller passes fetch_k = k when there is no metadata filter, as upstream
+ * does), then, in search order,
+ *   1. drops padding (-1) and rows whose bit in `allow` is clear (allow = NULL: no metadata filter; bit i of word
+ *      i / 32 = row i; allow_bits = rows covered, rows beyond it are dropped),
+ *   2. if use_raw_threshold: keeps score >= raw_threshold (inner product) or score <= raw_threshold (L2),
+ *   3. cuts the list at k,
+ *   4. if relevance_kind != B2_REL_NONE: keeps relevance(score) >= relevance_threshold,
+ * and writes the survivors' RAW scores and ids to D / I (nq x k, padded with -1 / the metric's worst score) and
+ * their number to counts (nq, int32; may be NULL).  Comparisons are in double on the widened fp32 score, like
+ * the numpy 1.26 the reference pins.  q, allow, D, I and counts each follow their *_where argument. */
+B2_API int b2_index_search_filtered(b2_index* h, int64_t nq, const float* q, int q_where, int k, int fetch_k,
+                                    const uint32_t* allow, int64_t allow_bits, int allow_where,
+                                    int use_raw_threshold, double raw_threshold, int relevance_kind,
+                                    double relevance_threshold, float* D, int64_t* I, int32_t* counts, int out_where,
+                                    void* stream);
+
+/* The same selection applied to results already on the device (nq x fetch_k, as b2_index_search wrote them):
+ * all pointers are device pointers.  metric: B2_METRIC_IP / B2_METRIC_L2. */
+B2_API int b2_filter_results(int metric, int64_t nq, int fetch_k, int k, const float* D_in, const int64_t* I_in,
+                             const uint32_t* allow, int64_t allow_bits, int use_raw_threshold, double raw_threshold,
+                             int relevance_kind, double relevance_threshold, float* D_out, int64_t* I_out,
+                             int32_t* counts, int device, void* stream);
+
 /* Engine options without a faiss counterpart.  "gemm_query_parts": how the query enters the tensor-core kernel
- * for batches of >= 20 queries: 2 (default) = split into hi + lo parts, so scores are exact with respect to the
- * stored rows (fp32-faithful on fp32 rows); 1 = single part: about 1.6x faster on bf16 rows, scores then carry the
- * bf16 (or tf32) rounding of the query, recall@100 0.9952 instead of 0.9970 at 10M x 1024 bf16; 0 = default. */
+ * for batches of >= 20 queries.  0 (default) = filter and refine: one approximate tensor-core product per score,
+ * every candidate within a rigorous error band of the k-th best is re-scored exactly in fp32, so results equal
+ * the all-exact arithmetic; 2 = all-exact tensor-core arithmetic (query split into hi + lo parts; tf32 main +
+ * bf16 correction product on fp32 rows); 1 = single part without re-scoring: scores then carry the bf16 (or tf32)
+ * rounding of the query, recall@100 0.9952 instead of 0.9970 at 10M x 1024 bf16. */
 B2_API int b2_index_set_option(b2_index* h, const char* name, int64_t value);
 
 /* Replaces index.reset(). */

@@ -18,11 +18,12 @@ DTYPE_F32, DTYPE_BF16 = 0, 1
 HOST, DEVICE = 0, 1
 ADD_NORMALIZE = 1
 MAX_K = 2048
+REL_NONE, REL_EUCLIDEAN, REL_COSINE, REL_MAX_INNER_PRODUCT = 0, 1, 2, 3  # langchain's relevance-score functions
 
 # Every symbol include/b2_flat.h declares (tests check the library exports all of them).
 SYMBOLS = [
     "b2_index_create", "b2_index_destroy", "b2_index_ntotal", "b2_index_d", "b2_index_metric", "b2_index_dtype",
-    "b2_index_device", "b2_index_add", "b2_index_search", "b2_index_search_static", "b2_index_reconstruct_batch", "b2_index_remove_ids",
+    "b2_index_device", "b2_index_add", "b2_index_search", "b2_index_search_static", "b2_index_search_filtered", "b2_filter_results", "b2_index_reconstruct_batch", "b2_index_remove_ids",
     "b2_index_merge_from", "b2_index_set_option", "b2_index_reset", "b2_index_mmr", "b2_merge_shard_lists", "b2_merge_shard_lists_packed", "b2_index_search_push", "b2_merge_shard_lists_wait", "b2_normalize_l2",
     "b2_synth_fill", "b2_launch_count", "b2_launch_count_reset", "b2_prof_enable", "b2_prof_read", "b2_prof_read_kernel", "b2_last_error",
     "b2_version",
@@ -54,6 +55,11 @@ def _load() -> ctypes.CDLL:
     L.b2_index_search.argtypes = [vp, i64, vp, i32, i32, vp, vp, i32, vp]
     L.b2_index_search_static.argtypes = [vp, i64, vp, i32, vp, vp, vp]
     L.b2_index_search_static.restype = i32
+    f64 = ctypes.c_double
+    L.b2_index_search_filtered.argtypes = [vp, i64, vp, i32, i32, i32, vp, i64, i32, i32, f64, i32, f64, vp, vp, vp, i32, vp]
+    L.b2_index_search_filtered.restype = i32
+    L.b2_filter_results.argtypes = [i32, i64, i32, i32, vp, vp, vp, i64, i32, f64, i32, f64, vp, vp, vp, i32, vp]
+    L.b2_filter_results.restype = i32
     L.b2_index_reconstruct_batch.argtypes = [vp, i64, vp, i32, vp, i32, vp]
     L.b2_index_remove_ids.argtypes = [vp, i64, vp, ctypes.POINTER(i64)]
     L.b2_index_merge_from.argtypes = [vp, vp]

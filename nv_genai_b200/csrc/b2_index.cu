@@ -595,6 +595,135 @@ int b2_index_search(b2_index* h, int64_t nq, const float* q, int q_where, int k,
     return rc;
 }
 
+static int check_filter_args(const char* who, int64_t nq, int k, int fetch_k, int relevance_kind) {
+    if (nq < 0 || k <= 0 || fetch_k < k) {
+        set_error("%s: bad arguments (nq=%lld, k=%d, fetch_k=%d; fetch_k must be >= k)", who, (long long)nq, k, fetch_k);
+        return B2_ERR_INVALID;
+    }
+    if (relevance_kind < B2_REL_NONE || relevance_kind > B2_REL_MAX_INNER_PRODUCT) {
+        set_error("%s: unknown relevance function %d", who, relevance_kind);
+        return B2_ERR_INVALID;
+    }
+    if (fetch_k > B2_MAX_K) {
+        set_error("%s: fetch_k=%d exceeds B2_MAX_K=%d", who, fetch_k, B2_MAX_K);
+        return B2_ERR_UNSUPPORTED;
+    }
+    return B2_OK;
+}
+
+int b2_index_search_filtered(b2_index* h, int64_t nq, const float* q, int q_where, int k, int fetch_k,
+                             const uint32_t* allow, int64_t allow_bits, int allow_where, int use_raw_threshold,
+                             double raw_threshold, int relevance_kind, double relevance_threshold, float* D, int64_t* I,
+                             int32_t* counts, int out_where, void* stream_) {
+    B2_TRY(check_handle(h));
+    B2_TRY(check_filter_args("b2_index_search_filtered", nq, k, fetch_k, relevance_kind));
+    if (nq > 0 && (q == nullptr || D == nullptr || I == nullptr)) {
+        set_error("b2_index_search_filtered: null pointer");
+        return B2_ERR_INVALID;
+    }
+    if (allow != nullptr && allow_bits < 0) {
+        set_error("b2_index_search_filtered: allow_bits=%lld", (long long)allow_bits);
+        return B2_ERR_INVALID;
+    }
+    if (nq == 0) return B2_OK;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    std::shared_lock<std::shared_mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    if (!g.ok) {
+        set_error("cannot select device %d", h->device);
+        return B2_ERR_CUDA;
+    }
+    // one block: [queries if host][fetch_k results I, D][k results I, D, counts if host][allow words if host]
+    auto al = [](size_t v) { return (v + 255) / 256 * 256; };
+    const size_t q_bytes = q_where == B2_HOST ? al((size_t)nq * h->d * sizeof(float)) : 0;
+    const size_t nfetch = (size_t)nq * fetch_k, nres = (size_t)nq * k;
+    const size_t fi_bytes = al(nfetch * 8), fd_bytes = al(nfetch * 4);
+    const size_t oi_bytes = out_where == B2_HOST ? al(nres * 8) : 0, od_bytes = out_where == B2_HOST ? al(nres * 4) : 0;
+    const size_t oc_bytes = out_where == B2_HOST ? al((size_t)nq * 4) : 0;
+    const size_t allow_words = allow != nullptr ? (size_t)((allow_bits + 31) / 32) : 0;
+    const size_t aw_bytes = (allow != nullptr && allow_where == B2_HOST) ? al(allow_words * 4 + 4) : 0;
+    char* blk = nullptr;
+    B2_CUDA_TRY(cudaMallocAsync(&blk, q_bytes + fi_bytes + fd_bytes + oi_bytes + od_bytes + oc_bytes + aw_bytes + 256, stream));
+    char* cur = blk;
+    float* q_tmp = reinterpret_cast<float*>(cur);
+    cur += q_bytes;
+    int64_t* FI = reinterpret_cast<int64_t*>(cur);
+    cur += fi_bytes;
+    float* FD = reinterpret_cast<float*>(cur);
+    cur += fd_bytes;
+    int64_t* OI = reinterpret_cast<int64_t*>(cur);
+    cur += oi_bytes;
+    float* OD = reinterpret_cast<float*>(cur);
+    cur += od_bytes;
+    int32_t* OC = reinterpret_cast<int32_t*>(cur);
+    cur += oc_bytes;
+    uint32_t* AW = reinterpret_cast<uint32_t*>(cur);
+    int rc = B2_OK;
+    cudaError_t e = cudaSuccess;
+    const float* q_dev = q;
+    if (q_where == B2_HOST) {
+        e = cudaMemcpyAsync(q_tmp, q, (size_t)nq * h->d * sizeof(float), cudaMemcpyHostToDevice, stream);
+        q_dev = q_tmp;
+    }
+    const uint32_t* allow_dev = allow;
+    if (e == cudaSuccess && aw_bytes != 0) {
+        e = cudaMemcpyAsync(AW, allow, allow_words * 4, cudaMemcpyHostToDevice, stream);
+        allow_dev = AW;
+    }
+    if (e != cudaSuccess) {
+        set_error("b2_index_search_filtered: input copy failed: %s", cudaGetErrorString(e));
+        rc = B2_ERR_CUDA;
+    }
+    if (rc == B2_OK) rc = search_device(h, nq, q_dev, fetch_k, FD, FI, stream);
+    float* D_dev = out_where == B2_HOST ? OD : D;
+    int64_t* I_dev = out_where == B2_HOST ? OI : I;
+    int32_t* C_dev = out_where == B2_HOST ? OC : counts;
+    if (rc == B2_OK)
+        rc = filter_results(FD, FI, nq, fetch_k, k, h->metric, allow_dev, allow_bits, use_raw_threshold, raw_threshold,
+                            relevance_kind, relevance_threshold, D_dev, I_dev, C_dev, stream);
+    if (rc == B2_OK && out_where == B2_HOST) {
+        e = cudaMemcpyAsync(I, OI, nres * 8, cudaMemcpyDeviceToHost, stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(D, OD, nres * 4, cudaMemcpyDeviceToHost, stream);
+        if (e == cudaSuccess && counts != nullptr) e = cudaMemcpyAsync(counts, OC, (size_t)nq * 4, cudaMemcpyDeviceToHost, stream);
+        if (e != cudaSuccess) {
+            set_error("b2_index_search_filtered: result copy failed: %s", cudaGetErrorString(e));
+            rc = B2_ERR_CUDA;
+        }
+    }
+    cudaFreeAsync(blk, stream);
+    if (rc == B2_OK && out_where == B2_HOST) {
+        e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess) {
+            set_error("b2_index_search_filtered: %s", cudaGetErrorString(e));
+            rc = B2_ERR_CUDA;
+        }
+    }
+    return rc;
+}
+
+int b2_filter_results(int metric, int64_t nq, int fetch_k, int k, const float* D_in, const int64_t* I_in,
+                      const uint32_t* allow, int64_t allow_bits, int use_raw_threshold, double raw_threshold,
+                      int relevance_kind, double relevance_threshold, float* D_out, int64_t* I_out, int32_t* counts,
+                      int device, void* stream_) {
+    B2_TRY(check_filter_args("b2_filter_results", nq, k, fetch_k, relevance_kind));
+    if (metric != B2_METRIC_IP && metric != B2_METRIC_L2) {
+        set_error("b2_filter_results: unknown metric %d", metric);
+        return B2_ERR_INVALID;
+    }
+    if (nq > 0 && (D_in == nullptr || I_in == nullptr || D_out == nullptr || I_out == nullptr)) {
+        set_error("b2_filter_results: null pointer");
+        return B2_ERR_INVALID;
+    }
+    if (nq == 0) return B2_OK;
+    DeviceGuard g(device);
+    if (!g.ok) {
+        set_error("cannot select device %d", device);
+        return B2_ERR_CUDA;
+    }
+    return filter_results(D_in, I_in, nq, fetch_k, k, metric, allow, allow_bits, use_raw_threshold, raw_threshold,
+                          relevance_kind, relevance_threshold, D_out, I_out, counts, static_cast<cudaStream_t>(stream_));
+}
+
 int b2_index_reconstruct_batch(b2_index* h, int64_t n, const int64_t* ids, int ids_where, float* out, int out_where,
                                void* stream_) {
     B2_TRY(check_handle(h));

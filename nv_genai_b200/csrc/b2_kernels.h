@@ -59,6 +59,13 @@ int merge_shards_wait(int metric, int nq, int k, int nparts, const char* blocks,
                       const uint32_t* flags, size_t flag_stride_elems, uint32_t epoch, const int64_t* id_bases, float* D,
                       int64_t* I, cudaStream_t stream);
 
+// b2_filter.cu -------------------------------------------------------------
+// langchain's post-search selection (metadata filter as a row bitmask, raw / relevance thresholds, cut at k) over
+// device results [nq][fetch_k] -> [nq][k] + counts[nq]; see include/b2_flat.h: b2_index_search_filtered.
+int filter_results(const float* D_in, const int64_t* I_in, int64_t nq, int fetch_k, int k, int metric,
+                   const uint32_t* allow, int64_t allow_bits, int use_raw, double raw_thr, int rel_kind, double rel_thr,
+                   float* D_out, int64_t* I_out, int32_t* counts, cudaStream_t stream);
+
 // b2_gemm.cu ---------------------------------------------------------------
 // Tensor-core search for batches of >= 20 queries (faiss's BLAS threshold), k <= 128.
 // q [nq][d] fp32 -> A [na][nq_pad][kp] operand parts (bf16 hi/lo, or fp32 words holding tf32 hi/lo), zero padded;

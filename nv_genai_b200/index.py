@@ -172,6 +172,58 @@ class IndexFlat:
         N.check(N.lib.b2_index_search(self._h, b.n, b.ptr, N.DEVICE, int(k), D.data_ptr(), I.data_ptr(), N.DEVICE,
                                       _stream_for(self.device)))
 
+    def upload_mask(self, words: np.ndarray):
+        """A row bitmask (uint32 words, bit i of word i // 32 = row i) as a CUDA int32 tensor on the index's device,
+        the form `search_filtered(allow=...)` takes without a copy per call."""
+        import torch
+
+        return torch.from_numpy(np.ascontiguousarray(words, dtype=np.uint32).view(np.int32)).to(f"cuda:{self.device}")
+
+    def search_filtered(self, x, k: int, fetch_k: Optional[int] = None, allow=None, score_threshold=None,
+                        relevance: int = N.REL_NONE, relevance_threshold: float = 0.0):
+        """`search(x, fetch_k)` followed, on the device, by the selection langchain's FAISS runs on the host
+        (b2_index_search_filtered in include/b2_flat.h): row bitmask `allow` (uint32 words, numpy or CUDA tensor; None =
+        no metadata filter), raw `score_threshold` (>= for inner product, <= for L2), cut at k, then the relevance
+        threshold if `relevance` names one of langchain's relevance functions.
+
+        Returns (D [n, k] raw scores, I [n, k], counts [n] int32): the first counts[i] entries of row i are results."""
+        b = _Buf(x, self.d, self.device, "search")
+        k = int(k)
+        fetch_k = k if fetch_k is None else int(fetch_k)
+        assert k > 0, "k must be positive"
+        use_raw = score_threshold is not None
+        raw = float(score_threshold) if use_raw else 0.0
+        a_ptr, a_bits, a_where = None, 0, N.DEVICE
+        if allow is not None:
+            if _is_tensor(allow):
+                t = _torch()
+                assert allow.is_cuda and allow.dtype in (t.int32, t.uint32) and allow.is_contiguous()
+                a_ptr, a_bits, a_where = allow.data_ptr(), allow.numel() * 32, N.DEVICE
+            else:
+                allow = np.ascontiguousarray(allow, dtype=np.uint32)
+                a_ptr, a_bits, a_where = allow.ctypes.data, allow.size * 32, N.HOST
+        if b.is_tensor:
+            t = _torch()
+            D = t.empty((b.n, k), dtype=t.float32, device=b.obj.device)
+            I = t.empty((b.n, k), dtype=t.int64, device=b.obj.device)
+            C = t.empty((b.n,), dtype=t.int32, device=b.obj.device)
+            if a_where == N.HOST and a_ptr is not None:  # device outputs take a device mask
+                allow = t.from_numpy(allow.view(np.int32)).to(b.obj.device)
+                a_ptr, a_where = allow.data_ptr(), N.DEVICE
+            N.check(N.lib.b2_index_search_filtered(self._h, b.n, b.ptr, N.DEVICE, k, fetch_k, a_ptr, a_bits, a_where,
+                                                   1 if use_raw else 0, raw, int(relevance), float(relevance_threshold),
+                                                   D.data_ptr(), I.data_ptr(), C.data_ptr(), N.DEVICE,
+                                                   _stream_for(self.device)))
+            return D, I, C
+        D = np.empty((b.n, k), dtype=np.float32)
+        I = np.empty((b.n, k), dtype=np.int64)
+        C = np.empty((b.n,), dtype=np.int32)
+        N.check(N.lib.b2_index_search_filtered(self._h, b.n, b.ptr, b.where, k, fetch_k, a_ptr, a_bits, a_where,
+                                               1 if use_raw else 0, raw, int(relevance), float(relevance_threshold),
+                                               D.ctypes.data, I.ctypes.data, C.ctypes.data, N.HOST,
+                                               _stream_for(self.device)))
+        return D, I, C
+
     # ---- index.reconstruct*
     def reconstruct_batch(self, ids):
         if _is_tensor(ids) and ids.is_cuda:

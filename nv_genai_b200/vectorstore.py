@@ -68,6 +68,11 @@ class FAISS:
         if self.distance_strategy != DistanceStrategy.EUCLIDEAN_DISTANCE and self._normalize_L2:
             warnings.warn(f"Normalizing L2 is not applicable for metric type: {self.distance_strategy}")
 
+    def __getstate__(self):
+        state = dict(self.__dict__)
+        state.pop("_filter_masks", None)  # device bitmasks are a cache, not state
+        return state
+
     # ------------------------------------------------------------------ embeddings
     @property
     def embeddings(self) -> Optional[Embeddings]:
@@ -127,6 +132,7 @@ class FAISS:
             return []
         vector = embeddings if _is_array(embeddings) else np.array(embeddings, dtype=np.float32)
         starting_len = len(self.index_to_docstore_id)
+        self.__dict__["_mutations"] = self.__dict__.get("_mutations", 0) + 1  # cached filter bitmasks are stale now
         self.index.add(vector, normalize=self._normalize_L2)
         self.docstore.add({id_: doc for id_, doc in zip(ids, documents)})
         self.index_to_docstore_id.update({starting_len + j: id_ for j, id_ in enumerate(ids)})
@@ -192,11 +198,88 @@ class FAISS:
             raise ValueError(f"Could not find document for id {_id}, got {doc}")
         return doc
 
+    # ---- metadata filters as row bitmasks on the device
+    #: dict filters are turned into a device bitmask automatically up to this many rows (one pass of Python over the
+    #: docstore per distinct filter); above it only after an explicit `prepare_filter(filter)`.
+    device_filter_auto_rows = 200_000
+
+    @staticmethod
+    def _filter_key(filter: Any) -> Optional[str]:
+        if not isinstance(filter, dict):
+            return None  # callables are evaluated on the host, hit by hit, as upstream does
+        try:
+            return repr(sorted((str(key), repr(value)) for key, value in filter.items()))
+        except Exception:
+            return None
+
+    def _store_stamp(self) -> Tuple[int, int]:
+        return (self.__dict__.get("_mutations", 0), len(self.index_to_docstore_id))
+
+    def clear_filter_cache(self) -> None:
+        """Drop the cached row bitmasks (call it after editing Document.metadata in place)."""
+        self.__dict__["_filter_masks"] = {}
+
+    def prepare_filter(self, filter: Dict[str, Any]):
+        """Evaluate a dict metadata filter once over the whole docstore and keep the result on the device as one bit
+        per row; later searches with an equal filter (single or `search_batch`) select on the device.  Returns the
+        mask (CUDA int32 tensor of ceil(n / 32) words)."""
+        key = self._filter_key(filter)
+        if key is None:
+            raise ValueError("prepare_filter takes a dict of metadata; callables are evaluated per hit on the host")
+        base = getattr(self.index, "wrapped", self.index)
+        n = len(self.index_to_docstore_id)
+        filter_func = self._build_filter(filter)
+        bits = np.zeros(((n + 31) // 32) * 32, dtype=np.uint8)
+        docs = self.docstore._dict if hasattr(self.docstore, "_dict") else None
+        for i in range(n):
+            _id = self.index_to_docstore_id[i]
+            doc = docs.get(_id) if docs is not None else self.docstore.search(_id)
+            if isinstance(doc, Document) and filter_func(doc.metadata):
+                bits[i] = 1
+        words = np.packbits(bits.reshape(-1, 32), axis=1, bitorder="little").view("<u4").reshape(-1)
+        mask = base.upload_mask(words.astype(np.uint32))
+        cache = self.__dict__.setdefault("_filter_masks", {})
+        if len(cache) >= 16:
+            cache.pop(next(iter(cache)))
+        cache[key] = (self._store_stamp(), mask)
+        return mask
+
+    def _device_mask(self, filter: Any, build: bool):
+        """The cached bitmask of `filter` if it is still valid, building it when allowed; else None."""
+        key = self._filter_key(filter)
+        if key is None:
+            return None
+        hit = self.__dict__.get("_filter_masks", {}).get(key)
+        if hit is not None and hit[0] == self._store_stamp():
+            return hit[1]
+        if build and (hit is not None or len(self.index_to_docstore_id) <= self.device_filter_auto_rows):
+            return self.prepare_filter(filter)
+        return None
+
+    def _raw_threshold_is_ge(self) -> bool:
+        return self.distance_strategy in (DistanceStrategy.MAX_INNER_PRODUCT, DistanceStrategy.JACCARD)
+
+    def _device_selection_ok(self, base: Any) -> bool:
+        """The device applies a raw threshold as `>=` on inner-product indexes and `<=` on L2 indexes; upstream picks the
+        direction from distance_strategy.  They agree except for odd pairings (say COSINE over IndexFlatIP)."""
+        return self._raw_threshold_is_ge() == (base.metric_type == _ix.METRIC_INNER_PRODUCT)
+
     def similarity_search_with_score_by_vector(self, embedding: List[float], k: int = 4,
                                                filter: Optional[Union[Callable, Dict[str, Any]]] = None,
                                                fetch_k: int = 20, **kwargs: Any) -> List[Tuple[Document, float]]:
         """Documents closest to `embedding` with their raw score (squared L2, or inner product)."""
         vector = self._query_matrix(embedding, normalize=True)
+        score_threshold = kwargs.get("score_threshold")
+        base = self.index
+        if isinstance(base, _ix.IndexFlat) and (filter is not None or score_threshold is not None) \
+                and (score_threshold is None or self._device_selection_ok(base)):
+            # selection on the device: metadata filter as a row bitmask, raw threshold, cut at k
+            mask = self._device_mask(filter, build=True) if filter is not None else None
+            if filter is None or mask is not None:
+                n_fetch = k if filter is None else fetch_k
+                if n_fetch >= k:
+                    D, I, C = base.search_filtered(vector, k, n_fetch, allow=mask, score_threshold=score_threshold)
+                    return [(self._doc_at(int(I[0][j])), D[0][j]) for j in range(int(C[0]))]
         scores, indices = self.index.search(vector, k if filter is None else fetch_k)
         docs: List[Tuple[Document, float]] = []
         filter_func = self._build_filter(filter) if filter is not None else None
@@ -246,15 +329,51 @@ class FAISS:
             self.index = proxy.wrapped
             proxy.close()
 
-    def search_batch(self, X: Any, k: int = 4):
-        """Batched fast path: X [B, d] (numpy or torch CUDA) -> (D [B, k], I [B, k]); no Python per row."""
+    def _relevance_kind(self) -> int:
+        """The device's code for the relevance function `_select_relevance_score_fn` would pick."""
+        from . import _native as N
+
+        if self.override_relevance_score_fn is not None:
+            raise NotImplementedError("a custom relevance_score_fn cannot run on the device; use the per-query API")
+        if self.distance_strategy == DistanceStrategy.MAX_INNER_PRODUCT:
+            return N.REL_MAX_INNER_PRODUCT
+        if self.distance_strategy == DistanceStrategy.EUCLIDEAN_DISTANCE:
+            return N.REL_EUCLIDEAN
+        if self.distance_strategy == DistanceStrategy.COSINE:
+            return N.REL_COSINE
+        raise ValueError("Unknown distance strategy, must be cosine, max_inner_product, or euclidean")
+
+    def search_batch(self, X: Any, k: int = 4, filter: Optional[Dict[str, Any]] = None, fetch_k: int = 20,
+                     score_threshold: Optional[float] = None, relevance_score_threshold: Optional[float] = None):
+        """Batched fast path: X [B, d] (numpy or torch CUDA) -> (D [B, k], I [B, k]); no Python per row.
+
+        With `filter` (a dict of metadata, turned into a device bitmask by `prepare_filter`), `score_threshold` (raw
+        score, as `similarity_search_with_score` takes it) or `relevance_score_threshold` (as a
+        `similarity_score_threshold` retriever takes it) the selection langchain runs per query on the host runs on
+        the device for the whole batch, and the call returns (D, I, counts): row i holds counts[i] results, raw scores."""
         if self._normalize_L2:
             if _ix._is_tensor(X) and X.is_cuda:
                 X = X.detach().float().contiguous().clone()
             else:
                 X = np.array(X, dtype=np.float32, copy=True)
             _ix.normalize_L2(X)
-        return self.index.search(X, k)
+        if filter is None and score_threshold is None and relevance_score_threshold is None:
+            return self.index.search(X, k)
+        from . import _native as N
+
+        base = getattr(self.index, "wrapped", self.index)
+        if score_threshold is not None and not self._device_selection_ok(base):
+            raise NotImplementedError("raw score_threshold direction of this distance_strategy does not match the index metric")
+        mask = None
+        if filter is not None:
+            if self._filter_key(filter) is None:
+                raise ValueError("search_batch takes a dict metadata filter")
+            mask = self._device_mask(filter, build=True)
+            if mask is None:
+                mask = self.prepare_filter(filter)
+        rel = self._relevance_kind() if relevance_score_threshold is not None else N.REL_NONE
+        return base.search_filtered(X, k, k if filter is None else fetch_k, allow=mask, score_threshold=score_threshold,
+                                    relevance=rel, relevance_threshold=(relevance_score_threshold or 0.0))
 
     def search(self, query: str, search_type: str, **kwargs: Any) -> List[Document]:
         """langchain_core VectorStore.search dispatch."""
@@ -362,6 +481,7 @@ class FAISS:
             raise ValueError(f"Some specified ids do not exist in the current store. Ids not found: {missing_ids}")
         reversed_index = {id_: idx for idx, id_ in self.index_to_docstore_id.items()}
         index_to_delete = {reversed_index[id_] for id_ in ids}
+        self.__dict__["_mutations"] = self.__dict__.get("_mutations", 0) + 1
         self.index.remove_ids(np.fromiter(index_to_delete, dtype=np.int64))
         self.docstore.delete(ids)
         remaining_ids = [id_ for i, id_ in sorted(self.index_to_docstore_id.items()) if i not in index_to_delete]
@@ -381,6 +501,8 @@ class FAISS:
         clash = {tid for _, tid, _ in full_info}.intersection(self.docstore._dict)
         if clash:
             raise ValueError(f"Tried to add ids that already exist: {clash}")
+        self.__dict__["_mutations"] = self.__dict__.get("_mutations", 0) + 1
+        target.__dict__["_mutations"] = target.__dict__.get("_mutations", 0) + 1
         self.index.merge_from(getattr(target.index, "wrapped", target.index))
         self.docstore.add({_id: doc for _, _id, doc in full_info})
         self.index_to_docstore_id.update({index: _id for index, _id, _ in full_info})

@@ -18,7 +18,7 @@ from __future__ import annotations
 import ctypes
 import os
 import subprocess
-from typing import List, Sequence, Tuple
+from typing import List, Optional, Sequence, Tuple
 
 import numpy as np
 
@@ -323,3 +323,55 @@ def euclidean_relevance(d: float) -> float:
 def max_inner_product_relevance(d: float) -> float:
     """langchain VectorStore._max_inner_product_relevance_score_fn."""
     return 1.0 - d if d > 0 else -1.0 * d
+
+
+def cosine_relevance(d: float) -> float:
+    """langchain VectorStore._cosine_relevance_score_fn."""
+    return 1.0 - d
+
+
+REL_NONE, REL_EUCLIDEAN, REL_COSINE, REL_MAX_INNER_PRODUCT = 0, 1, 2, 3
+_REL_FN = {REL_EUCLIDEAN: euclidean_relevance, REL_COSINE: cosine_relevance,
+           REL_MAX_INNER_PRODUCT: max_inner_product_relevance}
+
+
+def select_hits(D: np.ndarray, I: np.ndarray, k: int, metric: int, allow: Optional[np.ndarray] = None,
+                raw_threshold: Optional[float] = None, relevance: int = REL_NONE, relevance_threshold: float = 0.0):
+    """What langchain's FAISS does between index.search and the Document list (thresholded retrievers at
+    /root/reference/RetrievalAugmentedGeneration/examples/nvidia_api_catalog/chains.py:122,162), on index positions:
+
+        similarity_search_with_score_by_vector: skip -1; keep hits passing the metadata filter (`allow[i]`, a bool per
+        row); keep score >= thr (inner product) or <= thr (L2); docs[:k]
+        similarity_search_with_relevance_scores: keep relevance(score) >= thr
+
+    Comparisons on float(score), i.e. in double, as numpy 1.26 does for np.float32 against a Python float.
+    Returns (D [nq, k] raw scores, I [nq, k], counts [nq]) padded like index.search pads."""
+    D = np.atleast_2d(D)
+    I = np.atleast_2d(I)
+    nq, fetch_k = I.shape
+    pad = -FLT_MAX if metric == METRIC_IP else FLT_MAX
+    Do = np.full((nq, k), pad, dtype=np.float32)
+    Io = np.full((nq, k), -1, dtype=np.int64)
+    C = np.zeros((nq,), dtype=np.int32)
+    for q in range(nq):
+        docs = []
+        for j in range(fetch_k):
+            i = int(I[q, j])
+            if i == -1:
+                continue
+            if allow is not None and not (i < len(allow) and allow[i]):
+                continue
+            docs.append((D[q, j], i))
+        if raw_threshold is not None:
+            if metric == METRIC_IP:
+                docs = [(s, i) for s, i in docs if float(s) >= raw_threshold]
+            else:
+                docs = [(s, i) for s, i in docs if float(s) <= raw_threshold]
+        docs = docs[:k]
+        if relevance != REL_NONE:
+            fn = _REL_FN[relevance]
+            docs = [(s, i) for s, i in docs if fn(float(s)) >= relevance_threshold]
+        for j, (s, i) in enumerate(docs):
+            Do[q, j], Io[q, j] = s, i
+        C[q] = len(docs)
+    return Do, Io, C

@@ -54,6 +54,18 @@ class OracleIndex(IndexFlat):
         assert x.shape[1] == self._d and k > 0
         return flat.search(self._x, x, k, self._metric)
 
+    def upload_mask(self, words):
+        return np.ascontiguousarray(words, dtype=np.uint32)
+
+    def search_filtered(self, x, k, fetch_k=None, allow=None, score_threshold=None, relevance=0,
+                        relevance_threshold=0.0):
+        fetch_k = k if fetch_k is None else fetch_k
+        D, I = self.search(x, fetch_k)
+        bits = None
+        if allow is not None:
+            bits = np.unpackbits(np.asarray(allow, dtype="<u4").view(np.uint8), bitorder="little").astype(bool)
+        return flat.select_hits(D, I, k, self._metric, bits, score_threshold, relevance, relevance_threshold)
+
     def reconstruct_batch(self, ids):
         return self._x[np.asarray(ids, dtype=np.int64)]
 

@@ -342,3 +342,113 @@ def test_vectorstore_with_request_batching_gives_the_same_documents():
     finally:
         vs.disable_request_batching()
     assert isinstance(vs.index, OracleIndex)
+
+
+# ---------------------------------------------------------------- selection after the search
+def test_select_hits_oracle_known_answers():
+    """The restatement of langchain's post-search selection on hand-computable lists."""
+    Din = np.array([[0.9, 0.5, 0.2, -0.1, -0.4, -3.4e38]], np.float32)
+    Iin = np.array([[7, 3, 12, 5, 9, -1]], np.int64)
+    # no options: first k, padding skipped
+    Do, Io, C = flat.select_hits(Din, Iin, 8, flat.METRIC_IP)
+    assert C.tolist() == [5] and Io[0].tolist() == [7, 3, 12, 5, 9, -1, -1, -1] and Do[0, 5] == -flat.FLT_MAX
+    # metadata filter (rows 3 and 9 allowed), then cut at k
+    allow = np.zeros(16, bool)
+    allow[[3, 9]] = True
+    _, Io, C = flat.select_hits(Din, Iin, 1, flat.METRIC_IP, allow)
+    assert C.tolist() == [1] and Io[0].tolist() == [3]
+    # raw threshold: inner product keeps >=, L2 keeps <=
+    _, Io, C = flat.select_hits(Din, Iin, 4, flat.METRIC_IP, raw_threshold=0.2)
+    # the comparison is float(np.float32(0.2)) >= 0.2 in double: float32(0.2) = 0.20000000298 passes
+    assert Io[0, :C[0]].tolist() == [7, 3, 12]
+    Dl2 = np.array([[0.0, 0.3, 0.6, 2.5]], np.float32)
+    _, Io, C = flat.select_hits(Dl2, np.array([[4, 2, 8, 1]], np.int64), 4, flat.METRIC_L2, raw_threshold=0.6000001)
+    assert Io[0, :C[0]].tolist() == [4, 2, 8]
+    # the max-inner-product relevance function is not monotone: 1 - d for d > 0, -d otherwise; the cut at k
+    # comes BEFORE the relevance threshold (similarity_search_with_relevance_scores filters the k it got)
+    _, Io, C = flat.select_hits(Din, Iin, 3, flat.METRIC_IP, relevance=flat.REL_MAX_INNER_PRODUCT,
+                                relevance_threshold=0.45)
+    assert Io[0, :C[0]].tolist() == [3, 12]  # relevances 0.1, 0.5, 0.8 | rows 5, 9 are beyond k
+    _, Io, C = flat.select_hits(Dl2, np.array([[4, 2, 8, 1]], np.int64), 4, flat.METRIC_L2,
+                                relevance=flat.REL_EUCLIDEAN, relevance_threshold=0.25)
+    assert Io[0, :C[0]].tolist() == [4, 2, 8]  # 1 - 2.5 / sqrt(2) < 0.25
+
+
+def test_dict_filters_and_thresholds_select_like_the_per_hit_host_loop():
+    """A dict filter runs as a row bitmask + search_filtered; the same predicate as a callable runs upstream's
+    per-hit loop on the host.  Both must return the same documents and scores."""
+    metas = [{"source": f"f{i % 3}.txt", "page": i} for i in range(40)]
+    for ip in (False, True):
+        vs, emb = make_store(ip=ip, metadatas=metas)
+        for qi in (0, 7, 23):
+            q = emb.embed_query(TEXTS[qi])
+            full = vs.similarity_search_with_score_by_vector(q, k=40)
+            mid = float(full[10][1])
+            for k, fetch_k, thr in ((4, 20, None), (4, 40, mid), (10, 12, mid), (3, 3, None)):
+                kw = {} if thr is None else {"score_threshold": thr}
+                a = vs.similarity_search_with_score_by_vector(q, k=k, filter={"source": ["f1.txt", "f2.txt"]},
+                                                              fetch_k=fetch_k, **kw)
+                b = vs.similarity_search_with_score_by_vector(q, k=k, filter=lambda m: m["source"] != "f0.txt",
+                                                              fetch_k=fetch_k, **kw)
+                assert [(d.page_content, float(s)) for d, s in a] == [(d.page_content, float(s)) for d, s in b]
+            # threshold without a filter: only k are searched, as upstream does
+            a = vs.similarity_search_with_score_by_vector(q, k=12, score_threshold=mid)
+            want = [(d.page_content, float(s)) for d, s in full[:12] if (s >= mid if ip else s <= mid)]
+            assert [(d.page_content, float(s)) for d, s in a] == want and 0 < len(want) < 12
+
+
+def test_filter_bitmask_cache_follows_mutations():
+    metas = [{"source": f"f{i % 2}.txt"} for i in range(40)]
+    vs, emb = make_store(metadatas=metas)
+    flt = {"source": "f1.txt"}
+    assert len(vs.similarity_search(TEXTS[1], k=40, filter=flt, fetch_k=40)) == 20
+    mask = vs._device_mask(flt, build=False)
+    assert mask is not None and int(np.unpackbits(mask.view(np.uint8)).sum()) == 20
+    # add: the cached mask is stale, the next search rebuilds it
+    vs.add_texts(["a new chunk"], [{"source": "f1.txt"}])
+    assert vs._device_mask(flt, build=False) is None
+    assert len(vs.similarity_search(TEXTS[1], k=41, filter=flt, fetch_k=41)) == 21
+    # delete renumbers rows: stale again
+    victim = vs.index_to_docstore_id[1]
+    vs.delete([victim])
+    assert vs._device_mask(flt, build=False) is None
+    docs = vs.similarity_search(TEXTS[3], k=40, filter=flt, fetch_k=40)
+    assert len(docs) == 20 and all(d.metadata["source"] == "f1.txt" for d in docs)
+    # above device_filter_auto_rows a dict filter stays on the host path until it is prepared explicitly
+    vs.clear_filter_cache()
+    vs.device_filter_auto_rows = 10
+    assert len(vs.similarity_search(TEXTS[3], k=40, filter=flt, fetch_k=40)) == 20
+    assert vs._device_mask(flt, build=False) is None
+    vs.prepare_filter(flt)
+    assert vs._device_mask(flt, build=False) is not None
+    assert len(vs.similarity_search(TEXTS[3], k=40, filter=flt, fetch_k=40)) == 20
+    # the cache is not part of the pickled state
+    assert "_filter_masks" not in vs.__getstate__()
+    with pytest.raises(ValueError):
+        vs.prepare_filter(lambda m: True)
+
+
+def test_search_batch_with_filter_and_thresholds_returns_counts():
+    metas = [{"source": f"f{i % 3}.txt"} for i in range(40)]
+    vs, emb = make_store(metadatas=metas)
+    X = np.array([emb.embed_query(TEXTS[i]) for i in (0, 5, 11)], np.float32)
+    D0, I0 = vs.search_batch(X, 6)
+    assert D0.shape == (3, 6) and I0[:, 0].tolist() == [0, 5, 11]
+    Dm, Im, Cm = vs.search_batch(X, 4, filter={"source": "f2.txt"}, fetch_k=40)
+    assert Cm.tolist() == [4, 4, 4] and all(i % 3 == 2 for i in Im.reshape(-1))
+    assert Im[1, 0] == 5 and Im[2, 0] == 11
+    # relevance threshold as the chain server's retriever applies it (configuration.py:146: 0.25), per query on the host
+    r = vs.as_retriever(search_type="similarity_score_threshold", search_kwargs={"score_threshold": 0.25, "k": 6})
+    Dr, Ir, Cr = vs.search_batch(X, 6, relevance_score_threshold=0.25)
+    for row, qi in enumerate((0, 5, 11)):
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            want = [d.page_content for d in r.invoke(TEXTS[qi])]
+        assert [TEXTS[i] for i in Ir[row, :Cr[row]]] == want
+        assert (Ir[row, Cr[row]:] == -1).all()
+    # raw threshold
+    thr = float(D0[0, 3])
+    Dt, It, Ct = vs.search_batch(X[:1], 6, score_threshold=thr)
+    assert Ct.tolist() == [4] and It[0, :4].tolist() == I0[0, :4].tolist()
+    with pytest.raises(ValueError):
+        vs.search_batch(X, 4, filter=lambda m: True)
