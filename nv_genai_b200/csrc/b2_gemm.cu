@@ -754,7 +754,8 @@ __global__ void prep_queries_kernel(const float* __restrict__ q, int nq, int d, 
 // sqrt(max_norm) from the ingest side array; x2 again for L2 keys (2 q.x - |x|^2).
 template <int KIND>
 __global__ void band_kernel(const float* __restrict__ q, int nq, int d, int nq_pad, int steps, int l2,
-                            const uint32_t* __restrict__ max_norm_ord, float* __restrict__ band) {
+                            const uint32_t* __restrict__ max_norm_ord, const uint32_t* __restrict__ row_err_ord,
+                            float* __restrict__ band) {
     const int lane = threadIdx.x & 31;
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= nq_pad) return;
@@ -780,9 +781,12 @@ __global__ void band_kernel(const float* __restrict__ q, int nq, int d, int nq_p
         se += __shfl_xor_sync(kFull, se, s);
     }
     if (lane == 0) {
-        const float xn = sqrtf(fmaxf(ord2f(*max_norm_ord), 0.f)) * 1.0001f;
+        float xn = sqrtf(fmaxf(ord2f(*max_norm_ord), 0.f)) * 1.0001f;
         const float qn = sqrtf(ss) * 1.0001f, qe = sqrtf(se) * 1.0001f;
-        float err = qe * xn;
+        // rows replaced by a rounded copy x~ (bf16 shadow of fp32 rows): |q.x - q~.x~| <= |q~| |x - x~| + |q - q~| |x~|
+        const float xe = row_err_ord != nullptr ? sqrtf(fmaxf(ord2f(*row_err_ord), 0.f)) * 1.0001f : 0.f;
+        xn += xe;
+        float err = qe * xn + qn * xe;
         if (KIND != 0) err += qn * xn * 0.0009765625f;               // the row operand is truncated to tf32: 2^-10
         err += (float)steps * 4.76837158e-7f * qn * xn;              // accumulation: steps x 2^-21
         float b = 2.f * err * 1.001f + 1e-30f;
@@ -869,24 +873,31 @@ static int gemm_search_cg(const void* rows, int64_t n, size_t pitch_bytes, int d
                           cudaStream_t stream, const PeerPush* push, int cg, int query_parts);
 static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric,
                               const float* norms, const uint32_t* max_norm_ord, const float* q_dev, int64_t nq, int k,
-                              int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push, int cg);
+                              int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push, int cg,
+                              const ApproxRows* approx);
+
+bool gemm_uses_refine(int query_parts, const uint32_t* max_norm_ord) {
+    bool refine = max_norm_ord != nullptr && query_parts == 0 && getenv("B2_GEMM_QUERY_PARTS") == nullptr;
+    if (const char* e = getenv("B2_GEMM_REFINE")) refine = refine && atoi(e) != 0;
+    return refine;
+}
 
 int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* norms,
                 const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream,
-                const PeerPush* push, int query_parts, const uint32_t* max_norm_ord) {
+                const PeerPush* push, int query_parts, const uint32_t* max_norm_ord, const ApproxRows* approx) {
     // Filter and refine (default): one approximate product on the tensor cores, exact re-scoring of the few
     // candidates near the cut.  An explicit number of query parts (option / environment) selects the all-exact
     // tensor-core arithmetic instead, as does B2_GEMM_REFINE=0.
-    bool refine = max_norm_ord != nullptr && query_parts == 0 && getenv("B2_GEMM_QUERY_PARTS") == nullptr;
-    if (const char* e = getenv("B2_GEMM_REFINE")) refine = refine && atoi(e) != 0;
+    const bool refine = gemm_uses_refine(query_parts, max_norm_ord);
+    if (dtype == B2_DTYPE_BF16) approx = nullptr;
     if (refine) {
         int cgr = (num_sms % 2 == 0) ? 2 : 1;
         if (const char* e = getenv("B2_GEMM_CTA_GROUP")) cgr = (atoi(e) == 2 && num_sms % 2 == 0) ? 2 : 1;
         int rc = gemm_search_refine(rows, n, pitch_bytes, d, dtype, metric, norms, max_norm_ord, q_dev, nq, k, num_sms, D,
-                                    I, stream, push, cgr);
+                                    I, stream, push, cgr, approx);
         if (rc == B2_ERR_UNSUPPORTED && cgr == 2)
             rc = gemm_search_refine(rows, n, pitch_bytes, d, dtype, metric, norms, max_norm_ord, q_dev, nq, k, num_sms,
-                                    D, I, stream, push, 1);
+                                    D, I, stream, push, 1, approx);
         return rc;
     }
     // CTA pairs (cta_group::2) for bf16 rows when the SM count is even.  Measured at 10M x 1024, nq = 4096, k = 100:
@@ -1054,17 +1065,23 @@ static int launch_gemm_cg(const CUtensorMap& tmA, const CUtensorMap& tmB, const 
 
 static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric,
                               const float* norms, const uint32_t* max_norm_ord, const float* q_dev, int64_t nq, int k,
-                              int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push, int cg) {
+                              int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push, int cg,
+                              const ApproxRows* approx) {
     const bool bf16 = dtype == B2_DTYPE_BF16;
     const int elem = bf16 ? 2 : 4;
+    // the approximate pass reads bf16 operands when the rows are bf16 or a bf16 shadow of the fp32 rows exists
+    const bool abf16 = bf16 || approx != nullptr;
+    const int aelem = abf16 ? 2 : 4;
+    const void* arows = approx != nullptr ? approx->rows : rows;
+    const size_t apitch = approx != nullptr ? approx->pitch : pitch_bytes;
     auto fits = [&](bool fp32_exact, int na, int swb, int stages, int corr) {
         return gemm_smem_bytes(fp32_exact, na, swb, stages, k, cg, corr) <= 227 * 1024;
     };
     // ---- the approximate launch: one query part, no correction tiles
     int swb = fits(false, 1, 128, 3, 0) ? 128 : 64;
     if (const char* e = getenv("B2_GEMM_SWIZZLE")) swb = (atoi(e) == 128 && fits(false, 1, 128, 2, 0)) ? 128 : 64;
-    const size_t kbytes = (((size_t)d * elem + swb - 1) / swb) * swb;
-    const int kp = (int)(kbytes / elem);
+    const size_t kbytes = (((size_t)d * aelem + swb - 1) / swb) * swb;
+    const int kp = (int)(kbytes / aelem);
     int stages = kMaxStages;
     while (stages > 2 && !fits(false, 1, swb, stages, 0)) --stages;
     if (!fits(false, 1, swb, stages, 0)) {
@@ -1133,6 +1150,7 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     // k * z * band / sigma for scores with a Gaussian tail: ~0.4 k on 1024-d unit vectors with bf16 queries); a
     // segment that overflows the list is flagged and redone by the exact fix-up launch, so this is a speed knob only.
     int slack = std::max(48, 32 + 5 * k / 4);
+    if (approx != nullptr) slack = std::max(64, 32 + 3 * k);  // the band also covers the rows' bf16 rounding: ~2.3x wider
     if (const char* e = std::getenv("B2_GEMM_LIST_SLACK")) slack = std::max(8, std::min(1024 - k - 8, atoi(e)));
     p.list_len = ((k + slack) + 7) / 8 * 8;
 
@@ -1166,23 +1184,24 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
 
     int rc = B2_OK;
     CUtensorMap tmA, tmB, tmAx, tmBx;
-    rc = make_map(&tmA, bf16, swb, A, (uint64_t)kp, (uint64_t)p.nq_pad, kbytes, kTileM);
-    if (rc == B2_OK) rc = make_map(&tmB, bf16, swb, rows, (uint64_t)(pitch_bytes / elem), (uint64_t)n, pitch_bytes, kTileN / cg);
+    rc = make_map(&tmA, abf16, swb, A, (uint64_t)kp, (uint64_t)p.nq_pad, kbytes, kTileM);
+    if (rc == B2_OK) rc = make_map(&tmB, abf16, swb, arows, (uint64_t)(apitch / aelem), (uint64_t)n, apitch, kTileN / cg);
     if (rc == B2_OK) rc = make_map(&tmAx, bf16, swb_x, Ax, (uint64_t)kp_x, (uint64_t)2 * p.nq_pad, kbytes_x, kTileM);
     if (rc == B2_OK) rc = make_map(&tmBx, bf16, swb_x, rows, (uint64_t)(pitch_bytes / elem), (uint64_t)n, pitch_bytes, kTileN / cg);
     if (rc == B2_OK && cudaMemsetAsync(p.flags, 0, (size_t)p.n_qt * 4, stream) != cudaSuccess) {
         set_error("tensor-core search: cudaMemsetAsync failed");
         rc = B2_ERR_CUDA;
     }
-    if (rc == B2_OK) rc = prep_queries(q_dev, (int)nq, d, p.nq_pad, kp, 1, bf16, A, qn, p.tau, stream, 0);
+    if (rc == B2_OK) rc = prep_queries(q_dev, (int)nq, d, p.nq_pad, kp, 1, abf16, A, qn, p.tau, stream, 0);
     if (rc == B2_OK) rc = prep_queries(q_dev, (int)nq, d, p.nq_pad, kp_x, 2, bf16, Ax, nullptr, nullptr, stream, bf16 ? 0 : swb_x / 4);
     if (rc == B2_OK) {
         const int blocks = (p.nq_pad + 7) / 8;
-        const int steps = bf16 ? kp / 16 : kp / 8;
-        if (bf16)
-            band_kernel<0><<<blocks, 256, 0, stream>>>(q_dev, (int)nq, d, p.nq_pad, steps, metric == B2_METRIC_L2, max_norm_ord, band);
+        const int steps = abf16 ? kp / 16 : kp / 8;
+        const uint32_t* row_err = approx != nullptr ? approx->err_ord : nullptr;
+        if (abf16)
+            band_kernel<0><<<blocks, 256, 0, stream>>>(q_dev, (int)nq, d, p.nq_pad, steps, metric == B2_METRIC_L2, max_norm_ord, row_err, band);
         else
-            band_kernel<1><<<blocks, 256, 0, stream>>>(q_dev, (int)nq, d, p.nq_pad, steps, metric == B2_METRIC_L2, max_norm_ord, band);
+            band_kernel<1><<<blocks, 256, 0, stream>>>(q_dev, (int)nq, d, p.nq_pad, steps, metric == B2_METRIC_L2, max_norm_ord, row_err, band);
         B2_COUNT_LAUNCH();
         if (cudaGetLastError() != cudaSuccess) {
             set_error("band kernel launch failed");
@@ -1197,7 +1216,7 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
         cudaEventRecord(dbg_ev0, stream);
     }
     if (rc == B2_OK) {
-        if (bf16)
+        if (abf16)
             rc = swb == 128 ? launch_gemm_cg<0, 1, 128>(tmA, tmB, p, grid, smem, stream, cg)
                             : launch_gemm_cg<0, 1, 64>(tmA, tmB, p, grid, smem, stream, cg);
         else

@@ -232,7 +232,17 @@ struct b2_index {
     float* norms = nullptr;  // squared norm of each stored row
     int64_t norms_cap = 0;
     uint32_t* max_norm_ord = nullptr;  // device: ordered image of the largest squared row norm seen so far
-    int gemm_query_parts = 0;  // 0 = default (2: scores exact w.r.t. the stored rows), 1 = single part (faster, approximate)
+    int gemm_query_parts = 0;  // 0 = default (filter and refine), 2 = all-exact tensor arithmetic, 1 = single part (approximate)
+    // bf16 shadow of fp32 rows for the approximate pass of the tensor-core search: built lazily by the first large
+    // batch (under shadow_mu, readers hold only the shared lock), extended after adds, dropped by removals.
+    RowStore shadow;
+    size_t shadow_pitch = 0;
+    int64_t shadow_rows = 0;           // rows [0, shadow_rows) of the shadow are current
+    uint32_t* shadow_err_ord = nullptr;  // device: ordered image of max |x - bf16(x)|^2 over the shadowed rows
+    cudaEvent_t shadow_ev = nullptr;   // completion of the latest shadow build
+    int shadow_enabled = 1;            // option "bf16_shadow"
+    int64_t shadow_refused_rows = 0;   // last size the device had no room for (do not retry until the index changes)
+    std::mutex shadow_mu;
     std::shared_mutex mu;
 };
 
@@ -362,13 +372,21 @@ int b2_index_create(int d, int metric, int dtype, int device, b2_index** out) {
     h->num_sms = sms;
     h->pitch = row_pitch_bytes(d, dtype);
     h->store.init(device);
-    if (cudaMalloc(&h->max_norm_ord, sizeof(uint32_t)) != cudaSuccess ||
-        cudaMemset(h->max_norm_ord, 0, sizeof(uint32_t)) != cudaSuccess) {  // 0 orders below every float
+    if (dtype == B2_DTYPE_F32 && getenv("B2_NO_SHADOW") == nullptr) {
+        h->shadow_pitch = row_pitch_bytes(d, B2_DTYPE_BF16);
+        h->shadow.init(device);
+        if (!h->shadow.vmm) h->shadow_enabled = 0;  // growing a plain allocation would move rows under running searches
+    } else {
+        h->shadow_enabled = 0;
+    }
+    if (cudaMalloc(&h->max_norm_ord, 2 * sizeof(uint32_t)) != cudaSuccess ||
+        cudaMemset(h->max_norm_ord, 0, 2 * sizeof(uint32_t)) != cudaSuccess) {  // 0 orders below every float
         cudaGetLastError();
         delete h;
         set_error("out of device memory");
         return B2_ERR_OOM;
     }
+    h->shadow_err_ord = h->max_norm_ord + 1;
     *out = h;
     return B2_OK;
 }
@@ -379,6 +397,8 @@ int b2_index_destroy(b2_index* h) {
         DeviceGuard g(h->device);
         cudaDeviceSynchronize();
         h->store.release();
+        h->shadow.release();
+        if (h->shadow_ev) cudaEventDestroy(h->shadow_ev);
         if (h->norms) cudaFree(h->norms);
         if (h->max_norm_ord) cudaFree(h->max_norm_ord);
         cudaGetLastError();
@@ -474,6 +494,50 @@ __global__ void fill_empty_kernel(float* D, int64_t* I, int64_t n, float dval) {
     }
 }
 
+// The bf16 shadow of fp32 rows, current for all ntotal rows and ordered before later work on `stream`; false when the
+// index has none (bf16 rows, option off, no VMM, or no room on the device: the search then runs on the fp32 rows).
+// Caller holds the shared lock, so ntotal and the fp32 rows are stable; builders serialise on shadow_mu.
+static bool ensure_shadow(b2_index* h, cudaStream_t stream, ApproxRows* out) {
+    if (!h->shadow_enabled || h->dtype != B2_DTYPE_F32) return false;
+    std::lock_guard<std::mutex> lk(h->shadow_mu);
+    const int64_t n = h->ntotal;
+    if (h->shadow_rows < n) {
+        if (h->shadow_refused_rows == n) return false;
+        const size_t need = (size_t)n * h->shadow_pitch;
+        if (need > h->shadow.capacity()) {
+            size_t free_b = 0, total_b = 0;
+            if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) {
+                cudaGetLastError();
+                return false;
+            }
+            // leave room for the search scratch and for the application: the shadow is an accelerator, not a need
+            const size_t grow = need - h->shadow.capacity();
+            if (free_b < grow + grow / 4 + ((size_t)6 << 30) || h->shadow.ensure(need, stream) != B2_OK) {
+                h->shadow_refused_rows = n;
+                return false;
+            }
+        }
+        if (h->shadow_ev == nullptr && cudaEventCreateWithFlags(&h->shadow_ev, cudaEventDisableTiming) != cudaSuccess) {
+            cudaGetLastError();
+            h->shadow_ev = nullptr;
+            return false;
+        }
+        // an earlier build may still be running on another stream: order this one behind it
+        if (h->shadow_rows > 0) cudaStreamWaitEvent(stream, h->shadow_ev, 0);
+        if (build_shadow_rows(h->store.base(), h->pitch, h->shadow.base(), h->shadow_pitch, h->shadow_rows,
+                              n - h->shadow_rows, h->d, h->shadow_err_ord, stream) != B2_OK)
+            return false;
+        cudaEventRecord(h->shadow_ev, stream);
+        h->shadow_rows = n;
+    } else if (h->shadow_ev != nullptr) {
+        cudaStreamWaitEvent(stream, h->shadow_ev, 0);  // built on another stream, possibly still in flight
+    }
+    out->rows = h->shadow.base();
+    out->pitch = h->shadow_pitch;
+    out->err_ord = h->shadow_err_ord;
+    return true;
+}
+
 // Device-side search: q_dev [nq][d], D_dev/I_dev [nq][k]; caller holds the shared lock and the device.
 static int search_device(b2_index* h, int64_t nq, const float* q_dev, int k, float* D_dev, int64_t* I_dev,
                          cudaStream_t stream, const PeerPush* push = nullptr) {
@@ -497,9 +561,13 @@ static int search_device(b2_index* h, int64_t nq, const float* q_dev, int k, flo
     if (scan_tc_supported(h->ntotal, h->d, h->dtype, h->metric, k, nq))
         return scan_tc_search(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, q_dev, (int)nq, k, h->num_sms,
                               D_dev, I_dev, stream, push);
-    if (gemm_path_supported(h->ntotal, h->d, h->dtype, k, nq))
+    if (gemm_path_supported(h->ntotal, h->d, h->dtype, k, nq)) {
+        ApproxRows approx;
+        const bool shadowed = gemm_uses_refine(h->gemm_query_parts, h->max_norm_ord) && ensure_shadow(h, stream, &approx);
         return gemm_search(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, h->metric, h->norms, q_dev, nq, k,
-                           h->num_sms, D_dev, I_dev, stream, push, h->gemm_query_parts, h->max_norm_ord);
+                           h->num_sms, D_dev, I_dev, stream, push, h->gemm_query_parts, h->max_norm_ord,
+                           shadowed ? &approx : nullptr);
+    }
     const int kpad = next_pow2(k < 32 ? 32 : k);
     const int tmax = max_query_tile(h, kpad);
     if (tmax == 0) {
@@ -805,6 +873,8 @@ int b2_index_remove_ids(b2_index* h, int64_t n, const int64_t* ids, int64_t* n_r
     B2_CUDA_TRY(cudaStreamSynchronize(stream));
     if (rc != B2_OK) return rc;
     h->ntotal = nt - removed;
+    h->shadow_rows = std::min(h->shadow_rows, first);  // rows from the first removed one on moved: reconvert lazily
+    h->shadow_refused_rows = 0;
     if (n_removed) *n_removed = removed;
     return B2_OK;
 }
@@ -845,6 +915,8 @@ int b2_index_merge_from(b2_index* dst, b2_index* src) {
     B2_CUDA_TRY(cudaStreamSynchronize(stream));
     dst->ntotal += n;
     src->ntotal = 0;  // faiss: other.reset()
+    src->shadow_rows = 0;
+    dst->shadow_refused_rows = src->shadow_refused_rows = 0;
     return B2_OK;
 }
 
@@ -863,6 +935,28 @@ int b2_index_set_option(b2_index* h, const char* name, int64_t value) {
         h->gemm_query_parts = (int)value;
         return B2_OK;
     }
+    if (strcmp(name, "bf16_shadow") == 0) {
+        if (value != 0 && value != 1) {
+            set_error("b2_index_set_option: bf16_shadow must be 0 or 1");
+            return B2_ERR_INVALID;
+        }
+        if (value == 1 && (h->dtype != B2_DTYPE_F32 || !h->shadow.vmm)) {
+            if (h->dtype != B2_DTYPE_F32) return B2_OK;  // bf16 rows are their own shadow
+            set_error("b2_index_set_option: bf16_shadow needs the virtual-memory row store (B2_NO_VMM / B2_NO_SHADOW is set)");
+            return B2_ERR_UNSUPPORTED;
+        }
+        h->shadow_enabled = (int)value;
+        if (value == 0) {  // give the memory back (no search is running: this is the writer lock)
+            DeviceGuard g(h->device);
+            cudaDeviceSynchronize();
+            const int dev = h->device;
+            h->shadow.release();
+            h->shadow.init(dev);
+            h->shadow_rows = 0;
+        }
+        h->shadow_refused_rows = 0;
+        return B2_OK;
+    }
     set_error("b2_index_set_option: unknown option '%s'", name);
     return B2_ERR_INVALID;
 }
@@ -871,6 +965,8 @@ int b2_index_reset(b2_index* h) {
     B2_TRY(check_handle(h));
     std::unique_lock<std::shared_mutex> lk(h->mu);
     h->ntotal = 0;
+    h->shadow_rows = 0;
+    h->shadow_refused_rows = 0;
     return B2_OK;
 }
 

@@ -282,4 +282,52 @@ int update_max_norm(const float* norms, int64_t n, uint32_t* max_norm_ord, cudaS
     return B2_OK;
 }
 
+// ------------------------------------------------------------------ bf16 shadow of fp32 rows
+// The tensor-core search of fp32 rows filters with ONE bf16 product per score when a bf16 copy of the rows exists
+// (half the operand bytes, twice the tensor rate of tf32) and re-scores the candidates near the cut from the fp32
+// rows.  One warp per row: read the fp32 row once, write round-to-nearest bf16, and fold sum (x - bf16(x))^2 into a
+// running maximum (ordered-uint image) -- the rigorous bound on |q . (x - x~)| the error band is built from.
+__global__ void shadow_rows_kernel(const char* __restrict__ rows, size_t pitch, char* __restrict__ shadow, size_t spitch,
+                                   int64_t row0, int64_t n, int d, int dpad, uint32_t* __restrict__ err_ord) {
+    const int lane = threadIdx.x & 31;
+    const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int64_t nw = (int64_t)gridDim.x * (blockDim.x >> 5);
+    float emax = 0.f;
+    for (int64_t r = w; r < n; r += nw) {
+        const float4* src = reinterpret_cast<const float4*>(rows + (size_t)(row0 + r) * pitch);
+        uint2* dst = reinterpret_cast<uint2*>(shadow + (size_t)(row0 + r) * spitch);
+        float e = 0.f;
+        for (int c4 = lane; c4 * 4 < dpad; c4 += 32) {  // the pitch covers dpad (zero padded by the ingest kernel)
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c4 * 4 < d) v = __ldcs(src + c4);
+            if (c4 * 4 + 1 >= d) v.y = 0.f;
+            if (c4 * 4 + 2 >= d) v.z = 0.f;
+            if (c4 * 4 + 3 >= d) v.w = 0.f;
+            const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+            const float2 fl = __bfloat1622float2(lo), fh = __bfloat1622float2(hi);
+            const float dx = v.x - fl.x, dy = v.y - fl.y, dz = v.z - fh.x, dw = v.w - fh.y;
+            e = fmaf(dx, dx, fmaf(dy, dy, fmaf(dz, dz, fmaf(dw, dw, e))));
+            uint2 o;
+            o.x = *reinterpret_cast<const uint32_t*>(&lo);
+            o.y = *reinterpret_cast<const uint32_t*>(&hi);
+            dst[c4] = o;
+        }
+#pragma unroll
+        for (int s = 16; s >= 1; s >>= 1) e += __shfl_xor_sync(kFull, e, s);
+        emax = (e > emax) ? e : emax;  // NaN rows: ignored, they never enter a result
+    }
+    if (lane == 0 && emax > 0.f) atomicMax(err_ord, f2ord(emax * 1.0001f));
+}
+
+int build_shadow_rows(const void* rows, size_t pitch, void* shadow, size_t spitch, int64_t row0, int64_t n, int d,
+                      uint32_t* err_ord, cudaStream_t stream) {
+    if (n <= 0) return B2_OK;
+    const int dpad = (int)(spitch / 2);  // the whole shadow row, padding included, is written (zeros beyond d)
+    const int blocks = (int)std::min<int64_t>((n + 7) / 8, 148 * 8);
+    shadow_rows_kernel<<<blocks, 256, 0, stream>>>(static_cast<const char*>(rows), pitch, static_cast<char*>(shadow),
+                                                  spitch, row0, n, d, dpad, err_ord);
+    B2_AFTER_LAUNCH();
+    return B2_OK;
+}
+
 }  // namespace b2

@@ -66,6 +66,9 @@ int filter_results(const float* D_in, const int64_t* I_in, int64_t nq, int fetch
                    const uint32_t* allow, int64_t allow_bits, int use_raw, double raw_thr, int rel_kind, double rel_thr,
                    float* D_out, int64_t* I_out, int32_t* counts, cudaStream_t stream);
 
+int build_shadow_rows(const void* rows, size_t pitch, void* shadow, size_t spitch, int64_t row0, int64_t n, int d,
+                      uint32_t* err_ord, cudaStream_t stream);
+
 // b2_gemm.cu ---------------------------------------------------------------
 // Tensor-core search for batches of >= 20 queries (faiss's BLAS threshold), k <= 128.
 // q [nq][d] fp32 -> A [na][nq_pad][kp] operand parts (bf16 hi/lo, or fp32 words holding tf32 hi/lo), zero padded;
@@ -75,9 +78,18 @@ int filter_results(const float* D_in, const int64_t* I_in, int64_t nq, int fetch
 int prep_queries(const float* q_dev, int nq, int d, int nq_pad, int kp, int na, bool bf16, void* A, float* qn,
                  uint32_t* tau, cudaStream_t stream, int mixed_slice = 0);
 bool gemm_path_supported(int64_t n, int d, int dtype, int k, int64_t nq);
+// A bf16 copy of fp32 rows for the approximate pass of filter-and-refine (b2_ingest.cu: build_shadow_rows).
+struct ApproxRows {
+    const void* rows;         // [n][pitch] bf16
+    size_t pitch;             // bytes
+    const uint32_t* err_ord;  // device: ordered image of max over rows of |x - bf16(x)|^2
+};
 int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* norms,
                 const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream,
-                const PeerPush* push = nullptr, int query_parts = 0, const uint32_t* max_norm_ord = nullptr);
+                const PeerPush* push = nullptr, int query_parts = 0, const uint32_t* max_norm_ord = nullptr,
+                const ApproxRows* approx = nullptr);
+// true when gemm_search with these options would run filter-and-refine (and so can use a bf16 shadow of fp32 rows)
+bool gemm_uses_refine(int query_parts, const uint32_t* max_norm_ord);
 // (D_parts, I_parts): [nparts][nq][k] -> [nq][k]
 // part g's lists start d_stride_bytes / i_stride_bytes after part g-1's (0 = natural [nparts][nq][k] arrays);
 // id_bases (host, nparts entries, optional): ids in the lists are local to their part, global = base + local.

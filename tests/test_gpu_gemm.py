@@ -34,7 +34,8 @@ def _data(n, d, nq, normalize, seed=0):
 def _launched_tensor_kernel(fn):
     """Run fn() and return (result, kernel launches).  One pass for the whole batch: the tensor-core scan is prep +
     scan + merge = 3 launches, the GEMM path in its default filter-and-refine mode 2 x prep + band + gemm + fix-up +
-    merge = 6 (3 with an explicit number of query parts); ceil(nq/16) FFMA scan passes would be 2 per pass."""
+    merge = 6 (3 with an explicit number of query parts; 7 when the first large batch on fp32 rows also converts the
+    rows to their bf16 shadow); ceil(nq/16) FFMA scan passes would be 2 per pass."""
     from nv_genai_b200 import _native
 
     _native.launch_count_reset()
@@ -50,7 +51,7 @@ def test_fp32_store_matches_blas_oracle(metric, nq, k):
     idx = _mk(metric, d)
     idx.add(x)
     (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, k))
-    assert launches in (3, 6), launches  # one pass for the whole batch, not ceil(nq/16) scan passes
+    assert launches in (3, 6, 7), launches  # one pass for the whole batch, not ceil(nq/16) scan passes
     Dr, Ir = flat.search_blas(x, q, k, metric)
     assert_parity(D, I, Dr, Ir, x, q, metric_ip=(metric == flat.METRIC_IP))
     D64, I64 = flat.search_f64(x, q, k, metric)
@@ -80,7 +81,7 @@ def test_bf16_store_matches_oracle_on_rounded_rows(metric):
     idx = _mk(metric, d, "bfloat16")
     idx.add(x)
     (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, k))
-    assert launches in (3, 6)
+    assert launches in (3, 6, 7)
     xr = flat.round_bf16(x)
     Dr, Ir = flat.search_blas(xr, q, k, metric)
     assert_parity(D, I, Dr, Ir, xr, q, metric_ip=(metric == flat.METRIC_IP))
@@ -202,7 +203,7 @@ def test_medium_batch_rides_one_tensor_scan_pass_when_k_is_small(dtype, nq, k):
     idx = _mk(flat.METRIC_IP, d, dtype)
     idx.add(x)
     (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, k))
-    assert launches in (3, 6), launches
+    assert launches in (3, 6, 7), launches
     xr = flat.round_bf16(x) if dtype == "bfloat16" else x
     Dr, Ir = flat.search_f64(xr, q, k, flat.METRIC_IP)
     assert_parity(D, I, Dr.astype(np.float32), Ir, xr, q, metric_ip=True)
@@ -271,3 +272,59 @@ def test_concurrent_readers_across_all_three_kernels():
         par = list(ex.map(lambda j: idx.search(q[j[0]:j[0] + j[1]], j[2]), jobs))
     for (Ds, Is), (Dp, Ip) in zip(serial, par):
         assert np.array_equal(Is, Ip) and np.array_equal(Ds, Dp)
+
+
+@pytest.mark.parametrize("metric", [flat.METRIC_IP, flat.METRIC_L2])
+def test_bf16_shadow_of_fp32_rows_filters_and_the_fp32_rows_decide(metric):
+    """Large batches on fp32 rows filter with one bf16 product per score over a lazily built bf16 copy of the rows; every
+    candidate inside the (wider) error band is re-scored from the fp32 rows, so the results equal those without the
+    shadow bit for bit.  The shadow follows add / remove_ids / reset."""
+    n, d, nq = 40_000, 384, 70
+    x, q = _data(n + 5_000, d, nq, metric == flat.METRIC_IP, seed=77)
+    planted = np.array([5, 255, 256, 9_000, 39_999])
+    for r in range(3):  # exact copies of a query: score 1.0 / distance ~0 must survive the bf16 filter
+        x[planted + r] = q[r]
+    idx = _mk(metric, d)
+    idx.add(x[:n])
+
+    def both(k):
+        idx.set_option("bf16_shadow", 1)
+        (D1, I1), l1 = _launched_tensor_kernel(lambda: idx.search(q, k))
+        idx.set_option("bf16_shadow", 0)
+        (D0, I0), l0 = _launched_tensor_kernel(lambda: idx.search(q, k))
+        idx.set_option("bf16_shadow", 1)
+        assert l1 == 7 and l0 == 6, (l1, l0)  # shadow rebuilt after it was dropped: + the conversion kernel
+        assert np.array_equal(I1, I0) and np.array_equal(D1, D0)
+        return D1, I1
+
+    for k in (10, 100):
+        D, I = both(k)
+        Dr, Ir = flat.search_f64(x[:n], q, k, metric)
+        assert_parity(D, I, Dr.astype(np.float32), Ir, x[:n], q, metric_ip=(metric == flat.METRIC_IP))
+        for r in range(3):
+            assert np.array_equal(np.sort(I[r, :5]), planted + r)
+    # a second search reuses the shadow: no conversion launch
+    idx.search(q, 10)
+    _, launches = _launched_tensor_kernel(lambda: idx.search(q, 10))
+    assert launches == 6
+    # add: only the new rows are converted, results cover them
+    x[n + 17] = q[5]
+    idx.add(x[n:])
+    (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, 10))
+    assert launches == 7 and I[5, 0] == n + 17
+    Dr, Ir = flat.search_f64(x, q, 10, metric)
+    assert_parity(D, I, Dr.astype(np.float32), Ir, x, q, metric_ip=(metric == flat.METRIC_IP))
+    # remove_ids shifts rows: the shadow is reconverted from the first removed row on
+    gone = np.array([100, 101, 20_000, n + 17])
+    assert idx.remove_ids(gone) == 4
+    keep = np.ones(len(x), bool)
+    keep[gone] = False
+    (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, 10))
+    assert launches == 7
+    Dr, Ir = flat.search_f64(x[keep], q, 10, metric)
+    assert_parity(D, I, Dr.astype(np.float32), Ir, x[keep], q, metric_ip=(metric == flat.METRIC_IP))
+    idx.reset()
+    idx.add(x[:8_000])
+    D, I = idx.search(q, 10)
+    Dr, Ir = flat.search_f64(x[:8_000], q, 10, metric)
+    assert_parity(D, I, Dr.astype(np.float32), Ir, x[:8_000], q, metric_ip=(metric == flat.METRIC_IP))
