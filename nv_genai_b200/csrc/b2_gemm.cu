@@ -1083,6 +1083,7 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     const size_t kbytes = (((size_t)d * aelem + swb - 1) / swb) * swb;
     const int kp = (int)(kbytes / aelem);
     int stages = kMaxStages;
+    if (const char* e = getenv("B2_GEMM_STAGES")) stages = std::max(2, std::min(kMaxStages, atoi(e)));
     while (stages > 2 && !fits(false, 1, swb, stages, 0)) --stages;
     if (!fits(false, 1, swb, stages, 0)) {
         set_error("tensor-core search: k=%d does not fit shared memory", k);

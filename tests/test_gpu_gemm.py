@@ -281,7 +281,7 @@ def test_bf16_shadow_of_fp32_rows_filters_and_the_fp32_rows_decide(metric):
     shadow bit for bit.  The shadow follows add / remove_ids / reset."""
     n, d, nq = 40_000, 384, 70
     x, q = _data(n + 5_000, d, nq, metric == flat.METRIC_IP, seed=77)
-    planted = np.array([5, 255, 256, 9_000, 39_999])
+    planted = np.array([5, 255, 300, 9_000, 39_990])
     for r in range(3):  # exact copies of a query: score 1.0 / distance ~0 must survive the bf16 filter
         x[planted + r] = q[r]
     idx = _mk(metric, d)
