@@ -91,6 +91,9 @@ struct GemmParams {
     int list_len;       // entries emitted per (query, segment): k, or k + slack when refine
     int only_flagged;   // fix-up launch: process only query groups whose flag is set
     const float* band;  // [nq_pad] refine: 2 x (bound on |approximate key - exact key|), per query
+    unsigned long long* stats;  // diagnostics (B2_GEMM_DEBUG): [0] MMA cycles waiting for a free accumulator, [1] for operands,
+                        // [2] epilogue warp 0 cycles waiting for a full accumulator, [3] list insertions, [4] log entries,
+                        // [5] log compactions, [6] MMA warp cycles in total; nullptr = off
     uint32_t* flags;    // [n_qt] refine: set when a query of the group had more in-band candidates than fit
     const float* norms; // |x|^2 per stored row
     uint64_t* cand;     // [grid][kCandCap][128]
@@ -346,6 +349,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint32_t phase = 0;
         uint32_t tc = 0;
         int cslot = 0;
+        long long w_acc = 0, w_ops = 0;
+        const long long c_begin = p.stats ? clock64() : 0;
         for (int item = unit; cta_rank == 0 && item < p.n_items; item += n_units) {
             if (p.only_flagged && __ldcg(p.flags + item % p.n_qt) == 0u) continue;  // fix-up launch: flagged groups only
             const int seg = item / p.n_qt;
@@ -353,13 +358,17 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
             for (int t = t0; t < t1; ++t, ++tc) {
                 const uint32_t buf = tc % NBUF, par = (tc / NBUF) & 1u;
+                const long long c0 = p.stats ? clock64() : 0;
                 mbar_wait(smem_u32(tempty_bar + buf), par ^ 1u);
+                if (p.stats) w_acc += clock64() - c0;
                 tcgen05_fence_after();
                 const uint32_t d_tmem = tmem_base + buf * kTileN;
                 const uint32_t c_tmem = tmem_base + kTileN;  // fp32 rows: correction accumulator
                 for (int ks = 0; ks < p.kstages; ++ks) {
+                    const long long c1 = p.stats ? clock64() : 0;
                     mbar_wait(smem_u32((KIND == 1 ? xf_bar : full_bar) + stage), phase);
                     if (CG == 2 && KIND == 1) mbar_wait(smem_u32(pxf_bar + stage), phase);
+                    if (p.stats) w_ops += clock64() - c1;
                     tcgen05_fence_after();
                     if (elect_one()) {
                         const uint32_t sb = smem_u32(stages + (size_t)stage * STAGE_BYTES);
@@ -414,6 +423,11 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
                 __syncwarp();
             }
+        }
+        if (p.stats && cta_rank == 0 && lane == 0) {
+            atomicAdd(p.stats + 0, (unsigned long long)w_acc);
+            atomicAdd(p.stats + 1, (unsigned long long)w_ops);
+            atomicAdd(p.stats + 6, (unsigned long long)(clock64() - c_begin));
         }
         // CTA pairs, fp32 rows: the peer's MMA warp has nothing to issue; it forwards "my transform warps are done with
         // this K slice" to the leader with ONE cluster-scope arrival per slice (sixteen cluster-scope arrivals per
@@ -536,6 +550,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint64_t* log = p.cand + (size_t)blockIdx.x * kCandCap * kEpiThreads + ql;
         const bool l2 = p.metric == B2_METRIC_L2;
         uint32_t tc = 0;
+        long long w_full = 0;
+        unsigned n_ins = 0, n_log = 0, n_cmp = 0;
         for (int item = unit; item < p.n_items; item += n_units) {
             if (p.only_flagged && __ldcg(p.flags + item % p.n_qt) == 0u) continue;  // fix-up launch: flagged groups only
             const int qt = (item % p.n_qt) * CG + (int)cta_rank, seg = item / p.n_qt;
@@ -544,7 +560,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int q = qt * kTileM + ql;
             const bool active = q < p.nq;
             // bound imported from finished items of this query (exclusive); +inf parks padding lanes
-            const float thr0 = active ? ord2f(__ldcg(p.tau + q)) : -kNegInf;
+            float thr0 = active ? ord2f(__ldcg(p.tau + q)) : -kNegInf;
             float thr = thr0;      // a key enters the sorted list if it is above this
             // refine: approximate keys; everything within `band` below the running k-th is logged as well, and the
             // imported bound is already such a log threshold
@@ -558,6 +574,16 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             for (int t = t0; t < t1; ++t, ++tc) {
                 const uint32_t buf = tc % NBUF, par = (tc / NBUF) & 1u;
                 const uint32_t row0 = (uint32_t)t * kTileN;
+                // Every 32 tiles the segments of a query that run at the same time (on other SMs) trade bounds: publish
+                // this list's k-th, pick up the best one published so far.  Without it every segment re-learns its
+                // threshold from -inf (measured at k = 100: 300 insertions per (query, segment) where ~100 suffice).
+                if (((t - t0) & 31) == 31 && active) {
+                    const float kth_now = keys_w[(size_t)lane * k + (k - 1)];
+                    if (kth_now > kNegInf) atomicMax(p.tau + q, f2ord(refine ? kth_now - band : kth_now) - 1u);
+                    thr0 = fmaxf(thr0, ord2f(__ldcg(p.tau + q)));
+                    thr = fmaxf(thr, thr0);
+                    thr_log = fmaxf(thr_log, thr0);
+                }
                 if (l2) {
                     float* ns = nrm_s + (tc & 1u) * kTileN;  // always double-buffered: a faster warp may already be one tile ahead
                     for (int c = ql; c < kTileN; c += kEpiThreads) {
@@ -568,6 +594,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
                 // a whole tile of survivors must fit behind cnt: compact first if any lane is close (warp-uniform)
                 if (__any_sync(kFull, cnt > kCandCap - kTileN)) {
+                    ++n_cmp;
                     if (refine) {
                         compact_band(log, cnt, thr_log, active);
                         if (cnt > kCandCap - kTileN && !overflow) {  // too many in-band candidates: leave it to the fix-up pass
@@ -578,7 +605,9 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         compact_log(log, cnt, keys_w[(size_t)lane * k + (k - 1)], k, cnt > k);
                     }
                 }
+                const long long c2 = p.stats ? clock64() : 0;
                 mbar_wait(smem_u32(tfull_bar + buf), par);
+                if (p.stats) w_full += clock64() - c2;
                 tcgen05_fence_after();
                 const int limit = (int)min((uint32_t)kTileN, p.n - row0);
                 const uint32_t taddr0 = tmem_base + buf * kTileN + ((uint32_t)(warp * 32) << 16);
@@ -611,6 +640,17 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
                         for (int c = 0; c < 32; ++c) key[c] = __uint_as_float(raw32[c]) + 0.0f;
                     }
+                    // Fast reject: most chunks hold no candidate for any of the warp's 32 queries; a max tree (log depth,
+                    // independent operations) answers that without the 64 dependent compare-and-or steps of the masks.
+                    {
+                        float m8[8];
+#pragma unroll
+                        for (int c = 0; c < 8; ++c)
+                            m8[c] = fmaxf(fmaxf(key[c], key[c + 8]), fmaxf(key[c + 16], key[c + 24]));
+                        const float mx = fmaxf(fmaxf(fmaxf(m8[0], m8[1]), fmaxf(m8[2], m8[3])),
+                                               fmaxf(fmaxf(m8[4], m8[5]), fmaxf(m8[6], m8[7])));
+                        if (!__any_sync(kFull, mx > thr_log)) continue;  // thr_log <= thr always
+                    }
                     uint32_t m = 0;
                     const int left = limit - ch * 32;
                     const uint32_t valid = (left >= 32) ? 0xffffffffu : ((left <= 0) ? 0u : ((1u << left) - 1u));
@@ -628,6 +668,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             if (cnt < kCandCap) {
                                 log[(size_t)cnt * kEpiThreads] = pack_cand(select32(key, c), row0 + ch * 32 + c);
                                 ++cnt;
+                                ++n_log;
                             }
                         }
                     } else {
@@ -646,6 +687,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         if (xs > ts) {  // the threshold may have risen since the mask was built
                             const float kth = coop_insert(keys_w + (size_t)src * k, k, xs, lane);
                             if (lane == src) {
+                                ++n_ins;
                                 if (!refine) {
                                     log[(size_t)cnt * kEpiThreads] = pack_cand(kv, row0 + ch * 32 + c);
                                     ++cnt;
@@ -690,6 +732,12 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
             }
             __syncwarp();
+        }
+        if (p.stats) {
+            if (warp == 0 && lane == 0) atomicAdd(p.stats + 2, (unsigned long long)w_full);
+            atomicAdd(p.stats + 3, (unsigned long long)n_ins);
+            atomicAdd(p.stats + 4, (unsigned long long)n_log);
+            if (lane == 0) atomicAdd(p.stats + 5, (unsigned long long)n_cmp);
         }
     }
 
@@ -999,6 +1047,7 @@ static int gemm_search_cg(const void* rows, int64_t n, size_t pitch_bytes, int d
     p.list_len = k;
     p.band = nullptr;
     p.flags = nullptr;
+    p.stats = nullptr;
 
     // scratch: [A parts][qn][tau][partial][candidate logs]
     auto al = [](size_t v) { return (v + 1023) / 1024 * 1024; };
@@ -1160,7 +1209,7 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     const size_t a_bytes = al((size_t)p.nq_pad * kbytes);
     const size_t ax_bytes = al((size_t)2 * p.nq_pad * kbytes_x);
     const size_t qn_bytes = al((size_t)p.nq_pad * 4);
-    const size_t fl_bytes = al((size_t)p.n_qt * 4);
+    const size_t fl_bytes = al((size_t)p.n_qt * 4) + 1024;  // + diagnostics counters
     const size_t part_bytes = al((size_t)p.nq_pad * p.n_seg * p.list_len * 8);
     const size_t cand_bytes = al((size_t)grid * kCandCap * kEpiThreads * 8);
     char* blk = nullptr;
@@ -1177,6 +1226,8 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     float* band = reinterpret_cast<float*>(cur);
     cur += qn_bytes;
     p.flags = reinterpret_cast<uint32_t*>(cur);
+    static const bool want_stats = std::getenv("B2_GEMM_DEBUG") != nullptr;
+    p.stats = want_stats ? reinterpret_cast<unsigned long long*>(cur + fl_bytes - 1024) : nullptr;
     cur += fl_bytes;
     p.partial = reinterpret_cast<uint64_t*>(cur);
     cur += part_bytes;
@@ -1189,7 +1240,7 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     if (rc == B2_OK) rc = make_map(&tmB, abf16, swb, arows, (uint64_t)(apitch / aelem), (uint64_t)n, apitch, kTileN / cg);
     if (rc == B2_OK) rc = make_map(&tmAx, bf16, swb_x, Ax, (uint64_t)kp_x, (uint64_t)2 * p.nq_pad, kbytes_x, kTileM);
     if (rc == B2_OK) rc = make_map(&tmBx, bf16, swb_x, rows, (uint64_t)(pitch_bytes / elem), (uint64_t)n, pitch_bytes, kTileN / cg);
-    if (rc == B2_OK && cudaMemsetAsync(p.flags, 0, (size_t)p.n_qt * 4, stream) != cudaSuccess) {
+    if (rc == B2_OK && cudaMemsetAsync(p.flags, 0, fl_bytes, stream) != cudaSuccess) {
         set_error("tensor-core search: cudaMemsetAsync failed");
         rc = B2_ERR_CUDA;
     }
@@ -1240,11 +1291,21 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
         for (uint32_t f : fl) nf += f != 0u;
         std::fprintf(stderr, "[b2 gemm refine] k=%d list_len=%d n_seg=%d n_qt=%d flagged=%d band[0]=%g\n", k, p.list_len,
                      p.n_seg, p.n_qt, nf, bd.empty() ? 0.0 : (double)bd[0]);
+        unsigned long long st[8] = {0};
+        cudaMemcpy(st, p.stats, sizeof(st), cudaMemcpyDeviceToHost);
+        const double units = (double)(grid / cg), lanes = (double)p.nq_pad * p.n_seg;
+        std::fprintf(stderr,
+                     "[b2 gemm refine] per MMA warp: %.1f Mcycles, waiting for a free accumulator %.1f, for operands %.1f; "
+                     "epilogue warp 0 waiting for a full accumulator %.1f (per CTA); per (query, segment): %.1f insertions, "
+                     "%.1f log entries; %.2f compactions per warp-item\n",
+                     st[6] / units / 1e6, st[0] / units / 1e6, st[1] / units / 1e6, st[2] / (double)grid / 1e6,
+                     st[3] / lanes, st[4] / lanes, st[5] / ((double)p.n_items * cg * 4));
     }
     if (rc == B2_OK) {  // fix-up: the all-exact kernel over the flagged query groups only (normally none)
         GemmParams px = p;
         px.refine = 0;
         px.only_flagged = 1;
+        px.stats = nullptr;
         px.kstages = (int)(kbytes_x / swb_x);
         px.num_stages = stages_x;
         px.corr_slots = corr_x;
