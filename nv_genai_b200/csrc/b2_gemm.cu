@@ -843,6 +843,21 @@ __global__ void band_kernel(const float* __restrict__ q, int nq, int d, int nq_p
     }
 }
 
+}  // namespace
+
+int compute_band(const float* q_dev, int nq, int d, int nq_pad, int steps, bool bf16_operands, bool l2,
+                 const uint32_t* max_norm_ord, const uint32_t* row_err_ord, float* band, cudaStream_t stream) {
+    const int blocks = (nq_pad + 7) / 8;
+    if (bf16_operands)
+        band_kernel<0><<<blocks, 256, 0, stream>>>(q_dev, nq, d, nq_pad, steps, l2 ? 1 : 0, max_norm_ord, row_err_ord, band);
+    else
+        band_kernel<1><<<blocks, 256, 0, stream>>>(q_dev, nq, d, nq_pad, steps, l2 ? 1 : 0, max_norm_ord, row_err_ord, band);
+    B2_AFTER_LAUNCH();
+    return B2_OK;
+}
+
+namespace {
+
 size_t gemm_smem_bytes(bool fp32_rows, int na, int swb, int stages, int k, int cg = 1, int corr_slots = 2) {
     const size_t stage = (size_t)na * kTileM * swb + (size_t)(kTileN / cg) * swb;
     const size_t corr = fp32_rows ? (size_t)corr_slots * (kTileN / cg) * swb : 0;
@@ -1246,20 +1261,9 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     }
     if (rc == B2_OK) rc = prep_queries(q_dev, (int)nq, d, p.nq_pad, kp, 1, abf16, A, qn, p.tau, stream, 0);
     if (rc == B2_OK) rc = prep_queries(q_dev, (int)nq, d, p.nq_pad, kp_x, 2, bf16, Ax, nullptr, nullptr, stream, bf16 ? 0 : swb_x / 4);
-    if (rc == B2_OK) {
-        const int blocks = (p.nq_pad + 7) / 8;
-        const int steps = abf16 ? kp / 16 : kp / 8;
-        const uint32_t* row_err = approx != nullptr ? approx->err_ord : nullptr;
-        if (abf16)
-            band_kernel<0><<<blocks, 256, 0, stream>>>(q_dev, (int)nq, d, p.nq_pad, steps, metric == B2_METRIC_L2, max_norm_ord, row_err, band);
-        else
-            band_kernel<1><<<blocks, 256, 0, stream>>>(q_dev, (int)nq, d, p.nq_pad, steps, metric == B2_METRIC_L2, max_norm_ord, row_err, band);
-        B2_COUNT_LAUNCH();
-        if (cudaGetLastError() != cudaSuccess) {
-            set_error("band kernel launch failed");
-            rc = B2_ERR_CUDA;
-        }
-    }
+    if (rc == B2_OK)
+        rc = compute_band(q_dev, (int)nq, d, p.nq_pad, abf16 ? kp / 16 : kp / 8, abf16, metric == B2_METRIC_L2, max_norm_ord,
+                          approx != nullptr ? approx->err_ord : nullptr, band, stream);
     const size_t smem = gemm_smem_bytes(false, 1, swb, stages, k, cg, 0);
     static const bool debug_t = std::getenv("B2_GEMM_DEBUG") != nullptr;
     cudaEvent_t dbg_ev0 = nullptr;

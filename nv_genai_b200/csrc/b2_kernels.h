@@ -46,14 +46,19 @@ struct PeerPush {
 // b2_merge.cu --------------------------------------------------------------
 // partial: [nq][nlists][k] candidates (pos = local row id) -> D/I [nq][k] with I = id_base + pos.
 // qnorm (optional, L2 only): keys are 2 q.x - |x|^2 and D = max(0, qnorm[q] - key) (the BLAS-path form).
+// only_if (optional, device, [nq]): query q is merged only when only_if[q] != 0 (fix-up launches).
 int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metric, int64_t id_base, float* D,
                    int64_t* I, size_t out_stride, cudaStream_t stream, const float* qnorm = nullptr,
-                   const PeerPush* push = nullptr);
+                   const PeerPush* push = nullptr, const uint32_t* only_if = nullptr);
 // refine mode of the tensor-core kernel: merge by approximate key, re-score the candidates near the cut exactly
 // (fp32 FMA dot of q_dev[q] with the stored row), emit the exact top-k.  partial: [nq][nlists][list_len].
 int merge_rescore(const uint64_t* partial, int nq, int nlists, int list_len, int k, int metric, float* D, int64_t* I,
                   size_t out_stride, cudaStream_t stream, const float* qnorm, const float* q_dev, int d, const void* rows,
-                  size_t pitch_bytes, int dtype, const float* norms, const float* band, const PeerPush* push = nullptr);
+                  size_t pitch_bytes, int dtype, const float* norms, const float* band, const PeerPush* push = nullptr,
+                  uint32_t* overflow = nullptr);
+// overflow (optional, device, [nq + 1], zeroed by the caller): the lists are sorted best-first and may have dropped
+// candidates beyond list_len; a query whose cut reaches into a full list's last entry gets overflow[q] = 1 (and
+// overflow[nq] = 1) and NO output: the caller redoes it exactly.  Needs nlists * list_len <= 12288.
 // merge of exchanged blocks that first waits (per query) for every part's flag to reach `epoch`
 int merge_shards_wait(int metric, int nq, int k, int nparts, const char* blocks, size_t part_stride_bytes,
                       const uint32_t* flags, size_t flag_stride_elems, uint32_t epoch, const int64_t* id_bases, float* D,
@@ -88,6 +93,10 @@ int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtyp
                 const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream,
                 const PeerPush* push = nullptr, int query_parts = 0, const uint32_t* max_norm_ord = nullptr,
                 const ApproxRows* approx = nullptr);
+// band[q] = 2 x a rigorous bound on |approximate score - exact score| for one-product tensor-core scoring of query q
+// (bf16 or tf32 operands, `steps` accumulation steps, rows bounded by max_norm_ord, optional row rounding error).
+int compute_band(const float* q_dev, int nq, int d, int nq_pad, int steps, bool bf16_operands, bool l2,
+                 const uint32_t* max_norm_ord, const uint32_t* row_err_ord, float* band, cudaStream_t stream);
 // true when gemm_search with these options would run filter-and-refine (and so can use a bf16 shadow of fp32 rows)
 bool gemm_uses_refine(int query_parts, const uint32_t* max_norm_ord);
 // (D_parts, I_parts): [nparts][nq][k] -> [nq][k]
@@ -121,8 +130,10 @@ int mmr_select(const float* q, int d, int nq, const float* cand_rows /*[nq][fetc
 // b2_scan_tc.cu ------------------------------------------------------------
 // Tensor-core scan for 3..16 queries (inner product): the corpus is the M operand, HBM-bound.
 bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t nq);
+// max_norm_ord (optional): enables the approximate (filter-and-refine) mode on fp32 rows.
 int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, const float* q_dev, int nq, int k,
-                   int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push = nullptr);
+                   int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push = nullptr,
+                   const uint32_t* max_norm_ord = nullptr);
 
 // b2_synth.cu --------------------------------------------------------------
 int synth_fill(float* out, int64_t row0, int64_t nrows, int d, uint64_t seed, cudaStream_t stream);

@@ -76,10 +76,12 @@ __global__ void __launch_bounds__(kMergeThreads) merge_partials_kernel(const uin
                                                                       int metric, int64_t id_base, float* D,
                                                                       int64_t* I, size_t out_stride,
                                                                       const float* __restrict__ qnorm,
-                                                                      const PeerPush push) {
+                                                                      const PeerPush push,
+                                                                      const uint32_t* __restrict__ only_if) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw);
     const int q = blockIdx.x, tid = threadIdx.x;
+    if (only_if != nullptr && only_if[q] == 0u) return;
     const uint64_t* in = partial + (size_t)q * total;
     const int cap = sort_n - kpad;
     for (int i = tid; i < kpad; i += kMergeThreads) buf[i] = B2_SENTINEL;
@@ -127,9 +129,11 @@ __global__ void __launch_bounds__(kMergeThreads) merge_partials_small_kernel(con
                                                                             int64_t id_base, float* D, int64_t* I,
                                                                             size_t out_stride,
                                                                             const float* __restrict__ qnorm,
-                                                                            const PeerPush push) {
+                                                                            const PeerPush push,
+                                                                            const uint32_t* __restrict__ only_if) {
     __shared__ uint64_t lists[kMergeThreads / 32][32];
     const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (only_if != nullptr && only_if[q] == 0u) return;
     constexpr int kWarps = kMergeThreads / 32;
     const uint64_t* in = partial + (size_t)q * total;
     uint64_t best = B2_SENTINEL;
@@ -154,7 +158,8 @@ __global__ void __launch_bounds__(kMergeThreads) merge_partials_small_kernel(con
 }
 
 int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metric, int64_t id_base, float* D,
-                   int64_t* I, size_t out_stride, cudaStream_t stream, const float* qnorm, const PeerPush* push_in) {
+                   int64_t* I, size_t out_stride, cudaStream_t stream, const float* qnorm, const PeerPush* push_in,
+                   const uint32_t* only_if) {
     const int kpad = next_pow2(k < 32 ? 32 : k);
     const int total = nlists * k;
     PeerPush push;
@@ -171,7 +176,7 @@ int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metri
     }
     if (kpad == 32) {
         merge_partials_small_kernel<<<nq, kMergeThreads, 0, stream>>>(partial, total, k, metric, id_base, D, I,
-                                                                      out_stride, qnorm, push);
+                                                                      out_stride, qnorm, push, only_if);
         B2_AFTER_LAUNCH();
         return B2_OK;
     }
@@ -180,7 +185,7 @@ int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metri
     while (sort_n < want && sort_n < 4096) sort_n <<= 1;
     const size_t smem = (size_t)sort_n * sizeof(uint64_t);
     merge_partials_kernel<<<nq, kMergeThreads, smem, stream>>>(partial, total, k, kpad, sort_n, metric, id_base, D, I,
-                                                               out_stride, qnorm, push);
+                                                               out_stride, qnorm, push, only_if);
     B2_AFTER_LAUNCH();
     return B2_OK;
 }
@@ -294,7 +299,8 @@ __global__ void __launch_bounds__(kMergeThreads) merge_rescore_select_kernel(con
                                                                             int k, int kpad, int sort_n, int metric,
                                                                             float* D, int64_t* I, size_t out_stride,
                                                                             const float* __restrict__ qnorm,
-                                                                            const RescoreCtx ctx, const PeerPush push) {
+                                                                            const RescoreCtx ctx, const PeerPush push,
+                                                                            uint32_t* __restrict__ overflow, int list_len) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw);  // [sort_n]: running best kpad, then this round's re-scored candidates
     __shared__ int cnt_s[2][kMergeThreads / 32];
@@ -326,9 +332,20 @@ __global__ void __launch_bounds__(kMergeThreads) merge_rescore_select_kernel(con
     // prefix == 0: fewer than k candidates, everything is re-scored
     const float cut = (prefix == 0u) ? -__builtin_huge_valf() : ord2f(prefix) - ctx.band[q];
     uint32_t pending = 0;  // bit r: entry r still has to be re-scored
+    bool cut_in_last = false;  // a sorted, full list whose LAST entry is above the cut may have dropped candidates
 #pragma unroll
     for (int r = 0; r < kSelMaxPerThread; ++r)
-        if ((uint32_t)e[r] != 0u && cand_key(e[r]) > cut) pending |= 1u << r;
+        if ((uint32_t)e[r] != 0u && cand_key(e[r]) > cut) {
+            pending |= 1u << r;
+            if (overflow != nullptr && (tid + r * kMergeThreads) % list_len == list_len - 1) cut_in_last = true;
+        }
+    if (overflow != nullptr && __syncthreads_or(cut_in_last ? 1 : 0)) {
+        if (tid == 0) {
+            overflow[q] = 1u;
+            overflow[gridDim.x] = 1u;
+        }
+        return;  // no output for this query: the caller's exact fix-up launch produces it
+    }
     const float* qrow = ctx.q + (size_t)q * ctx.d;
     for (int i = tid; i < kpad; i += kMergeThreads) buf[i] = B2_SENTINEL;
     // ---- rounds of at most `cap` candidates (one round unless the data is full of near-ties)
@@ -374,7 +391,8 @@ __global__ void __launch_bounds__(kMergeThreads) merge_rescore_select_kernel(con
 
 int merge_rescore(const uint64_t* partial, int nq, int nlists, int list_len, int k, int metric, float* D, int64_t* I,
                   size_t out_stride, cudaStream_t stream, const float* qnorm, const float* q_dev, int d, const void* rows,
-                  size_t pitch_bytes, int dtype, const float* norms, const float* band, const PeerPush* push_in) {
+                  size_t pitch_bytes, int dtype, const float* norms, const float* band, const PeerPush* push_in,
+                  uint32_t* overflow) {
     const int kpad = next_pow2(k < 32 ? 32 : k);
     const int total = nlists * list_len;
     PeerPush push;
@@ -406,9 +424,13 @@ int merge_rescore(const uint64_t* partial, int nq, int nlists, int list_len, int
         // a round holds up to sort_n - kpad re-scored candidates; 1024 is plenty (k + in-band entries, typically < 300)
         const int sel_sort_n = std::max(2 * kpad, 1024);
         merge_rescore_select_kernel<<<nq, kMergeThreads, (size_t)sel_sort_n * sizeof(uint64_t), stream>>>(
-            partial, total, k, kpad, sel_sort_n, metric, D, I, out_stride, qnorm, ctx, push);
+            partial, total, k, kpad, sel_sort_n, metric, D, I, out_stride, qnorm, ctx, push, overflow, list_len);
         B2_AFTER_LAUNCH();
         return B2_OK;
+    }
+    if (overflow != nullptr) {
+        set_error("merge_rescore: %d candidates per query are too many for the overflow check", total);
+        return B2_ERR_UNSUPPORTED;
     }
     merge_rescore_kernel<<<nq, kMergeThreads, smem, stream>>>(partial, total, k, kpad, sort_n, metric, D, I, out_stride,
                                                               qnorm, ctx, push);

@@ -55,7 +55,9 @@ constexpr int kThreadsBf16 = 192, kThreadsFp32 = 192 + kXfWarps * 32;
 struct ScanTcParams {
     uint32_t n;
     int nq, k, kpad, kslices, n_tiles, num_stages;
-    uint64_t* partial;  // [nq][gridDim.x][k] sorted best-first
+    int klist;                // entries each (warp, query) list keeps and each CTA emits: k, or kpad in the approximate mode
+    uint64_t* partial;        // [nq][gridDim.x][klist] sorted best-first
+    const uint32_t* run_if;   // not null: the whole launch is skipped unless *run_if != 0 (fix-up launch of the approximate mode)
 };
 
 __device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
@@ -81,15 +83,20 @@ __device__ __forceinline__ void epi_bitonic_desc(uint64_t* buf, int n, int tid) 
 }
 
 // KIND 0: bf16 rows (kind::f16).  KIND 1: fp32 rows (kind::tf32, 3xTF32).  NQ: queries per pass (16, 32, 64).
-template <int KIND, int NQ>
-__global__ void __launch_bounds__(KIND == 1 ? kThreadsFp32 : kThreadsBf16, 1)
+// APX (fp32 rows only): filter-and-refine.  ONE tf32 product per score straight from the raw tile -- no q_lo half, no
+// transform warps, no A_lo in TMEM -- so the kernel has nothing left to do but stream the rows; each CTA emits its
+// kpad (> k) best approximate candidates per query, and merge_rescore re-scores in fp32 everything within the error
+// band of the k-th best (b2_merge.cu).  A query whose band does not fit a CTA's list is redone by the exact kernel.
+template <int KIND, int NQ, bool APX>
+__global__ void __launch_bounds__((KIND == 1 && !APX) ? kThreadsFp32 : kThreadsBf16, 1)
 scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant__ CUtensorMap tmQ, const ScanTcParams p) {
+    if (p.run_if != nullptr && *p.run_if == 0u) return;  // uniform over the grid, before anything is allocated
     constexpr int ELEM = (KIND == 0) ? 2 : 4;
     constexpr int KSLICE = kSlice / ELEM;
     constexpr uint32_t FMT = (KIND == 0) ? 1u : 2u;
     constexpr uint32_t IDESC_BASE = (1u << 4) | (FMT << 7) | (FMT << 10) | ((uint32_t)(kTileRows >> 4) << 24);
     constexpr int kNQ = NQ;
-    constexpr int kBTile = 2 * NQ * kSlice;          // [q_hi; q_lo]: 4 / 8 / 16 KB
+    constexpr int kBTile = (APX ? 1 : 2) * NQ * kSlice;  // [q_hi; q_lo]: 4 / 8 / 16 KB (q_hi alone when APX)
     constexpr int kStage = kATile + kBTile;
     constexpr uint32_t IDESC_N32 = IDESC_BASE | (((uint32_t)(2 * NQ) >> 3) << 17);  // D1: N = 2 NQ
     constexpr uint32_t IDESC_N16 = IDESC_BASE | (((uint32_t)NQ >> 3) << 17);        // D2: N = NQ
@@ -97,8 +104,8 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
     // slices.  With -DB2_SCAN_TC_CHAINS4=1 the four 32-byte K steps of a slice accumulate into four independent
     // chains that the epilogue adds up (shorter chains halve the truncation bias); measured speed is the same
     // (7.35 / 3.57 ms at 16 queries either way), so the default is one chain and three TMEM loads per tile.
-    constexpr uint32_t kChains = (NQ == 16 && B2_SCAN_TC_CHAINS4) ? kSlice / 32 : 1;  // more queries: one chain (TMEM has 512 columns)
-    constexpr uint32_t kChainCols = 3u * NQ;                    // D1 (2 NQ) + D2 (NQ)
+    constexpr uint32_t kChains = (NQ == 16 && B2_SCAN_TC_CHAINS4 && !APX) ? kSlice / 32 : 1;  // more queries: one chain (TMEM has 512 columns)
+    constexpr uint32_t kChainCols = APX ? (uint32_t)NQ : 3u * NQ;  // D1 (2 NQ) + D2 (NQ); APX: D1 (NQ)
     constexpr uint32_t kBufCols = kChains * kChainCols;         // 192 / 96 / 192
     constexpr uint32_t kTmemCols = 512;
     constexpr uint32_t kLoCol0 = 2 * kBufCols;    // 384
@@ -184,7 +191,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
             tcgen05_fence_after();
             const uint32_t dbase = tmem_base + buf * kBufCols;
             for (int ks = 0; ks < p.kslices; ++ks) {
-                mbar_wait(smem_u32((KIND == 1 ? xf_bar : full_bar) + stage), phase);
+                mbar_wait(smem_u32(((KIND == 1 && !APX) ? xf_bar : full_bar) + stage), phase);
                 tcgen05_fence_after();
                 if (elect_one()) {
                     const uint32_t a = smem_u32(stages + (size_t)stage * kStage);
@@ -195,14 +202,14 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
                     for (int j = 0; j < kSlice / 32; ++j) {
                         const uint32_t acc = (kChains == 1 ? (ks | j) : ks) ? 1u : 0u;
                         const uint32_t d1 = dbase + (kChains == 1 ? 0u : j * kChainCols), d2 = d1 + 2u * NQ;
-                        umma<KIND>(d1, ad + (uint64_t)(j * 2), bd + (uint64_t)(j * 2), IDESC_N32, acc);  // +32 B in the address field
-                        if (KIND == 1) umma_tf32_ts(d2, alo + j * 8, bd + (uint64_t)(j * 2), IDESC_N16, acc);
+                        umma<KIND>(d1, ad + (uint64_t)(j * 2), bd + (uint64_t)(j * 2), APX ? IDESC_N16 : IDESC_N32, acc);  // +32 B in the address field
+                        if (KIND == 1 && !APX) umma_tf32_ts(d2, alo + j * 8, bd + (uint64_t)(j * 2), IDESC_N16, acc);
                     }
                     tcgen05_commit(smem_u32(empty_bar + stage));
-                    if (KIND == 1) tcgen05_commit(smem_u32(lo_empty_bar + lo_slot));
+                    if (KIND == 1 && !APX) tcgen05_commit(smem_u32(lo_empty_bar + lo_slot));
                 }
                 __syncwarp();
-                if (KIND == 1 && ++lo_slot == kLoSlots) lo_slot = 0;
+                if (KIND == 1 && !APX && ++lo_slot == kLoSlots) lo_slot = 0;
                 if (++stage == S) {
                     stage = 0;
                     phase ^= 1u;
@@ -213,7 +220,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
         }
     } else if (warp >= 6) {
         // ================= fp32 rows: A_lo = x - trunc_tf32(x), thread = row, written to TMEM
-        if (KIND == 1) {
+        if (KIND == 1 && !APX) {
             const int quarter = warp & 3;                 // the TMEM lanes this warp may touch: 32 * (warp % 4) ..
             const int half = (warp - 6) >> 2;             // which 64 bytes of the 128-byte row slice
             const int r = quarter * 32 + lane;            // row of the tile = TMEM lane
@@ -270,14 +277,14 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
                 for (int c = 0; c < (int)kChains; ++c) {
                     uint32_t dh[16], dl[16], d2[16];
                     tmem_ld16(taddr + c * kChainCols + g * 16u, dh);
-                    tmem_ld16(taddr + c * kChainCols + NQ + g * 16u, dl);
-                    if (KIND == 1) tmem_ld16(taddr + c * kChainCols + 2u * NQ + g * 16u, d2);
+                    if (!APX) tmem_ld16(taddr + c * kChainCols + NQ + g * 16u, dl);
+                    if (KIND == 1 && !APX) tmem_ld16(taddr + c * kChainCols + 2u * NQ + g * 16u, d2);
                     tmem_ld_wait();
 #pragma unroll
                     for (int j = 0; j < 16; ++j) {
                         big[j] += __uint_as_float(dh[j]);
-                        small[j] += __uint_as_float(dl[j]);
-                        if (KIND == 1) small[j] += __uint_as_float(d2[j]);
+                        if (!APX) small[j] += __uint_as_float(dl[j]);
+                        if (KIND == 1 && !APX) small[j] += __uint_as_float(d2[j]);
                     }
                 }
                 if (g == NQ / 16 - 1) {
@@ -298,7 +305,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
                             const int src = __ffs(m) - 1;
                             m &= m - 1;
                             const uint64_t c = shfl_u64(cand, src);
-                            warp_list_insert(lists + (size_t)li * p.kpad, p.k, c, worst_s + li, worstpos_s + li, lane);
+                            warp_list_insert(lists + (size_t)li * p.kpad, p.klist, c, worst_s + li, worstpos_s + li, lane);
                         }
                     }
                 }
@@ -309,8 +316,8 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
         for (int qi = 0; qi < p.nq; ++qi) {
             uint64_t* buf = lists + (size_t)qi * region;
             epi_bitonic_desc(buf, region, tid);
-            uint64_t* out = p.partial + ((size_t)qi * gridDim.x + blockIdx.x) * p.k;
-            for (int i = tid; i < p.k; i += kEpi) out[i] = buf[i];
+            uint64_t* out = p.partial + ((size_t)qi * gridDim.x + blockIdx.x) * p.klist;
+            for (int i = tid; i < p.klist; i += kEpi) out[i] = buf[i];
         }
     }
 
@@ -322,8 +329,8 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
     }
 }
 
-size_t scan_tc_smem_bytes(int nqt, int stages, int kpad) {
-    const size_t stage = (size_t)kATile + (size_t)2 * nqt * kSlice;
+size_t scan_tc_smem_bytes(int nqt, int stages, int kpad, int parts = 2) {
+    const size_t stage = (size_t)kATile + (size_t)parts * nqt * kSlice;
     return 1024 + (size_t)stages * stage + (size_t)nqt * kEpiWarps * kpad * 8 + (size_t)nqt * kEpiWarps * 12 +
            (3 * kMaxStages + kLoSlots + 4) * 8 + 16;
 }
@@ -335,10 +342,10 @@ int scan_tc_max_queries(int k) {
     return std::min(kMaxNQ, 2048 / kpad);  // kpad 32, 64 -> 32 queries, 128 -> 16
 }
 
-template <int KIND, int NQ>
+template <int KIND, int NQ, bool APX = false>
 int launch_scan_tc(const CUtensorMap& tmRows, const CUtensorMap& tmQ, const ScanTcParams& p, int grid, size_t smem,
                    cudaStream_t stream) {
-    auto kern = scan_tc_kernel<KIND, NQ>;
+    auto kern = scan_tc_kernel<KIND, NQ, APX>;
     static std::mutex mu;
     static size_t attr[64] = {0};
     int dev = 0;
@@ -350,8 +357,8 @@ int launch_scan_tc(const CUtensorMap& tmRows, const CUtensorMap& tmQ, const Scan
             attr[dev & 63] = smem;
         }
     }
-    void* tok = prof_begin(stream);
-    kern<<<grid, KIND == 1 ? kThreadsFp32 : kThreadsBf16, smem, stream>>>(tmRows, tmQ, p);
+    void* tok = p.run_if != nullptr ? nullptr : prof_begin(stream);  // the (normally skipped) fix-up launch is not the profiled kernel
+    kern<<<grid, (KIND == 1 && !APX) ? kThreadsFp32 : kThreadsBf16, smem, stream>>>(tmRows, tmQ, p);
     prof_end(tok, 0, stream);
     B2_AFTER_LAUNCH();
     return B2_OK;
@@ -372,10 +379,91 @@ bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t n
            n < ((int64_t)1 << 31) && (int64_t)d * elem >= kSlice;
 }
 
+// fp32 rows, k <= 64: filter and refine (see scan_tc_kernel, APX).  Launches: prep (1 part) + band + approximate scan +
+// merge_rescore, then the exact fix-up -- prep (2 parts) + exact scan + merge -- whose kernels return at once unless
+// merge_rescore raised a query's overflow flag (never seen on real data: a CTA would have to hold kpad candidates within
+// the error band of the k-th best).
+static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes, int d, const float* q_dev, int nq, int k,
+                                 int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push,
+                                 const uint32_t* max_norm_ord) {
+    const size_t kbytes = (((size_t)d * 4 + kSlice - 1) / kSlice) * kSlice;
+    const int kp = (int)(kbytes / 4);
+    ScanTcParams p;
+    p.n = (uint32_t)n;
+    p.nq = nq;
+    p.k = k;
+    p.kpad = next_pow2(k < 32 ? 32 : k);
+    p.klist = p.kpad;
+    p.kslices = (int)(kbytes / kSlice);
+    p.n_tiles = (int)((n + kTileRows - 1) / kTileRows);
+    p.run_if = nullptr;
+    const int nqt = nq <= 16 ? 16 : 32;
+    int stages = kMaxStages, stages_x = kMaxStages;
+    while (stages > 2 && scan_tc_smem_bytes(nqt, stages, p.kpad, 1) > 227 * 1024) --stages;
+    while (stages_x > 2 && scan_tc_smem_bytes(nqt, stages_x, p.kpad, 2) > 227 * 1024) --stages_x;
+    const size_t smem = scan_tc_smem_bytes(nqt, stages, p.kpad, 1), smem_x = scan_tc_smem_bytes(nqt, stages_x, p.kpad, 2);
+    if (smem > 227 * 1024 || smem_x > 227 * 1024) {
+        set_error("tensor-core scan: k=%d does not fit shared memory", k);
+        return B2_ERR_UNSUPPORTED;
+    }
+    p.num_stages = stages;
+    const int grid = (int)std::min<long long>(num_sms, p.n_tiles);
+
+    auto al = [](size_t v) { return (v + 1023) / 1024 * 1024; };
+    const size_t q_bytes = al((size_t)nqt * kbytes), qx_bytes = al((size_t)2 * nqt * kbytes);
+    const size_t part_bytes = al((size_t)nq * grid * p.kpad * 8);
+    const size_t band_bytes = al((size_t)nqt * 4), flag_bytes = al((size_t)(nq + 1) * 4);
+    char* blk = nullptr;
+    B2_CUDA_TRY(cudaMallocAsync(&blk, q_bytes + qx_bytes + part_bytes + band_bytes + flag_bytes, stream));
+    void* Q = blk;
+    void* Qx = blk + q_bytes;
+    p.partial = reinterpret_cast<uint64_t*>(blk + q_bytes + qx_bytes);
+    float* band = reinterpret_cast<float*>(blk + q_bytes + qx_bytes + part_bytes);
+    uint32_t* flags = reinterpret_cast<uint32_t*>(blk + q_bytes + qx_bytes + part_bytes + band_bytes);
+
+    CUtensorMap tmRows, tmQ, tmQx;
+    int promo = 256;
+    if (const char* e = getenv("B2_SCAN_TC_L2PROMO")) promo = atoi(e);
+    int rc = make_map(&tmRows, false, kSlice, rows, (uint64_t)(pitch_bytes / 4), (uint64_t)n, pitch_bytes, kTileRows, promo);
+    if (rc == B2_OK) rc = make_map(&tmQ, false, kSlice, Q, (uint64_t)kp, (uint64_t)nqt, kbytes, nqt);
+    if (rc == B2_OK) rc = make_map(&tmQx, false, kSlice, Qx, (uint64_t)kp, (uint64_t)2 * nqt, kbytes, 2 * nqt);
+    if (rc == B2_OK && cudaMemsetAsync(flags, 0, (size_t)(nq + 1) * 4, stream) != cudaSuccess) {
+        set_error("tensor-core scan: cudaMemsetAsync failed");
+        rc = B2_ERR_CUDA;
+    }
+    if (rc == B2_OK) rc = prep_queries(q_dev, nq, d, nqt, kp, 1, false, Q, nullptr, nullptr, stream);
+    if (rc == B2_OK) rc = compute_band(q_dev, nq, d, nqt, kp / 8, false, false, max_norm_ord, nullptr, band, stream);
+    if (rc == B2_OK)
+        rc = nqt == 16 ? launch_scan_tc<1, 16, true>(tmRows, tmQ, p, grid, smem, stream)
+                       : launch_scan_tc<1, 32, true>(tmRows, tmQ, p, grid, smem, stream);
+    if (rc == B2_OK)
+        rc = merge_rescore(p.partial, nq, grid, p.kpad, k, B2_METRIC_IP, D, I, (size_t)k, stream, nullptr, q_dev, d, rows,
+                           pitch_bytes, B2_DTYPE_F32, nullptr, band, push, flags);
+    // ---- exact fix-up for the flagged queries (each kernel returns immediately when there is none)
+    if (rc == B2_OK) rc = prep_queries(q_dev, nq, d, nqt, kp, 2, false, Qx, nullptr, nullptr, stream);
+    if (rc == B2_OK) {
+        ScanTcParams px = p;
+        px.klist = k;
+        px.num_stages = stages_x;
+        px.run_if = flags + nq;
+        rc = nqt == 16 ? launch_scan_tc<1, 16>(tmRows, tmQx, px, grid, smem_x, stream)
+                       : launch_scan_tc<1, 32>(tmRows, tmQx, px, grid, smem_x, stream);
+    }
+    if (rc == B2_OK)
+        rc = merge_partials(p.partial, nq, grid, k, B2_METRIC_IP, 0, D, I, (size_t)k, stream, nullptr, push, flags);
+    cudaFreeAsync(blk, stream);
+    return rc;
+}
+
 int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, const float* q_dev, int nq, int k,
-                   int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push) {
+                   int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push,
+                   const uint32_t* max_norm_ord) {
     const bool bf16 = dtype == B2_DTYPE_BF16;
     const int elem = bf16 ? 2 : 4;
+    static const bool no_approx = getenv("B2_SCAN_TC_EXACT") != nullptr;
+    if (!bf16 && max_norm_ord != nullptr && !no_approx && k <= 64 &&
+        (long long)std::min<long long>(num_sms, (n + kTileRows - 1) / kTileRows) * next_pow2(k < 32 ? 32 : k) <= 12288)
+        return scan_tc_search_approx(rows, n, pitch_bytes, d, q_dev, nq, k, num_sms, D, I, stream, push, max_norm_ord);
     const size_t kbytes = (((size_t)d * elem + kSlice - 1) / kSlice) * kSlice;
     const int kp = (int)(kbytes / elem);
 
@@ -383,6 +471,8 @@ int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int d
     p.n = (uint32_t)n;
     p.nq = nq;
     p.k = k;
+    p.klist = k;
+    p.run_if = nullptr;
     p.kpad = next_pow2(k < 32 ? 32 : k);
     p.kslices = (int)(kbytes / kSlice);
     p.n_tiles = (int)((n + kTileRows - 1) / kTileRows);

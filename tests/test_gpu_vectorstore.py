@@ -119,7 +119,7 @@ def test_normalize_l2_store_and_mmr_and_async():
 
 def test_concurrent_single_vector_searches_are_coalesced_into_batched_scans():
     """faiss_vdb_service.py:169-174 fires many asimilarity_search_by_vector at once: with request batching on, they
-    share scans of the corpus (fewer kernel launches) and return what the one-at-a-time searches return."""
+    share scans of the corpus (fewer passes over the rows) and return what the one-at-a-time searches return."""
     from nv_genai_b200 import FAISS, IndexFlatIP, InMemoryDocstore, DistanceStrategy, _native
 
     emb = HashEmbeddings(D)
@@ -131,22 +131,24 @@ def test_concurrent_single_vector_searches_are_coalesced_into_batched_scans():
     qs = flat.synth(0, 48, D, 78)
     flat.normalize_L2(qs)
     want = [vs.similarity_search_with_score_by_vector(q.tolist(), k=5) for q in qs]
-    _native.launch_count_reset()
+    _native.prof_enable(True)  # counts the scan kernels = passes over the rows
+    _native.prof_read(reset=True)
     for q in qs[:8]:
         vs.similarity_search_with_score_by_vector(q.tolist(), k=5)
-    alone = _native.launch_count() / 8
+    alone = _native.prof_read(reset=True)[1] / 8
+    assert alone == 1
 
     vs.enable_request_batching(max_batch=16, max_wait_us=20_000)
     try:
         async def fire():
             return await asyncio.gather(*[vs.asimilarity_search_with_score_by_vector(q.tolist(), k=5) for q in qs])
 
-        _native.launch_count_reset()
         got = asyncio.run(fire())
-        launches = _native.launch_count()
+        passes = _native.prof_read(reset=True)[1]
     finally:
         vs.disable_request_batching()
-    assert launches < alone * len(qs) * 0.6, (launches, alone)  # scans were shared
+        _native.prof_enable(False)
+    assert passes < alone * len(qs) * 0.6, (passes, alone)  # scans were shared
     for a, b in zip(got, want):
         assert [d.page_content for d, _ in a] == [d.page_content for d, _ in b]
         np.testing.assert_allclose([float(s) for _, s in a], [float(s) for _, s in b], rtol=1e-5, atol=1e-6)
