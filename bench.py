@@ -480,17 +480,20 @@ def run_b200(a):
         k_avg_ms = k_ms / max(k_n, 1)
         if tensor:
             fp32_rows = dtype != "bfloat16"
-            tpeak, tsrc = measured_tensor_peak(fp32_rows)
             flops = 2.0 * batch * (hi - lo) * a.dim  # algorithmic: one product per (query, row, dim)
             # default: filter and refine = ONE approximate product per score on the tensor cores (the candidates near
             # the cut are re-scored in fp32 by the merge kernel); the all-exact arithmetic (B2_GEMM_REFINE=0 or an
             # explicit number of query parts) issues 2 (bf16 rows) / 3 (fp32 rows) products per score
             refine = os.environ.get("B2_GEMM_REFINE", "1") != "0" and "B2_GEMM_QUERY_PARTS" not in os.environ
+            # fp32 rows under refine are filtered through their bf16 shadow: the approximate pass is a bf16 product
+            shadow = fp32_rows and refine and "B2_NO_SHADOW" not in os.environ and "B2_NO_VMM" not in os.environ
+            tpeak, tsrc = measured_tensor_peak(fp32_rows and not shadow)
             products = 1 if refine else (3 if fp32_rows else 2)
             achieved = flops / (k_avg_ms * 1e-3) / 1e12 if k_n else None
             roof = {"bound": "tensor", "achieved": achieved, "peak": tpeak, "unit": "TFLOP/s",
                     "frac": (achieved / tpeak) if achieved else None, "traffic": None,
-                    "kernel": "gemm_topk_kernel (%s)" % ("approximate pass of filter-and-refine" if refine else "all-exact"),
+                    "kernel": "gemm_topk_kernel (%s)" % (("approximate pass of filter-and-refine" +
+                                                          (", bf16 shadow of the fp32 rows" if shadow else "")) if refine else "all-exact"),
                     "algorithmic_flops_per_launch": flops,
                     "mma_products_per_score": products,
                     "issued_mma_tflops": (achieved * products * (-(-batch // 128) * 128) / batch) if achieved else None,

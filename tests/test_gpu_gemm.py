@@ -330,3 +330,27 @@ def test_bf16_shadow_of_fp32_rows_filters_and_the_fp32_rows_decide(metric):
     D, I = idx.search(q, 10)
     Dr, Ir = flat.search_f64(x[:8_000], q, 10, metric)
     assert_parity(D, I, Dr.astype(np.float32), Ir, x[:8_000], q, metric_ip=(metric == flat.METRIC_IP))
+
+
+@pytest.mark.parametrize("dtype,nq", [("float32", 8), ("float32", 70), ("bfloat16", 70)])
+def test_more_near_ties_than_the_candidate_lists_hold_take_the_exact_fix_up(dtype, nq):
+    """Filter-and-refine keeps k + slack approximate candidates per list.  90 copies of one query packed into
+    neighbouring rows put more candidates inside the error band of that query's k-th best than a list holds: the
+    query (scan) or its query group (GEMM) is flagged and redone by the exact kernel.  The answer must still be the
+    lowest ids among the copies, and the other queries must be unaffected."""
+    n, d, k = 30_000, 256, 10
+    x, q = _data(n, d, nq, True, seed=91)
+    copies = np.arange(1000, 1090)
+    x[copies] = q[0]
+    x[20_000:20_005] = q[1]  # a second query with a handful of ties: stays on the normal path
+    idx = _mk(flat.METRIC_IP, d, dtype)
+    idx.add(x)
+    D, I = idx.search(q, k)
+    assert np.array_equal(I[0], copies[:k]), I[0]
+    assert np.array_equal(I[1, :5], np.arange(20_000, 20_005))
+    xr = flat.round_bf16(x) if dtype == "bfloat16" else x
+    Dr, Ir = flat.search_f64(xr, q, k, flat.METRIC_IP)
+    assert_parity(D, I, Dr.astype(np.float32), Ir, xr, q, metric_ip=True)
+    # k = 60: still more copies than k, list = 64 (scan) / k + slack (GEMM)
+    D, I = idx.search(q, 60)
+    assert np.array_equal(I[0], copies[:60])
