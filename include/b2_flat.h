@@ -180,7 +180,11 @@ B2_API int b2_filter_results(int metric, int64_t nq, int fetch_k, int k, const f
  * every candidate within a rigorous error band of the k-th best is re-scored exactly in fp32, so results equal
  * the all-exact arithmetic; 2 = all-exact tensor-core arithmetic (query split into hi + lo parts; tf32 main +
  * bf16 correction product on fp32 rows); 1 = single part without re-scoring: scores then carry the bf16 (or tf32)
- * rounding of the query, recall@100 0.9952 instead of 0.9970 at 10M x 1024 bf16. */
+ * rounding of the query, recall@100 0.9952 instead of 0.9970 at 10M x 1024 bf16.
+ * "bf16_shadow" (fp32 rows; default 1): keep a bf16 copy of the rows (+2 bytes per element of HBM, built by the
+ * first batch of >= 20 queries, kept current across add / remove_ids) that the approximate product of
+ * filter-and-refine reads instead of the fp32 rows: twice the tensor rate, same results (the fp32 rows decide).
+ * 0 releases the copy.  Skipped silently when the device has no room for it. */
 B2_API int b2_index_set_option(b2_index* h, const char* name, int64_t value);
 
 /* Replaces index.reset(). */

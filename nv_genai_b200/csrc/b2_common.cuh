@@ -130,15 +130,14 @@ __device__ __forceinline__ void warp_list_insert(uint64_t* L, int k, uint64_t c,
             mp = i;
         }
     }
-#pragma unroll
-    for (int s = 16; s >= 1; s >>= 1) {
-        const uint64_t o = shfl_xor_u64(mn, s);
-        const int op = __shfl_xor_sync(kFull, mp, s);
-        if (o < mn || (o == mn && op < mp)) {
-            mn = o;
-            mp = op;
-        }
-    }
+    // warp minimum of a 64-bit value with two 32-bit redux operations (high word, then low word among the lanes that
+    // hold the minimal high word); entries are unique except for sentinels, where any position will do
+    const uint32_t hi = (uint32_t)(mn >> 32), lo = (uint32_t)mn;
+    const uint32_t hmin = __reduce_min_sync(kFull, hi);
+    const uint32_t lmin = __reduce_min_sync(kFull, hi == hmin ? lo : 0xffffffffu);
+    const int src = __ffs(__ballot_sync(kFull, hi == hmin && lo == lmin)) - 1;
+    mp = __shfl_sync(kFull, mp, src);
+    mn = ((uint64_t)hmin << 32) | lmin;
     if (lane == 0) {
         *worst = mn;
         *worstpos = mp;

@@ -55,6 +55,7 @@ constexpr int kThreadsBf16 = 192, kThreadsFp32 = 192 + kXfWarps * 32;
 struct ScanTcParams {
     uint32_t n;
     int nq, k, kpad, kslices, n_tiles, num_stages;
+    int sps;                  // K slices per pipeline stage (1, 2 or 4; kslices % sps == 0; the exact fp32 variant uses 1)
     int klist;                // entries each (warp, query) list keeps and each CTA emits: k, or kpad in the approximate mode
     uint64_t* partial;        // [nq][gridDim.x][klist] sorted best-first
     const uint32_t* run_if;   // not null: the whole launch is skipped unless *run_if != 0 (fix-up launch of the approximate mode)
@@ -114,8 +115,10 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
     const uint32_t raw = smem_u32(smem_raw);
     uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
     const int S = p.num_stages;
+    const int SPS = p.sps;
+    const uint32_t stage_bytes = (uint32_t)SPS * kStage;  // a stage = SPS consecutive K slices of the same 128 rows
     uint8_t* stages = smem;
-    uint64_t* lists = reinterpret_cast<uint64_t*>(stages + (size_t)S * kStage);  // [kNQ][4 warps][kpad]
+    uint64_t* lists = reinterpret_cast<uint64_t*>(stages + (size_t)S * stage_bytes);  // [kNQ][4 warps][kpad]
     uint64_t* worst_s = lists + (size_t)kNQ * kEpiWarps * p.kpad;                                    // [kNQ][4]
     int* worstpos_s = reinterpret_cast<int*>(worst_s + kNQ * kEpiWarps);                             // [kNQ][4]
     uint64_t* bars = reinterpret_cast<uint64_t*>(worstpos_s + kNQ * kEpiWarps);
@@ -165,14 +168,18 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
         int stage = 0;
         uint32_t phase = 0;
         for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-            for (int ks = 0; ks < p.kslices; ++ks) {
+            for (int ks = 0; ks < p.kslices; ks += SPS) {
                 mbar_wait(smem_u32(empty_bar + stage), phase ^ 1u);
                 if (elect_one()) {
                     const uint32_t fb = smem_u32(full_bar + stage);
-                    mbar_expect_tx(fb, (uint32_t)kStage);
-                    const uint32_t sb = smem_u32(stages + (size_t)stage * kStage);
-                    tma_load_2d(sb, &tmRows, ks * KSLICE, tile * kTileRows, fb);
-                    tma_load_2d(sb + kATile, &tmQ, ks * KSLICE, 0, fb);
+                    mbar_expect_tx(fb, stage_bytes);
+                    const uint32_t sb = smem_u32(stages + (size_t)stage * stage_bytes);
+                    // the SPS slices of a row are neighbours in memory and are requested back to back, so DRAM sees
+                    // SPS x 128 contiguous bytes per row instead of 128 bytes from each of 128 different pages
+                    for (int u = 0; u < SPS; ++u) {
+                        tma_load_2d(sb + u * kStage, &tmRows, (ks + u) * KSLICE, tile * kTileRows, fb);
+                        tma_load_2d(sb + u * kStage + kATile, &tmQ, (ks + u) * KSLICE, 0, fb);
+                    }
                 }
                 __syncwarp();
                 if (++stage == S) {
@@ -190,20 +197,22 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
             mbar_wait(smem_u32(tempty_bar + buf), par ^ 1u);
             tcgen05_fence_after();
             const uint32_t dbase = tmem_base + buf * kBufCols;
-            for (int ks = 0; ks < p.kslices; ++ks) {
+            for (int ks = 0; ks < p.kslices; ks += SPS) {
                 mbar_wait(smem_u32(((KIND == 1 && !APX) ? xf_bar : full_bar) + stage), phase);
                 tcgen05_fence_after();
                 if (elect_one()) {
-                    const uint32_t a = smem_u32(stages + (size_t)stage * kStage);
+                    for (int u = 0; u < SPS; ++u) {
+                    const uint32_t a = smem_u32(stages + (size_t)stage * stage_bytes + (size_t)u * kStage);
                     const uint64_t ad = smem_desc<kSlice>(a);
                     const uint64_t bd = smem_desc<kSlice>(a + kATile);
                     const uint32_t alo = tmem_base + kLoCol0 + (uint32_t)lo_slot * 32u;  // TMEM columns of this slice's A_lo
 #pragma unroll
                     for (int j = 0; j < kSlice / 32; ++j) {
-                        const uint32_t acc = (kChains == 1 ? (ks | j) : ks) ? 1u : 0u;
+                        const uint32_t acc = (kChains == 1 ? (ks | u | j) : ks) ? 1u : 0u;
                         const uint32_t d1 = dbase + (kChains == 1 ? 0u : j * kChainCols), d2 = d1 + 2u * NQ;
                         umma<KIND>(d1, ad + (uint64_t)(j * 2), bd + (uint64_t)(j * 2), APX ? IDESC_N16 : IDESC_N32, acc);  // +32 B in the address field
                         if (KIND == 1 && !APX) umma_tf32_ts(d2, alo + j * 8, bd + (uint64_t)(j * 2), IDESC_N16, acc);
+                    }
                     }
                     tcgen05_commit(smem_u32(empty_bar + stage));
                     if (KIND == 1 && !APX) tcgen05_commit(smem_u32(lo_empty_bar + lo_slot));
@@ -231,7 +240,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
                     mbar_wait(smem_u32(full_bar + stage), phase);
                     mbar_wait(smem_u32(lo_empty_bar + lo_slot), lo_phase ^ 1u);
                     tcgen05_fence_after();
-                    const uint8_t* rowp = stages + (size_t)stage * kStage + r * kSlice;
+                    const uint8_t* rowp = stages + (size_t)stage * stage_bytes + r * kSlice;  // SPS == 1 in this variant
                     uint32_t lo[16];
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
@@ -329,8 +338,8 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
     }
 }
 
-size_t scan_tc_smem_bytes(int nqt, int stages, int kpad, int parts = 2) {
-    const size_t stage = (size_t)kATile + (size_t)parts * nqt * kSlice;
+size_t scan_tc_smem_bytes(int nqt, int stages, int kpad, int parts = 2, int sps = 1) {
+    const size_t stage = ((size_t)kATile + (size_t)parts * nqt * kSlice) * sps;
     return 1024 + (size_t)stages * stage + (size_t)nqt * kEpiWarps * kpad * 8 + (size_t)nqt * kEpiWarps * 12 +
            (3 * kMaxStages + kLoSlots + 4) * 8 + 16;
 }
@@ -379,6 +388,25 @@ bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t n
            n < ((int64_t)1 << 31) && (int64_t)d * elem >= kSlice;
 }
 
+// K slices per pipeline stage (see the producer loop) and the number of stages that fit next to the lists.  Measured at
+// 10M x 1024, 16 queries: 1 / 2 / 4 slices per stage -> 6.87 / 6.79 / 6.64 ms on fp32 rows, 3.61 / 3.53 / 3.43 ms on bf16
+// rows (each row then gets its requests 512 contiguous bytes at a time).  The exact fp32 variant needs 1.
+static void pick_pipeline(int kslices, bool sps_allowed, int nqt, int kpad, int parts, int* sps_out, int* stages_out) {
+    int sps = 4;
+    if (const char* e = getenv("B2_SCAN_TC_SPS")) sps = atoi(e);
+    if (!sps_allowed || (sps != 2 && sps != 4)) sps = 1;
+    for (;; sps >>= 1) {
+        int stages = kMaxStages;
+        while (stages > 2 && scan_tc_smem_bytes(nqt, stages, kpad, parts, sps) > 227 * 1024) --stages;
+        const bool fits = scan_tc_smem_bytes(nqt, stages, kpad, parts, sps) <= 227 * 1024;
+        if ((fits && kslices % sps == 0) || sps == 1) {
+            *sps_out = sps;
+            *stages_out = fits ? stages : 0;
+            return;
+        }
+    }
+}
+
 // fp32 rows, k <= 64: filter and refine (see scan_tc_kernel, APX).  Launches: prep (1 part) + band + approximate scan +
 // merge_rescore, then the exact fix-up -- prep (2 parts) + exact scan + merge -- whose kernels return at once unless
 // merge_rescore raised a query's overflow flag (never seen on real data: a CTA would have to hold kpad candidates within
@@ -393,16 +421,19 @@ static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes
     p.nq = nq;
     p.k = k;
     p.kpad = next_pow2(k < 32 ? 32 : k);
-    p.klist = p.kpad;
+    // every list keeps k plus a little room for the candidates inside the error band (a CTA sees 1/148 of the rows: a
+    // full list whose last entry is still inside the band is the rare overflow case).  Longer lists cost insertions
+    // while the thresholds settle: with kpad = 32 entries at k = 10 the start-up phase cost 0.7 ms at 16 queries.
+    p.klist = std::min(p.kpad, k + std::max(4, k / 4));
     p.kslices = (int)(kbytes / kSlice);
     p.n_tiles = (int)((n + kTileRows - 1) / kTileRows);
     p.run_if = nullptr;
     const int nqt = nq <= 16 ? 16 : 32;
-    int stages = kMaxStages, stages_x = kMaxStages;
-    while (stages > 2 && scan_tc_smem_bytes(nqt, stages, p.kpad, 1) > 227 * 1024) --stages;
-    while (stages_x > 2 && scan_tc_smem_bytes(nqt, stages_x, p.kpad, 2) > 227 * 1024) --stages_x;
-    const size_t smem = scan_tc_smem_bytes(nqt, stages, p.kpad, 1), smem_x = scan_tc_smem_bytes(nqt, stages_x, p.kpad, 2);
-    if (smem > 227 * 1024 || smem_x > 227 * 1024) {
+    int stages = 0, stages_x = 0, sps_x = 1;
+    pick_pipeline(p.kslices, true, nqt, p.kpad, 1, &p.sps, &stages);
+    pick_pipeline(p.kslices, false, nqt, p.kpad, 2, &sps_x, &stages_x);
+    const size_t smem = scan_tc_smem_bytes(nqt, stages, p.kpad, 1, p.sps), smem_x = scan_tc_smem_bytes(nqt, stages_x, p.kpad, 2);
+    if (stages == 0 || stages_x == 0) {
         set_error("tensor-core scan: k=%d does not fit shared memory", k);
         return B2_ERR_UNSUPPORTED;
     }
@@ -411,7 +442,7 @@ static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes
 
     auto al = [](size_t v) { return (v + 1023) / 1024 * 1024; };
     const size_t q_bytes = al((size_t)nqt * kbytes), qx_bytes = al((size_t)2 * nqt * kbytes);
-    const size_t part_bytes = al((size_t)nq * grid * p.kpad * 8);
+    const size_t part_bytes = al((size_t)nq * grid * std::max(p.klist, k) * 8);
     const size_t band_bytes = al((size_t)nqt * 4), flag_bytes = al((size_t)(nq + 1) * 4);
     char* blk = nullptr;
     B2_CUDA_TRY(cudaMallocAsync(&blk, q_bytes + qx_bytes + part_bytes + band_bytes + flag_bytes, stream));
@@ -437,13 +468,14 @@ static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes
         rc = nqt == 16 ? launch_scan_tc<1, 16, true>(tmRows, tmQ, p, grid, smem, stream)
                        : launch_scan_tc<1, 32, true>(tmRows, tmQ, p, grid, smem, stream);
     if (rc == B2_OK)
-        rc = merge_rescore(p.partial, nq, grid, p.kpad, k, B2_METRIC_IP, D, I, (size_t)k, stream, nullptr, q_dev, d, rows,
+        rc = merge_rescore(p.partial, nq, grid, p.klist, k, B2_METRIC_IP, D, I, (size_t)k, stream, nullptr, q_dev, d, rows,
                            pitch_bytes, B2_DTYPE_F32, nullptr, band, push, flags);
     // ---- exact fix-up for the flagged queries (each kernel returns immediately when there is none)
     if (rc == B2_OK) rc = prep_queries(q_dev, nq, d, nqt, kp, 2, false, Qx, nullptr, nullptr, stream);
     if (rc == B2_OK) {
         ScanTcParams px = p;
         px.klist = k;
+        px.sps = 1;
         px.num_stages = stages_x;
         px.run_if = flags + nq;
         rc = nqt == 16 ? launch_scan_tc<1, 16>(tmRows, tmQx, px, grid, smem_x, stream)
@@ -477,10 +509,10 @@ int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int d
     p.kslices = (int)(kbytes / kSlice);
     p.n_tiles = (int)((n + kTileRows - 1) / kTileRows);
     const int nqt = nq <= 16 ? 16 : 32;  // query tile of the pass
-    int stages = kMaxStages;
-    while (stages > 2 && scan_tc_smem_bytes(nqt, stages, p.kpad) > 227 * 1024) --stages;
-    const size_t smem = scan_tc_smem_bytes(nqt, stages, p.kpad);
-    if (smem > 227 * 1024) {
+    int stages = 0;
+    pick_pipeline(p.kslices, bf16, nqt, p.kpad, 2, &p.sps, &stages);
+    const size_t smem = scan_tc_smem_bytes(nqt, stages, p.kpad, 2, p.sps);
+    if (stages == 0) {
         set_error("tensor-core scan: k=%d does not fit shared memory", k);
         return B2_ERR_UNSUPPORTED;
     }
