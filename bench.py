@@ -145,6 +145,19 @@ def scan_tc_max_queries(k):
     return 0 if kpad > 128 else min(32, 2048 // kpad)
 
 
+def scan_kernel_name(batch, k, rows, dim, dtype):
+    """Which scan kernel b2_index_search picks for an inner-product batch (b2_scan_tc.cu: scan_tc_supported)."""
+    bf16 = dtype == "bfloat16"
+    min_nq = 3 if bf16 else 5
+    if rows * dim * (2 if bf16 else 4) >= 8e9 and (bf16 or k <= 64):
+        min_nq = 1
+    if "B2_SCAN_TC_MIN_NQ" in os.environ:
+        min_nq = int(os.environ["B2_SCAN_TC_MIN_NQ"])
+    if "B2_NO_TENSOR" in os.environ or "B2_NO_SCAN_TC" in os.environ or rows < 4096:
+        return "scan_topk_kernel"
+    return "scan_tc_kernel" if min_nq <= batch <= scan_tc_max_queries(k) else "scan_topk_kernel"
+
+
 def uses_tensor_path(batch, k, rows):
     """True when b2_index_search sends this batch to the GEMM kernel (tensor-bound), not to a scan (HBM-bound)."""
     return batch >= 20 and k <= 128 and rows >= 4096 and batch > scan_tc_max_queries(k)
@@ -506,8 +519,7 @@ def run_b200(a):
             roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": (achieved / peak) if achieved else None,
                     "traffic": ncu_traffic() if (batch == 1 and dtype == "float32" and world == 1) else None,
-                    "kernel": ("scan_tc_kernel" if (3 if dtype == "bfloat16" else 5) <= batch <= max(16, scan_tc_max_queries(k))
-                               else "scan_topk_kernel"),
+                    "kernel": scan_kernel_name(batch, k, hi - lo, a.dim, dtype),
                     "algorithmic_bytes_per_launch": shard_bytes,
                     "avg_launch_ms": k_avg_ms, "launches_timed": k_n, "peak_source": peak_src,
                     "scan_share_of_step": (k_avg_ms * k_n / ms) if k_n else None, "scan_passes_per_step": per_step}

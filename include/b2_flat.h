@@ -120,8 +120,8 @@ B2_API int b2_index_search(b2_index* h, int64_t nq, const float* q, int q_where,
  *     calls whose kernels overlap on the GPU (different streams, or threads) race on it:
  *     serialise them.
  * It always runs the FFMA scan kernel: results are bit-identical to b2_index_search whenever that runs the same
- * kernel (L2; up to 4 inner-product queries on fp32 rows, 2 on bf16 rows) and within the 1e-5 relative score
- * tolerance where b2_index_search uses the tensor-core scan instead. */
+ * kernel (L2; inner product on a row store under 8 GB with up to 4 queries on fp32 rows, 2 on bf16 rows) and
+ * within the 1e-5 relative score tolerance where b2_index_search uses the tensor-core scan instead. */
 B2_API int b2_index_search_static(b2_index* h, int64_t nq, const float* q_dev, int k, float* D_dev, int64_t* I_dev,
                            void* stream);
 

@@ -378,9 +378,14 @@ int launch_scan_tc(const CUtensorMap& tmRows, const CUtensorMap& tmQ, const Scan
 bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t nq) {
     if (getenv("B2_NO_TENSOR") != nullptr || getenv("B2_NO_SCAN_TC") != nullptr) return false;
     const int elem = dtype == B2_DTYPE_BF16 ? 2 : 4;
-    // measured at 10M x 1024 on B200: fp32 rows, FFMA scan 5.9-6.0 ms up to 4 queries and 7.2 ms at 5..8, this kernel
-    // 6.7-7.3 ms for 3..16; bf16 rows, this kernel 3.1-3.6 ms for 3..16 (the FFMA scan needs 3.3 ms for ONE query)
+    // Measured at 10M x 1024 on B200 (kernel time, one pass): fp32 rows, FFMA scan 5.7-5.9 ms at 1 query, 6.1 ms at 4,
+    // 7.2 ms at 5..8; this kernel 5.5 ms at 1, 5.7 ms at 2..4, 6.0 ms at 16, 6.8 ms at 32.  bf16 rows: FFMA scan
+    // 2.9-3.3 ms at 1..2 queries; this kernel 2.76 ms at 1, 2.83 ms at 2, 3.2 ms at 16.  So on a large index every
+    // inner-product batch up to the tile size takes this kernel; on a small one (1M x 1024: 0.61 vs 0.62 ms at one
+    // query) the FFMA scan's two launches win until the FP32 pipe falls behind (5 queries fp32, 3 bf16).
+    // (fp32 rows with k > 64 run the all-exact variant, 7.3 ms: the small thresholds stay)
     int min_nq = (dtype == B2_DTYPE_BF16) ? 3 : 5;
+    if ((double)n * d * elem >= 8e9 && (dtype == B2_DTYPE_BF16 || k <= 64)) min_nq = 1;
     if (const char* e = getenv("B2_SCAN_TC_MIN_NQ")) min_nq = atoi(e);
     // up to 32 queries ride along in one pass when k is small (gemm path at 20..128 queries: 10-11.6 ms fp32,
     // 5.9-6.7 ms bf16 at 10M x 1024, against the 5.8 / 3.1 ms it takes to stream the rows once)
