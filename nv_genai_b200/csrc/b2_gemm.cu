@@ -117,37 +117,33 @@ __device__ __forceinline__ float select32(const float (&v)[32], int c) {
     return (c & 1) ? f1 : f0;
 }
 
-// ------------------------------------------------------------------ per-query running top-k
-// Every epilogue warp owns 32 queries.  For each query, shared memory holds the k best KEYS seen so far,
-// sorted best-first (unfilled slots = -inf); slot k-1 is the exact running k-th best, i.e. the admission
-// threshold.  A survivor is inserted by the whole warp at once: lane l holds slots l, l+32, ..., the insertion
-// point is a ballot count, and every slot behind it takes its left neighbour's value (shuffle) - about a
-// hundred cycles per insertion with no dependent chain of shared-memory loads.  The (key, row) pair itself is
-// appended to the query's candidate log in global memory (arrival order = row order).
-__device__ __forceinline__ float coop_insert(float* __restrict__ A, int k, float x, int lane) {
-    constexpr float kNegInf = -__builtin_huge_valf();
-    float v[kGemmMaxK / 32];
-    int p = 0;
-#pragma unroll
-    for (int i = 0; i < kGemmMaxK / 32; ++i) {
-        const int idx = lane + 32 * i;
-        v[i] = (idx < k) ? A[idx] : kNegInf;
-        p += __popc(__ballot_sync(kFull, v[i] >= x));
-    }
-    float last = x;
-#pragma unroll
-    for (int i = 0; i < kGemmMaxK / 32; ++i) {
-        const int idx = lane + 32 * i;
-        float left = __shfl_up_sync(kFull, v[i], 1);
-        const float carry = __shfl_sync(kFull, v[i > 0 ? i - 1 : 0], 31);
-        if (lane == 0) left = carry;
-        const float nv = (idx < p) ? v[i] : (idx == p ? x : left);
-        if (idx >= p && idx < k) A[idx] = nv;
-        if (i == ((k - 1) >> 5)) last = nv;
-    }
-    last = __shfl_sync(kFull, last, (k - 1) & 31);
+// The running k best keys of a query as an UNSORTED list plus the position of its minimum (kept in registers of the
+// query's lane): the new key overwrites the minimum, then the warp finds the new minimum with one 32-bit redux on the
+// order-preserving integer image of the keys.  About a third of the latency of a sorted insertion (ballots to find the
+// position, shuffles to shift), and the k-th best (= the minimum once the list is full; -inf before) is all the
+// epilogue needs from the list.  Survivors are also appended to the query's candidate log in global memory.
+__device__ __forceinline__ void coop_replace_min(float* __restrict__ A, int k, float x, int wpos, int lane, float& new_min,
+                                                 int& new_pos) {
+    if (lane == 0) A[wpos] = x;
     __syncwarp();
-    return last;  // the new k-th best key of this query
+    uint32_t mn = 0xffffffffu;
+    int mp = 0;
+#pragma unroll
+    for (int i = 0; i < kGemmMaxK / 32; ++i) {
+        const int idx = lane + 32 * i;
+        if (idx < k) {
+            const uint32_t u = f2ord(A[idx]);
+            if (u < mn) {
+                mn = u;
+                mp = idx;
+            }
+        }
+    }
+    const uint32_t umin = __reduce_min_sync(kFull, mn);
+    const int who = __ffs(__ballot_sync(kFull, mn == umin)) - 1;
+    new_pos = __shfl_sync(kFull, mp, who);
+    new_min = ord2f(umin);
+    __syncwarp();
 }
 
 // Keep exactly the current top-k of this thread's log, in arrival order: keys above tau, plus the earliest
@@ -546,7 +542,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         constexpr float kNegInf = -__builtin_huge_valf();
         const int ql = tid;  // 0..127
         const int k = p.k;
-        float* keys_w = heap_s + (size_t)(warp * 32) * k;  // this warp's 32 sorted key lists, k slots each
+        float* keys_w = heap_s + (size_t)(warp * 32) * k;  // this warp's 32 key lists (unsorted, minimum tracked), k slots each
         uint64_t* log = p.cand + (size_t)blockIdx.x * kCandCap * kEpiThreads + ql;
         const bool l2 = p.metric == B2_METRIC_L2;
         uint32_t tc = 0;
@@ -570,6 +566,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             bool overflow = false;
             int cnt = 0;
             for (int i = lane; i < 32 * k; i += 32) keys_w[i] = kNegInf;
+            float kth_own = kNegInf;  // minimum of this lane's list = its k-th best key once the list is full
+            int wpos = 0;             // where that minimum sits
             __syncwarp();
             for (int t = t0; t < t1; ++t, ++tc) {
                 const uint32_t buf = tc % NBUF, par = (tc / NBUF) & 1u;
@@ -578,7 +576,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 // this list's k-th, pick up the best one published so far.  Without it every segment re-learns its
                 // threshold from -inf (measured at k = 100: 300 insertions per (query, segment) where ~100 suffice).
                 if (((t - t0) & 31) == 31 && active) {
-                    const float kth_now = keys_w[(size_t)lane * k + (k - 1)];
+                    const float kth_now = kth_own;
                     if (kth_now > kNegInf) atomicMax(p.tau + q, f2ord(refine ? kth_now - band : kth_now) - 1u);
                     thr0 = fmaxf(thr0, ord2f(__ldcg(p.tau + q)));
                     thr = fmaxf(thr, thr0);
@@ -602,7 +600,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             atomicOr(p.flags + item % p.n_qt, 1u);
                         }
                     } else {
-                        compact_log(log, cnt, keys_w[(size_t)lane * k + (k - 1)], k, cnt > k);
+                        compact_log(log, cnt, kth_own, k, cnt > k);
                     }
                 }
                 const long long c2 = p.stats ? clock64() : 0;
@@ -611,20 +609,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 tcgen05_fence_after();
                 const int limit = (int)min((uint32_t)kTileN, p.n - row0);
                 const uint32_t taddr0 = tmem_base + buf * kTileN + ((uint32_t)(warp * 32) << 16);
-#pragma unroll 1
-                for (int ch = 0; ch < kTileN / 32; ++ch) {
-                    uint32_t raw32[32];
-                    tmem_ld32(taddr0 + ch * 32, raw32);
-                    if (KIND == 1) {
-                        uint32_t cor32[32];
-                        tmem_ld32(taddr0 + kTileN + ch * 32, cor32);
-                        tmem_ld_wait();
-#pragma unroll
-                        for (int c = 0; c < 32; ++c)
-                            raw32[c] = __float_as_uint(__uint_as_float(raw32[c]) + __uint_as_float(cor32[c]));
-                    } else {
-                        tmem_ld_wait();
-                    }
+                // one 32-column chunk of the tile: raw32 = this thread's 32 accumulator values (already loaded)
+                auto process_chunk = [&](int ch, uint32_t (&raw32)[32]) {
                     float key[32];
                     if (l2) {
                         const float4* n4 = reinterpret_cast<const float4*>(nrm_s + (tc & 1u) * kTileN + ch * 32);
@@ -649,7 +635,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             m8[c] = fmaxf(fmaxf(key[c], key[c + 8]), fmaxf(key[c + 16], key[c + 24]));
                         const float mx = fmaxf(fmaxf(fmaxf(m8[0], m8[1]), fmaxf(m8[2], m8[3])),
                                                fmaxf(fmaxf(m8[4], m8[5]), fmaxf(m8[6], m8[7])));
-                        if (!__any_sync(kFull, mx > thr_log)) continue;  // thr_log <= thr always
+                        if (!__any_sync(kFull, mx > thr_log)) return;  // thr_log <= thr always
                     }
                     uint32_t m = 0;
                     const int left = limit - ch * 32;
@@ -685,8 +671,12 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         const float xs = __shfl_sync(kFull, kv, src);
                         const float ts = __shfl_sync(kFull, thr, src);
                         if (xs > ts) {  // the threshold may have risen since the mask was built
-                            const float kth = coop_insert(keys_w + (size_t)src * k, k, xs, lane);
+                            float kth;
+                            int npos;
+                            coop_replace_min(keys_w + (size_t)src * k, k, xs, __shfl_sync(kFull, wpos, src), lane, kth, npos);
                             if (lane == src) {
+                                kth_own = kth;
+                                wpos = npos;
                                 ++n_ins;
                                 if (!refine) {
                                     log[(size_t)cnt * kEpiThreads] = pack_cand(kv, row0 + ch * 32 + c);
@@ -699,6 +689,35 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         if (lane == src) m &= m - 1u;
                         pending = __ballot_sync(kFull, m != 0u);
                     }
+                };
+                if (KIND == 1) {
+                    // exact fp32 arithmetic: main + correction accumulators, loaded chunk by chunk
+#pragma unroll 1
+                    for (int ch = 0; ch < kTileN / 32; ++ch) {
+                        uint32_t raw32[32], cor32[32];
+                        tmem_ld32(taddr0 + ch * 32, raw32);
+                        tmem_ld32(taddr0 + kTileN + ch * 32, cor32);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int c = 0; c < 32; ++c)
+                            raw32[c] = __float_as_uint(__uint_as_float(raw32[c]) + __uint_as_float(cor32[c]));
+                        process_chunk(ch, raw32);
+                    }
+                } else {
+                    // software pipeline over the chunks: the TMEM load of chunk ch + 1 is in flight while chunk ch is
+                    // examined (the load latency was most of a chunk's cost: one epilogue warp per scheduler, nothing
+                    // else to issue)
+                    uint32_t ra[32], rb[32];
+                    tmem_ld32(taddr0, ra);
+#pragma unroll 1
+                    for (int ch = 0; ch < kTileN / 32; ch += 2) {
+                        tmem_ld_wait_regs(ra);
+                        tmem_ld32(taddr0 + (ch + 1) * 32, rb);
+                        process_chunk(ch, ra);
+                        tmem_ld_wait_regs(rb);
+                        if (ch + 2 < kTileN / 32) tmem_ld32(taddr0 + (ch + 2) * 32, ra);
+                        process_chunk(ch + 1, rb);
+                    }
                 }
                 tcgen05_fence_before();
                 __syncwarp();
@@ -708,7 +727,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
             }
             // ---- item done: emit this query's k best of the segment, publish the bound
-            const float tau = keys_w[(size_t)lane * k + (k - 1)];
+            const float tau = kth_own;
             const bool full = active && tau > kNegInf;
             const int L = p.list_len;
             if (refine) {
