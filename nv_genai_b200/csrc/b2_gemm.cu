@@ -857,7 +857,10 @@ __global__ void band_kernel(const float* __restrict__ q, int nq, int d, int nq_p
         if (KIND != 0) err += qn * xn * 0.0009765625f;               // the row operand is truncated to tf32: 2^-10
         err += (float)steps * 4.76837158e-7f * qn * xn;              // accumulation: steps x 2^-21
         float b = 2.f * err * 1.001f + 1e-30f;
-        if (l2) b *= 2.f;
+        // L2 keys are 2 q.x - |x|^2: twice the product error, plus the rounding of the stored squared norm and of the
+        // fp32 distance the candidates are finally ranked by (sums of d squares: relative error below d * 2^-24 of
+        // at most (|q| + |x|)^2)
+        if (l2) b = 2.f * b + 2.f * (xn + qn) * (xn + qn) * (float)d * 5.9604645e-8f;
         band[row] = b;
     }
 }

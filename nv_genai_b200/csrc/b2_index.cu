@@ -558,9 +558,10 @@ static int search_device(b2_index* h, int64_t nq, const float* q_dev, int k, flo
         B2_AFTER_LAUNCH();
         return B2_OK;
     }
-    if (scan_tc_supported(h->ntotal, h->d, h->dtype, h->metric, k, nq))
+    const bool tc_approx = h->gemm_query_parts == 0 && h->max_norm_ord != nullptr;
+    if (scan_tc_supported(h->ntotal, h->d, h->dtype, h->metric, k, nq, tc_approx))
         return scan_tc_search(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, q_dev, (int)nq, k, h->num_sms,
-                              D_dev, I_dev, stream, push, h->gemm_query_parts == 0 ? h->max_norm_ord : nullptr);
+                              D_dev, I_dev, stream, push, tc_approx ? h->max_norm_ord : nullptr, h->metric, h->norms);
     if (gemm_path_supported(h->ntotal, h->d, h->dtype, k, nq)) {
         ApproxRows approx;
         const bool shadowed = gemm_uses_refine(h->gemm_query_parts, h->max_norm_ord) && ensure_shadow(h, stream, &approx);

@@ -10,7 +10,8 @@ namespace b2 {
 // b2_scan.cu ---------------------------------------------------------------
 size_t scan_smem_bytes(int nq_tile, int nchunks, bool bf16, int kpad);
 int scan_pass(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* q_dev,
-              int nq_valid, int nq_tile, int k, int num_sms, cudaStream_t stream, uint64_t** partial, int* grid);
+              int nq_valid, int nq_tile, int k, int num_sms, cudaStream_t stream, uint64_t** partial, int* grid,
+              const uint32_t* run_if = nullptr);
 
 void prof_enable(int on);
 void* prof_begin(cudaStream_t stream);                       // nullptr when profiling is off
@@ -55,7 +56,7 @@ int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metri
 int merge_rescore(const uint64_t* partial, int nq, int nlists, int list_len, int k, int metric, float* D, int64_t* I,
                   size_t out_stride, cudaStream_t stream, const float* qnorm, const float* q_dev, int d, const void* rows,
                   size_t pitch_bytes, int dtype, const float* norms, const float* band, const PeerPush* push = nullptr,
-                  uint32_t* overflow = nullptr);
+                  uint32_t* overflow = nullptr, bool l2_direct = false);
 // overflow (optional, device, [nq + 1], zeroed by the caller): the lists are sorted best-first and may have dropped
 // candidates beyond list_len; a query whose cut reaches into a full list's last entry gets overflow[q] = 1 (and
 // overflow[nq] = 1) and NO output: the caller redoes it exactly.  Needs nlists * list_len <= 12288.
@@ -129,11 +130,13 @@ int mmr_select(const float* q, int d, int nq, const float* cand_rows /*[nq][fetc
 
 // b2_scan_tc.cu ------------------------------------------------------------
 // Tensor-core scan for 3..16 queries (inner product): the corpus is the M operand, HBM-bound.
-bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t nq);
-// max_norm_ord (optional): enables the approximate (filter-and-refine) mode on fp32 rows.
+// approx: the filter-and-refine mode is available (fp32 rows; needed for L2).
+bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t nq, bool approx = true);
+// max_norm_ord (optional): enables the approximate (filter-and-refine) mode on fp32 rows.  metric L2 (fp32 rows,
+// approximate mode only) takes the rows' squared norms.
 int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, const float* q_dev, int nq, int k,
                    int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push = nullptr,
-                   const uint32_t* max_norm_ord = nullptr);
+                   const uint32_t* max_norm_ord = nullptr, int metric = B2_METRIC_IP, const float* norms = nullptr);
 
 // b2_synth.cu --------------------------------------------------------------
 int synth_fill(float* out, int64_t row0, int64_t nrows, int d, uint64_t seed, cudaStream_t stream);

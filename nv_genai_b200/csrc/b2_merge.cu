@@ -208,7 +208,27 @@ struct RescoreCtx {
     size_t pitch_bytes;
     int d;
     int bf16;
+    int l2_direct;  // re-score with sum (x - q)^2, faiss's form below 20 queries (exactly 0 for a stored copy of the query)
 };
+
+// sum (x - q)^2 over the row in the FFMA scan's order (fp32 rows)
+__device__ __forceinline__ float warp_exact_l2(const RescoreCtx& c, const float* __restrict__ qrow, uint32_t row, int lane) {
+    const char* r = c.rows + (size_t)row * c.pitch_bytes;
+    float acc = 0.f;
+    for (int e0 = lane * 4; e0 < c.d; e0 += 128) {
+        const float4 w = *reinterpret_cast<const float4*>(r + (size_t)e0 * 4);
+        const float x[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+            if (e0 + e < c.d) {
+                const float t = x[e] - __ldg(qrow + e0 + e);
+                acc = fmaf(t, t, acc);
+            }
+    }
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) acc += __shfl_xor_sync(kFull, acc, s);
+    return acc;
+}
 
 __device__ __forceinline__ float warp_exact_dot(const RescoreCtx& c, const float* __restrict__ qrow, uint32_t row, int lane) {
     const char* r = c.rows + (size_t)row * c.pitch_bytes;
@@ -372,9 +392,9 @@ __global__ void __launch_bounds__(kMergeThreads) merge_rescore_select_kernel(con
         const bool more = left_s != 0;
         for (int j = warp; j < n; j += kMergeThreads / 32) {
             const uint32_t row = cand_pos(buf[kpad + j]);
-            const float s = warp_exact_dot(ctx, qrow, row, lane);
+            const float s = ctx.l2_direct ? warp_exact_l2(ctx, qrow, row, lane) : warp_exact_dot(ctx, qrow, row, lane);
             if (lane == 0) {
-                const float key = (metric == B2_METRIC_IP) ? (s + 0.0f) : fmaf(2.f, s, -ctx.norms[row]);
+                const float key = ctx.l2_direct ? -s : ((metric == B2_METRIC_IP) ? (s + 0.0f) : fmaf(2.f, s, -ctx.norms[row]));
                 buf[kpad + j] = (key > -FLT_MAX) ? pack_cand(key, row) : B2_SENTINEL;  // NaN / -FLT_MAX never enter
             }
         }
@@ -392,7 +412,7 @@ __global__ void __launch_bounds__(kMergeThreads) merge_rescore_select_kernel(con
 int merge_rescore(const uint64_t* partial, int nq, int nlists, int list_len, int k, int metric, float* D, int64_t* I,
                   size_t out_stride, cudaStream_t stream, const float* qnorm, const float* q_dev, int d, const void* rows,
                   size_t pitch_bytes, int dtype, const float* norms, const float* band, const PeerPush* push_in,
-                  uint32_t* overflow) {
+                  uint32_t* overflow, bool l2_direct) {
     const int kpad = next_pow2(k < 32 ? 32 : k);
     const int total = nlists * list_len;
     PeerPush push;
@@ -415,6 +435,7 @@ int merge_rescore(const uint64_t* partial, int nq, int nlists, int list_len, int
     ctx.pitch_bytes = pitch_bytes;
     ctx.d = d;
     ctx.bf16 = dtype == B2_DTYPE_BF16;
+    ctx.l2_direct = l2_direct ? 1 : 0;
     int sort_n = 2 * kpad;
     const int want = next_pow2(total + kpad);
     while (sort_n < want && sort_n < 4096) sort_n <<= 1;
@@ -428,8 +449,8 @@ int merge_rescore(const uint64_t* partial, int nq, int nlists, int list_len, int
         B2_AFTER_LAUNCH();
         return B2_OK;
     }
-    if (overflow != nullptr) {
-        set_error("merge_rescore: %d candidates per query are too many for the overflow check", total);
+    if (overflow != nullptr || l2_direct) {
+        set_error("merge_rescore: %d candidates per query are too many for the register-resident merge", total);
         return B2_ERR_UNSUPPORTED;
     }
     merge_rescore_kernel<<<nq, kMergeThreads, smem, stream>>>(partial, total, k, kpad, sort_n, metric, D, I, out_stride,

@@ -93,6 +93,7 @@ struct ScanParams {
     int nq_valid;          // <= NQ
     int k, kpad;
     uint64_t* partial;     // [NQ][gridDim.x][k] sorted best-first
+    const uint32_t* run_if;  // not null: the launch does nothing unless *run_if != 0 (fix-up pass of the tensor-core scan)
 };
 
 // Transposing butterfly: V per-lane partial sums -> max(V/32,1) complete sums per lane.
@@ -127,6 +128,7 @@ __device__ __forceinline__ int warp_transpose_reduce(float (&v)[V], int lane) {
 template <int METRIC, bool BF16, int NQ, int R>
 __global__ void __launch_bounds__(kScanThreads) scan_topk_kernel(const ScanParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    if (p.run_if != nullptr && *p.run_if == 0u) return;
     constexpr int CH = BF16 ? 256 : 128;  // elements per 512-byte chunk
     constexpr int V = R * NQ;
     constexpr int VL = (V >= 32) ? V / 32 : 1;
@@ -380,8 +382,10 @@ static int dispatch_nq(int nq_tile, const ScanParams& p, int num_sms, cudaStream
 // One pass over the rows for a tile of <= 16 queries.  Leaves [nq_tile][grid][k] sorted
 // partial lists in *partial (stream-ordered allocation; the caller frees it with cudaFreeAsync).
 int scan_pass(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* q_dev,
-              int nq_valid, int nq_tile, int k, int num_sms, cudaStream_t stream, uint64_t** partial, int* grid) {
+              int nq_valid, int nq_tile, int k, int num_sms, cudaStream_t stream, uint64_t** partial, int* grid,
+              const uint32_t* run_if) {
     ScanParams p;
+    p.run_if = run_if;
     p.rows = static_cast<const char*>(rows);
     p.n = (uint32_t)n;
     p.pitch_bytes = (uint32_t)pitch_bytes;
@@ -515,6 +519,7 @@ extern "C" int b2_index_search_static(b2_index* h, int64_t nq, const float* q_de
         p.k = k;
         p.kpad = next_pow2(k < 32 ? 32 : k);
         p.partial = nullptr;
+        p.run_if = nullptr;
         const bool bf16 = v.dtype == B2_DTYPE_BF16;
         const int tile = next_pow2((int)nq);
         uint64_t* scratch = nullptr;

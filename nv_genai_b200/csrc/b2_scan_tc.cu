@@ -59,6 +59,7 @@ struct ScanTcParams {
     int klist;                // entries each (warp, query) list keeps and each CTA emits: k, or kpad in the approximate mode
     uint64_t* partial;        // [nq][gridDim.x][klist] sorted best-first
     const uint32_t* run_if;   // not null: the whole launch is skipped unless *run_if != 0 (fix-up launch of the approximate mode)
+    const float* norms;       // not null (approximate mode only): L2, keys are 2 q.x - |x|^2
 };
 
 __device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
@@ -276,6 +277,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
             tcgen05_fence_after();
             const uint32_t taddr = tmem_base + buf * kBufCols + ((uint32_t)(warp * 32) << 16);
             const uint32_t row = (uint32_t)tile * kTileRows + warp * 32 + lane;
+            const float nrm = (APX && p.norms != nullptr && row < p.n) ? __ldg(p.norms + row) : 0.f;
             // queries in groups of 16: columns [g*16, +16) of the q_hi block, of the q_lo block and of D2
 #pragma unroll 1
             for (int g = 0; g < NQ / 16; ++g) {
@@ -305,7 +307,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
                 for (int jj = 0; jj < 16; ++jj) {
                     const int j = g * 16 + jj;
                     if (j < p.nq) {  // warp-uniform
-                        const float key = (big[jj] + small[jj]) + 0.0f;
+                        const float key = (APX && p.norms != nullptr) ? fmaf(2.f, big[jj], -nrm) : (big[jj] + small[jj]) + 0.0f;
                         const uint64_t cand = pack_cand(key, row);
                         const int li = j * kEpiWarps + warp;
                         const bool pass = row < p.n && key > -FLT_MAX && cand > worst_s[li];
@@ -375,9 +377,14 @@ int launch_scan_tc(const CUtensorMap& tmRows, const CUtensorMap& tmQ, const Scan
 
 }  // namespace
 
-bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t nq) {
+bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t nq, bool approx) {
     if (getenv("B2_NO_TENSOR") != nullptr || getenv("B2_NO_SCAN_TC") != nullptr) return false;
     const int elem = dtype == B2_DTYPE_BF16 ? 2 : 4;
+    // L2 rides the approximate mode only (fp32 rows, k <= 64): keys 2 q.x - |x|^2 for the filter, the direct form
+    // sum (x - q)^2 -- faiss's arithmetic below 20 queries -- for the candidates that are re-scored
+    static const bool exact_only = getenv("B2_SCAN_TC_EXACT") != nullptr;
+    // (from 20 queries on, L2 takes the GEMM kernel and the |q|^2 + |x|^2 - 2 q.x form, as faiss does)
+    if (metric == B2_METRIC_L2 && (dtype != B2_DTYPE_F32 || k > 64 || !approx || exact_only || nq >= 20)) return false;
     // Measured at 10M x 1024 on B200 (kernel time, one pass): fp32 rows, FFMA scan 5.7-5.9 ms at 1 query, 6.1 ms at 4,
     // 7.2 ms at 5..8; this kernel 5.5 ms at 1, 5.7 ms at 2..4, 6.0 ms at 16, 6.8 ms at 32.  bf16 rows: FFMA scan
     // 2.9-3.3 ms at 1..2 queries; this kernel 2.76 ms at 1, 2.83 ms at 2, 3.2 ms at 16.  So on a large index every
@@ -389,8 +396,8 @@ bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t n
     if (const char* e = getenv("B2_SCAN_TC_MIN_NQ")) min_nq = atoi(e);
     // up to 32 queries ride along in one pass when k is small (gemm path at 20..128 queries: 10-11.6 ms fp32,
     // 5.9-6.7 ms bf16 at 10M x 1024, against the 5.8 / 3.1 ms it takes to stream the rows once)
-    return metric == B2_METRIC_IP && nq >= min_nq && nq <= scan_tc_max_queries(k) && n >= 4096 &&
-           n < ((int64_t)1 << 31) && (int64_t)d * elem >= kSlice;
+    return nq >= min_nq && nq <= scan_tc_max_queries(k) && n >= 4096 && n < ((int64_t)1 << 31) &&
+           (int64_t)d * elem >= kSlice;
 }
 
 // K slices per pipeline stage (see the producer loop) and the number of stages that fit next to the lists.  Measured at
@@ -418,7 +425,12 @@ static void pick_pipeline(int kslices, bool sps_allowed, int nqt, int kpad, int 
 // the error band of the k-th best).
 static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes, int d, const float* q_dev, int nq, int k,
                                  int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push,
-                                 const uint32_t* max_norm_ord) {
+                                 const uint32_t* max_norm_ord, int metric, const float* norms) {
+    const bool l2 = metric == B2_METRIC_L2;
+    if (l2 && norms == nullptr) {
+        set_error("tensor-core scan: L2 needs the rows' squared norms");
+        return B2_ERR_INVALID;
+    }
     const size_t kbytes = (((size_t)d * 4 + kSlice - 1) / kSlice) * kSlice;
     const int kp = (int)(kbytes / 4);
     ScanTcParams p;
@@ -433,6 +445,7 @@ static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes
     p.kslices = (int)(kbytes / kSlice);
     p.n_tiles = (int)((n + kTileRows - 1) / kTileRows);
     p.run_if = nullptr;
+    p.norms = l2 ? norms : nullptr;
     const int nqt = nq <= 16 ? 16 : 32;
     int stages = 0, stages_x = 0, sps_x = 1;
     pick_pipeline(p.kslices, true, nqt, p.kpad, 1, &p.sps, &stages);
@@ -468,14 +481,36 @@ static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes
         rc = B2_ERR_CUDA;
     }
     if (rc == B2_OK) rc = prep_queries(q_dev, nq, d, nqt, kp, 1, false, Q, nullptr, nullptr, stream);
-    if (rc == B2_OK) rc = compute_band(q_dev, nq, d, nqt, kp / 8, false, false, max_norm_ord, nullptr, band, stream);
+    if (rc == B2_OK) rc = compute_band(q_dev, nq, d, nqt, kp / 8, false, l2, max_norm_ord, nullptr, band, stream);
     if (rc == B2_OK)
         rc = nqt == 16 ? launch_scan_tc<1, 16, true>(tmRows, tmQ, p, grid, smem, stream)
                        : launch_scan_tc<1, 32, true>(tmRows, tmQ, p, grid, smem, stream);
     if (rc == B2_OK)
-        rc = merge_rescore(p.partial, nq, grid, p.klist, k, B2_METRIC_IP, D, I, (size_t)k, stream, nullptr, q_dev, d, rows,
-                           pitch_bytes, B2_DTYPE_F32, nullptr, band, push, flags);
+        rc = merge_rescore(p.partial, nq, grid, p.klist, k, metric, D, I, (size_t)k, stream, nullptr, q_dev, d, rows,
+                           pitch_bytes, B2_DTYPE_F32, norms, band, push, flags, l2);
     // ---- exact fix-up for the flagged queries (each kernel returns immediately when there is none)
+    if (rc == B2_OK && l2) {
+        // L2: the FFMA scan (direct form), a pass per 16 queries
+        for (int off = 0; off < nq && rc == B2_OK; off += 16) {
+            const int valid = std::min(16, nq - off);
+            uint64_t* part = nullptr;
+            int g2 = 0;
+            rc = scan_pass(rows, n, pitch_bytes, d, B2_DTYPE_F32, B2_METRIC_L2, q_dev + (size_t)off * d, valid,
+                           next_pow2(valid), k, num_sms, stream, &part, &g2, flags + nq);
+            if (rc != B2_OK) break;
+            PeerPush pp;
+            if (push != nullptr) {
+                pp = *push;
+                pp.q_offset += off;
+            }
+            rc = merge_partials(part, valid, g2, k, B2_METRIC_L2, 0, D ? D + (size_t)off * k : nullptr,
+                                I ? I + (size_t)off * k : nullptr, (size_t)k, stream, nullptr, push != nullptr ? &pp : nullptr,
+                                flags + off);
+            cudaFreeAsync(part, stream);
+        }
+        cudaFreeAsync(blk, stream);
+        return rc;
+    }
     if (rc == B2_OK) rc = prep_queries(q_dev, nq, d, nqt, kp, 2, false, Qx, nullptr, nullptr, stream);
     if (rc == B2_OK) {
         ScanTcParams px = p;
@@ -483,6 +518,7 @@ static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes
         px.sps = 1;
         px.num_stages = stages_x;
         px.run_if = flags + nq;
+        px.norms = nullptr;
         rc = nqt == 16 ? launch_scan_tc<1, 16>(tmRows, tmQx, px, grid, smem_x, stream)
                        : launch_scan_tc<1, 32>(tmRows, tmQx, px, grid, smem_x, stream);
     }
@@ -494,13 +530,18 @@ static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes
 
 int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, const float* q_dev, int nq, int k,
                    int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push,
-                   const uint32_t* max_norm_ord) {
+                   const uint32_t* max_norm_ord, int metric, const float* norms) {
     const bool bf16 = dtype == B2_DTYPE_BF16;
     const int elem = bf16 ? 2 : 4;
     static const bool no_approx = getenv("B2_SCAN_TC_EXACT") != nullptr;
     if (!bf16 && max_norm_ord != nullptr && !no_approx && k <= 64 &&
         (long long)std::min<long long>(num_sms, (n + kTileRows - 1) / kTileRows) * next_pow2(k < 32 ? 32 : k) <= 12288)
-        return scan_tc_search_approx(rows, n, pitch_bytes, d, q_dev, nq, k, num_sms, D, I, stream, push, max_norm_ord);
+        return scan_tc_search_approx(rows, n, pitch_bytes, d, q_dev, nq, k, num_sms, D, I, stream, push, max_norm_ord,
+                                     metric, norms);
+    if (metric != B2_METRIC_IP) {
+        set_error("tensor-core scan: L2 needs the approximate mode (fp32 rows, k <= 64)");
+        return B2_ERR_UNSUPPORTED;
+    }
     const size_t kbytes = (((size_t)d * elem + kSlice - 1) / kSlice) * kSlice;
     const int kp = (int)(kbytes / elem);
 
@@ -510,6 +551,7 @@ int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int d
     p.k = k;
     p.klist = k;
     p.run_if = nullptr;
+    p.norms = nullptr;
     p.kpad = next_pow2(k < 32 ? 32 : k);
     p.kslices = (int)(kbytes / kSlice);
     p.n_tiles = (int)((n + kTileRows - 1) / kTileRows);

@@ -9,9 +9,9 @@ inside the library image instead of taking them from cudaMallocAsync.
 This file checks, through the C ABI only, that the entry point returns what b2_index_search
 returns, on two calls in a row — the second call reuses the array with the first call's
 contents still in it — and that it refuses sizes beyond its fixed scratch with a clear error.
-The entry point always runs the FFMA scan kernel; b2_index_search runs the same kernel for L2
-and for very small batches (then the comparison is bit for bit) and the tensor-core scan for
-5..16 inner-product queries (3..16 on bf16 rows), where the two agree within the 1e-5 relative
+The entry point always runs the FFMA scan kernel; b2_index_search runs the same kernel for
+very small batches on a small index (then the comparison is bit for bit) and the tensor-core
+scan for 5..16 queries (3..16 on bf16 rows), where the two agree within the 1e-5 relative
 score tolerance every parity test here uses (tests/parity.py).  It is named test_zz_* so
 that pytest collects it after every other test file.
 """
@@ -70,7 +70,9 @@ def test_static_scratch_search_equals_the_allocating_search_twice_in_a_row(metri
         for nq, k, first in ((16, 10, 0), (3, 100, 5)):
             qs = q[first:first + nq].contiguous()
             D0, I0, D1, I1 = _search_pair(N, h, qs, k, None)
-            same_kernel = metric_name == "l2" or nq < (5 if dtype_name == "f32" else 3)
+            # below 5 queries on fp32 rows (3 on bf16 rows) b2_index_search runs the FFMA scan as well; from there on the
+            # tensor-core scan (fp32 rows: L2 too, re-scored with the FFMA scan's direct form)
+            same_kernel = nq < (5 if dtype_name == "f32" else 3)
             if same_kernel:
                 assert np.array_equal(I0, I1) and np.array_equal(D0, D1), (nq, k)  # bit for bit
             else:
