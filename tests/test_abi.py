@@ -58,6 +58,13 @@ def test_argument_validation_happens_before_any_device_work():
     assert N.lib.b2_index_create(8, N.METRIC_L2, 9, 0, ctypes.byref(h)) == N.B2_ERR_INVALID
     assert N.lib.b2_index_search(None, 1, None, 0, 1, None, None, 0, None) == N.B2_ERR_INVALID
     assert N.lib.b2_index_ntotal(None) == -1
+    # the post-search selection entry points check their arguments first as well
+    assert N.lib.b2_index_search_filtered(None, 1, None, 0, 1, 1, None, 0, 0, 0, 0.0, 0, 0.0, None, None, None, 0,
+                                          None) == N.B2_ERR_INVALID
+    assert N.lib.b2_filter_results(0, 1, 3, 4, None, None, None, 0, 0, 0.0, 0, 0.0, None, None, None, 0, None) \
+        == N.B2_ERR_INVALID and b"fetch_k must be >= k" in N.lib.b2_last_error()
+    assert N.lib.b2_filter_results(0, 1, 4, 4, None, None, None, 0, 0, 0.0, 7, 0.0, None, None, None, 0, None) \
+        == N.B2_ERR_INVALID and b"relevance function" in N.lib.b2_last_error()
     assert N.lib.b2_index_destroy(None) == N.B2_OK
 
 
