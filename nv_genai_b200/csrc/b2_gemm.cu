@@ -627,39 +627,46 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         for (int c = 0; c < 32; ++c) key[c] = __uint_as_float(raw32[c]) + 0.0f;
                     }
                     // Fast reject: most chunks hold no candidate for any of the warp's 32 queries; a max tree (log depth,
-                    // independent operations) answers that without the 64 dependent compare-and-or steps of the masks.
-                    {
-                        float m8[8];
+                    // independent operations) answers that without building any mask.  m8[c] = max over the columns
+                    // c, c + 8, c + 16, c + 24.
+                    float m8[8];
 #pragma unroll
-                        for (int c = 0; c < 8; ++c)
-                            m8[c] = fmaxf(fmaxf(key[c], key[c + 8]), fmaxf(key[c + 16], key[c + 24]));
+                    for (int c = 0; c < 8; ++c)
+                        m8[c] = fmaxf(fmaxf(key[c], key[c + 8]), fmaxf(key[c + 16], key[c + 24]));
+                    {
                         const float mx = fmaxf(fmaxf(fmaxf(m8[0], m8[1]), fmaxf(m8[2], m8[3])),
                                                fmaxf(fmaxf(m8[4], m8[5]), fmaxf(m8[6], m8[7])));
                         if (!__any_sync(kFull, mx > thr_log)) return;  // thr_log <= thr always
                     }
-                    uint32_t m = 0;
+                    // the mask of columns above the log threshold, only for the column classes whose maximum passes
+                    // (a chunk that gets here typically holds one candidate for one or two of the 32 queries)
+                    uint32_t ml = 0;
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) {
+                        if (m8[c] > thr_log) {
+                            ml |= ((key[c] > thr_log) ? (1u << c) : 0u) | ((key[c + 8] > thr_log) ? (1u << (c + 8)) : 0u) |
+                                  ((key[c + 16] > thr_log) ? (1u << (c + 16)) : 0u) |
+                                  ((key[c + 24] > thr_log) ? (1u << (c + 24)) : 0u);
+                        }
+                    }
                     const int left = limit - ch * 32;
                     const uint32_t valid = (left >= 32) ? 0xffffffffu : ((left <= 0) ? 0u : ((1u << left) - 1u));
+                    ml &= valid;
+                    uint32_t m = 0;  // columns above the insertion threshold (a subset of ml)
                     if (refine) {
-                        uint32_t ml = 0;
-#pragma unroll
-                        for (int c = 0; c < 32; ++c) {
-                            ml |= (key[c] > thr_log) ? (1u << c) : 0u;
-                            m |= (key[c] > thr) ? (1u << c) : 0u;
-                        }
-                        ml &= valid;
                         while (ml) {  // lane-local: log every in-band candidate of this chunk, in row order
                             const int c = __ffs(ml) - 1;
                             ml &= ml - 1u;
+                            const float kv = select32(key, c);
+                            if (kv > thr) m |= 1u << c;
                             if (cnt < kCandCap) {
-                                log[(size_t)cnt * kEpiThreads] = pack_cand(select32(key, c), row0 + ch * 32 + c);
+                                log[(size_t)cnt * kEpiThreads] = pack_cand(kv, row0 + ch * 32 + c);
                                 ++cnt;
                                 ++n_log;
                             }
                         }
                     } else {
-#pragma unroll
-                        for (int c = 0; c < 32; ++c) m |= (key[c] > thr) ? (1u << c) : 0u;
+                        m = ml;  // thr_log == thr
                     }
                     m &= valid;
                     // survivors, one (query, column) at a time, each inserted by the whole warp
