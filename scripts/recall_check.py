@@ -1,6 +1,7 @@
 #!/usr/bin/env python
-"""Developer check at full size: recall@k of the bf16 row store (tensor path, 1 and 2 query parts) against the exact
-fp32 scan, and score/id agreement of the fp32 tensor path (3xTF32, rounded vs truncated hi operand) with the scan."""
+"""Developer check at full size: recall@k of the bf16 row store against the exact fp32 scan, and score/id agreement of
+the large-batch tensor path with the FFMA scan of the same rows, in its default mode (filter and refine; fp32 rows with
+and without the bf16 shadow) and with the all-exact tensor arithmetic."""
 import argparse
 import json
 import os
@@ -52,17 +53,24 @@ def main():
 
     Dx, Ix = run(f32, B2_NO_TENSOR="1")
     out = {"rows": a.rows, "nq": a.nq, "k": a.k}
-    for name, idx, env in (("f32_tensor_default", f32, {}), ("f32_tensor_3xtf32", f32, {"B2_GEMM_MIXED": "0"}),
-                           ("bf16_scan", b16, {"B2_NO_TENSOR": "1"}), ("bf16_tensor_2parts", b16, {}),
-                           ("bf16_tensor_1part", b16, {"B2_GEMM_QUERY_PARTS": "1"})):
+    cases = [("f32_refine_bf16_shadow (default)", f32, {}), ("f32_refine_tf32_no_shadow", f32, {"_shadow": "0"}),
+             ("f32_all_exact_tf32_plus_bf16_correction", f32, {"B2_GEMM_REFINE": "0"}),
+             ("bf16_scan", b16, {"B2_NO_TENSOR": "1"}), ("bf16_refine (default)", b16, {}),
+             ("bf16_all_exact_2parts", b16, {"B2_GEMM_REFINE": "0"}), ("bf16_tensor_1part_no_rescoring", b16, {"B2_GEMM_QUERY_PARTS": "1"})]
+    for name, idx, env in cases:
+        env = dict(env)
+        if env.pop("_shadow", None) == "0":
+            idx.set_option("bf16_shadow", 0)
         D, I = run(idx, **env)
         out[name] = {"recall@k": recall(I, Ix, a.k), "recall@10": recall(I, Ix, 10),
                      "ids_equal_frac": float((I == Ix).float().mean()),
                      "max_rel_score_diff": float(((D - Dx).abs() / Dx.abs().clamp_min(1e-9)).max()),
                      "mean_rel_score_diff_signed": float(((D - Dx) / Dx.abs().clamp_min(1e-9)).mean())}
+        if idx is f32:
+            idx.set_option("bf16_shadow", 1)
     Db, Ib = run(b16, B2_NO_TENSOR="1")
     D2, I2 = run(b16)
-    out["bf16_tensor_2parts_vs_bf16_scan"] = {"ids_equal_frac": float((I2 == Ib).float().mean()),
+    out["bf16_refine_vs_bf16_scan"] = {"ids_equal_frac": float((I2 == Ib).float().mean()),
                                               "max_rel_score_diff": float(((D2 - Db).abs() / Db.abs().clamp_min(1e-9)).max())}
     print(json.dumps(out), flush=True)
 
