@@ -93,7 +93,7 @@ struct GemmParams {
     const float* band;  // [nq_pad] refine: 2 x (bound on |approximate key - exact key|), per query
     unsigned long long* stats;  // diagnostics (B2_GEMM_DEBUG): [0] MMA cycles waiting for a free accumulator, [1] for operands,
                         // [2] epilogue warp 0 cycles waiting for a full accumulator, [3] list insertions, [4] log entries,
-                        // [5] log compactions, [6] MMA warp cycles in total; nullptr = off
+                        // [5] log compactions, [6] MMA warp cycles in total, [7] as [0] but only inside a unit's first item; nullptr = off
     uint32_t* flags;    // [n_qt] refine: set when a query of the group had more in-band candidates than fit
     const float* norms; // |x|^2 per stored row
     uint64_t* cand;     // [grid][kCandCap][128]
@@ -141,6 +141,37 @@ __device__ __forceinline__ void coop_replace_min(float* __restrict__ A, int k, f
     }
     const uint32_t umin = __reduce_min_sync(kFull, mn);
     const int who = __ffs(__ballot_sync(kFull, mn == umin)) - 1;
+    new_pos = __shfl_sync(kFull, mp, who);
+    new_min = ord2f(umin);
+    __syncwarp();
+}
+
+// Up to FOUR replacements at once, one per 8-lane group, into the lists of four different queries (src = the query's lane
+// in this warp, -1 = this group has nothing to do; doit = its key still beats the threshold).  While the thresholds of a
+// cold item settle, every lane has candidates in every chunk, and one insertion at a time was what stalled the tensor
+// pipe (70 % of the accumulator wait at k = 100 fell into each unit's first item).
+__device__ __forceinline__ void coop_replace_min4(float* __restrict__ keys_w, int k, int src, float x, int wpos, bool doit,
+                                                  int lane, float& new_min, int& new_pos) {
+    const int sl = lane & 7;
+    const unsigned gmask = 0xffu << (lane & 24);
+    float* A = keys_w + (size_t)(src < 0 ? 0 : src) * k;
+    if (doit && sl == 0) A[wpos] = x;
+    __syncwarp();
+    uint32_t mn = 0xffffffffu;
+    int mp = 0;
+#pragma unroll
+    for (int i = 0; i < kGemmMaxK / 8; ++i) {
+        const int idx = sl + 8 * i;
+        if (idx < k) {
+            const uint32_t u = f2ord(A[idx]);
+            if (u < mn) {
+                mn = u;
+                mp = idx;
+            }
+        }
+    }
+    const uint32_t umin = __reduce_min_sync(gmask, mn);
+    const int who = __ffs(__ballot_sync(kFull, mn == umin) & gmask) - 1;
     new_pos = __shfl_sync(kFull, mp, who);
     new_min = ord2f(umin);
     __syncwarp();
@@ -345,7 +376,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint32_t phase = 0;
         uint32_t tc = 0;
         int cslot = 0;
-        long long w_acc = 0, w_ops = 0;
+        long long w_acc = 0, w_ops = 0, w_acc_first = 0;
         const long long c_begin = p.stats ? clock64() : 0;
         for (int item = unit; cta_rank == 0 && item < p.n_items; item += n_units) {
             if (p.only_flagged && __ldcg(p.flags + item % p.n_qt) == 0u) continue;  // fix-up launch: flagged groups only
@@ -356,7 +387,10 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 const uint32_t buf = tc % NBUF, par = (tc / NBUF) & 1u;
                 const long long c0 = p.stats ? clock64() : 0;
                 mbar_wait(smem_u32(tempty_bar + buf), par ^ 1u);
-                if (p.stats) w_acc += clock64() - c0;
+                if (p.stats) {
+                    w_acc += clock64() - c0;
+                    if (item == unit) w_acc_first += clock64() - c0;
+                }
                 tcgen05_fence_after();
                 const uint32_t d_tmem = tmem_base + buf * kTileN;
                 const uint32_t c_tmem = tmem_base + kTileN;  // fp32 rows: correction accumulator
@@ -424,6 +458,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             atomicAdd(p.stats + 0, (unsigned long long)w_acc);
             atomicAdd(p.stats + 1, (unsigned long long)w_ops);
             atomicAdd(p.stats + 6, (unsigned long long)(clock64() - c_begin));
+            atomicAdd(p.stats + 7, (unsigned long long)w_acc_first);
         }
         // CTA pairs, fp32 rows: the peer's MMA warp has nothing to issue; it forwards "my transform warps are done with
         // this K slice" to the leader with ONE cluster-scope arrival per slice (sixteen cluster-scope arrivals per
@@ -672,6 +707,47 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     // survivors, one (query, column) at a time, each inserted by the whole warp
                     unsigned pending = __ballot_sync(kFull, m != 0u);
                     while (pending) {
+                        if (__popc(pending) >= 2) {
+                            // several queries have a survivor: serve up to four of them at once, one per 8-lane group
+                            unsigned pm = pending;
+#pragma unroll
+                            for (int j = 0; j < 3; ++j)
+                                if (j < (lane >> 3)) pm &= pm - 1u;  // group g takes the (g + 1)-th pending lane
+                            const int src4 = pm ? (__ffs(pm) - 1) : -1;
+                            const int ssafe = src4 < 0 ? 0 : src4;
+                            const int c = m ? (__ffs(m) - 1) : 0;
+                            const float kv = select32(key, c);
+                            const float xs = __shfl_sync(kFull, kv, ssafe);
+                            const float ts = __shfl_sync(kFull, thr, ssafe);
+                            const int wp = __shfl_sync(kFull, wpos, ssafe);
+                            const bool doit = src4 >= 0 && xs > ts;  // the threshold may have risen since the mask was built
+                            float nmin;
+                            int npos;
+                            coop_replace_min4(keys_w, k, src4, xs, wp, doit, lane, nmin, npos);
+                            // back to the owners: pending lane number r (in lane order) was served by group r
+                            const int rank = __popc(pending & ((1u << lane) - 1u));
+                            const bool mine = ((pending >> lane) & 1u) != 0u && rank < 4;
+                            const int gl = (rank & 3) * 8;
+                            const float omin = __shfl_sync(kFull, nmin, gl);
+                            const int opos = __shfl_sync(kFull, npos, gl);
+                            const int odid = __shfl_sync(kFull, doit ? 1 : 0, gl);
+                            if (mine) {
+                                if (odid) {
+                                    kth_own = omin;
+                                    wpos = opos;
+                                    ++n_ins;
+                                    if (!refine) {
+                                        log[(size_t)cnt * kEpiThreads] = pack_cand(kv, row0 + ch * 32 + c);
+                                        ++cnt;
+                                    }
+                                    thr = fmaxf(thr0, omin);
+                                    thr_log = fmaxf(thr0, omin - band);
+                                }
+                                m &= m - 1u;
+                            }
+                            pending = __ballot_sync(kFull, m != 0u);
+                            continue;
+                        }
                         const int src = __ffs(pending) - 1;
                         const int c = m ? (__ffs(m) - 1) : 0;
                         const float kv = select32(key, c);
@@ -1330,9 +1406,9 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
         std::fprintf(stderr,
                      "[b2 gemm refine] per MMA warp: %.1f Mcycles, waiting for a free accumulator %.1f, for operands %.1f; "
                      "epilogue warp 0 waiting for a full accumulator %.1f (per CTA); per (query, segment): %.1f insertions, "
-                     "%.1f log entries; %.2f compactions per warp-item\n",
+                     "%.1f log entries; %.2f compactions per warp-item; accumulator wait inside the first item of each unit %.1f Mcycles\n",
                      st[6] / units / 1e6, st[0] / units / 1e6, st[1] / units / 1e6, st[2] / (double)grid / 1e6,
-                     st[3] / lanes, st[4] / lanes, st[5] / ((double)p.n_items * cg * 4));
+                     st[3] / lanes, st[4] / lanes, st[5] / ((double)p.n_items * cg * 4), st[7] / units / 1e6);
     }
     if (rc == B2_OK) {  // fix-up: the all-exact kernel over the flagged query groups only (normally none)
         GemmParams px = p;
