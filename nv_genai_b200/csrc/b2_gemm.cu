@@ -10,12 +10,20 @@
 // Like faiss's BLAS path, L2 is |q|^2 + |x|^2 - 2 q.x clamped at 0 (the |x|^2 come from the
 // ingest kernel's side array), IP is the plain dot product.
 //
+// Default mode = FILTER AND REFINE (gemm_search_refine below): ONE approximate product per score on the tensor cores
+//   (bf16 rows: bf16(q).x; fp32 rows: bf16(q).bf16(x) over a bf16 shadow of the rows, or tf32 straight from the raw
+//   fp32 tile when there is no shadow), a rigorous per-query error band (band_kernel), every candidate within the band
+//   of the running k-th best logged, and merge_rescore (b2_merge.cu) re-scoring the candidates near the final cut in
+//   fp32, so ids and scores equal the all-exact arithmetic.  Lists that cannot hold a band are flagged and redone by
+//   a second launch with the ALL-EXACT arithmetic described next (also selected by B2_GEMM_REFINE=0 or the
+//   gemm_query_parts option).
+//
 // Mapping (one persistent CTA per SM, warp-specialised: TMA producer warp, MMA issuer warp, four
-// epilogue warps, and for fp32 rows eight transform warps):
+// epilogue warps, and for the exact fp32 arithmetic eight transform warps):
 //   M = 128 queries per CTA (TMEM lanes), N = 256 corpus rows (TMEM columns), K = the row,
 //   streamed in 64- or 128-byte slices.  Both operands are K-major, swizzled, brought in by TMA:
 //     A = the query tile, prepared by prep_queries_kernel,
-//     B = corpus rows straight from the row store.
+//     B = corpus rows straight from the row store (or its bf16 shadow).
 //   bf16 rows (kind::f16, 2 products):  D += q_hi.x + q_lo.x with q split into bf16 hi + lo, so q is
 //     carried to ~16 mantissa bits and the scores are exact with respect to the stored rows.  CTAs run
 //     as PAIRS (cta_group::2): one M = 256 instruction stream issued by the leader CTA, each CTA holds
@@ -36,20 +44,22 @@
 //     products in one accumulator), hence the separate accumulators: columns [0,256) main, [256,512)
 //     corrections, added in fp32 registers by the epilogue.  That uses all 512 TMEM columns, so the
 //     fp32 path is single-buffered (tile time ~33k cycles vs ~2k for the read-out).
-//   Epilogue: tcgen05.ld, one thread = one query = one TMEM lane; every score is compared with the
-//   thread's running threshold and the few survivors are pushed into (a) the query's sorted list of its
-//   k best keys in shared memory (warp-cooperative insertion; slot k-1 is the exact running k-th best =
-//   the threshold), and (b) a candidate log in global memory.
+//   Epilogue: tcgen05.ld (software-pipelined over 32-column chunks), one thread = one query = one TMEM lane.  A max
+//   tree rejects the chunks without a candidate for any of the warp's 32 queries; survivors replace the minimum of
+//   the query's UNSORTED list of its k best keys in shared memory (warp-cooperative, redux-tracked minimum = the
+//   running k-th best = the threshold; up to four queries per step while several have survivors) and are appended
+//   to the query's candidate log in global memory.
 //   Work item = (query tile, corpus segment); items are dealt round-robin to the CTAs with the
 //   query tile varying fastest, so the CTAs that run at the same time read the same corpus
 //   segment and the corpus is streamed from HBM about once.  A finished item publishes its
 //   k-th best key per query (atomicMax); later items of the same query tile start from that
-//   bound.  Every item emits k candidates per query; merge_partials_kernel finishes.
+//   bound, and running items trade bounds every 32 tiles.  Every item emits k (refine: k + slack) candidates per
+//   query; merge_partials_kernel / merge_rescore finish.
 //
 // Tie rule: equal keys keep the lower row id (a key has to be strictly better than the running
 // k-th to enter, rows arrive in id order, and bounds imported from other segments admit ties).
 //
-// Algorithmic work per launch: 2 * nq_pad * ntotal * K flop per product (x2 bf16, x3 fp32);
+// Algorithmic work per launch: 2 * nq_pad * ntotal * K flop per product (x1 filter-and-refine; all-exact: x2 bf16, x3 fp32);
 // corpus bytes ntotal * pitch read ~once from HBM, query tile re-read from L2 per corpus tile.
 #include <algorithm>
 #include <cstdlib>

@@ -1,12 +1,20 @@
-// Small-batch exact scan on the tensor cores: 3..32 queries (fp32 rows: from 5; up to 32 queries for k <= 64,
-// 16 for k <= 128), inner product, one pass over the rows.
+// Small-batch exact scan on the tensor cores: up to 32 queries (up to 32 for k <= 64, 16 for k <= 128) in one pass over
+// the rows; from 1 query on a row store of 8 GB or more, from 5 (fp32 rows) / 3 (bf16 rows) on a smaller one.
 //
-// Replaces faiss exhaustive_inner_product_seq + HeapResultHandler (faiss/utils/distances.cpp, the
-// nq < 20 path of IndexFlat::search), the same routine b2_scan.cu replaces, for the query counts
+// Replaces faiss exhaustive_inner_product_seq / exhaustive_L2sqr_seq + HeapResultHandler (faiss/utils/distances.cpp,
+// the nq < 20 path of IndexFlat::search), the same routines b2_scan.cu replaces, for the query counts
 // where the FP32 pipe cannot keep up with HBM: 16 queries x 10M x 1024 rows are 1.6e11 FMAs, 4.7 ms
 // at the FFMA peak against 5.8 ms of HBM time, and the FFMA scan reaches 13.7 ms.  Reached from
 // index.search at /root/reference/RetrievalAugmentedGeneration/examples/nvidia_api_catalog/chains.py:122-123
-// when a handful of requests are batched (BASELINE.json configs[1], batch 16).
+// (BASELINE.json configs[1], batch 1 and 16).
+//
+// Default on fp32 rows with k <= 64 = FILTER AND REFINE (template parameter APX, scan_tc_search_approx): ONE tf32
+// product per score straight from the raw tile -- no q_lo half, no transform warps, the kernel only streams the rows
+// (measured at 10M x 1024: 5.5 ms at 1 query, 6.0 ms at 16 = 1.13 / 1.04 of the copy peak) -- every CTA emits its
+// k + slack best approximate candidates per query and merge_rescore re-scores everything within the rigorous error
+// band of the k-th best in fp32 (inner product: the FFMA scan's dot product; L2: faiss's direct form sum (x - q)^2,
+// the filter keys being 2 q.x - |x|^2).  Queries whose band reaches the end of a full CTA list are redone exactly.
+// The all-exact arithmetic below serves bf16 rows, k > 64 and B2_SCAN_TC_EXACT=1 (inner product only).
 //
 // Mapping: the CORPUS is the M operand.  A tile is 128 consecutive rows (TMEM lanes), the 16 queries
 // are the N operand, K = the row, streamed by TMA in 128-byte swizzled slices straight from the row
