@@ -211,19 +211,33 @@ struct RescoreCtx {
     int l2_direct;  // re-score with sum (x - q)^2, faiss's form below 20 queries (exactly 0 for a stored copy of the query)
 };
 
-// sum (x - q)^2 over the row in the FFMA scan's order (fp32 rows)
+// sum (x - q)^2 over the row in the FFMA scan's order
 __device__ __forceinline__ float warp_exact_l2(const RescoreCtx& c, const float* __restrict__ qrow, uint32_t row, int lane) {
     const char* r = c.rows + (size_t)row * c.pitch_bytes;
     float acc = 0.f;
-    for (int e0 = lane * 4; e0 < c.d; e0 += 128) {
-        const float4 w = *reinterpret_cast<const float4*>(r + (size_t)e0 * 4);
-        const float x[4] = {w.x, w.y, w.z, w.w};
+    if (c.bf16) {
+        for (int e0 = lane * 8; e0 < c.d; e0 += 256) {
+            const uint4 w = *reinterpret_cast<const uint4*>(r + (size_t)e0 * 2);
+            const float x[8] = {bf16lo(w.x), bf16hi(w.x), bf16lo(w.y), bf16hi(w.y),
+                                bf16lo(w.z), bf16hi(w.z), bf16lo(w.w), bf16hi(w.w)};
 #pragma unroll
-        for (int e = 0; e < 4; ++e)
-            if (e0 + e < c.d) {
-                const float t = x[e] - __ldg(qrow + e0 + e);
-                acc = fmaf(t, t, acc);
-            }
+            for (int e = 0; e < 8; ++e)
+                if (e0 + e < c.d) {
+                    const float t = x[e] - __ldg(qrow + e0 + e);
+                    acc = fmaf(t, t, acc);
+                }
+        }
+    } else {
+        for (int e0 = lane * 4; e0 < c.d; e0 += 128) {
+            const float4 w = *reinterpret_cast<const float4*>(r + (size_t)e0 * 4);
+            const float x[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if (e0 + e < c.d) {
+                    const float t = x[e] - __ldg(qrow + e0 + e);
+                    acc = fmaf(t, t, acc);
+                }
+        }
     }
 #pragma unroll
     for (int s = 16; s >= 1; s >>= 1) acc += __shfl_xor_sync(kFull, acc, s);

@@ -388,11 +388,11 @@ int launch_scan_tc(const CUtensorMap& tmRows, const CUtensorMap& tmQ, const Scan
 bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t nq, bool approx) {
     if (getenv("B2_NO_TENSOR") != nullptr || getenv("B2_NO_SCAN_TC") != nullptr) return false;
     const int elem = dtype == B2_DTYPE_BF16 ? 2 : 4;
-    // L2 rides the approximate mode only (fp32 rows, k <= 64): keys 2 q.x - |x|^2 for the filter, the direct form
+    // L2 rides the approximate mode only (k <= 64; bf16 rows too: one bf16 product): keys 2 q.x - |x|^2 for the filter, the direct form
     // sum (x - q)^2 -- faiss's arithmetic below 20 queries -- for the candidates that are re-scored
     static const bool exact_only = getenv("B2_SCAN_TC_EXACT") != nullptr;
     // (from 20 queries on, L2 takes the GEMM kernel and the |q|^2 + |x|^2 - 2 q.x form, as faiss does)
-    if (metric == B2_METRIC_L2 && (dtype != B2_DTYPE_F32 || k > 64 || !approx || exact_only || nq >= 20)) return false;
+    if (metric == B2_METRIC_L2 && (k > 64 || !approx || exact_only || nq >= 20)) return false;
     // Measured at 10M x 1024 on B200 (kernel time, one pass): fp32 rows, FFMA scan 5.7-5.9 ms at 1 query, 6.1 ms at 4,
     // 7.2 ms at 5..8; this kernel 5.5 ms at 1, 5.7 ms at 2..4, 6.0 ms at 16, 6.8 ms at 32.  bf16 rows: FFMA scan
     // 2.9-3.3 ms at 1..2 queries; this kernel 2.76 ms at 1, 2.83 ms at 2, 3.2 ms at 16.  So on a large index every
@@ -433,14 +433,16 @@ static void pick_pipeline(int kslices, bool sps_allowed, int nqt, int kpad, int 
 // the error band of the k-th best).
 static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes, int d, const float* q_dev, int nq, int k,
                                  int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push,
-                                 const uint32_t* max_norm_ord, int metric, const float* norms) {
+                                 const uint32_t* max_norm_ord, int metric, const float* norms, int dtype) {
     const bool l2 = metric == B2_METRIC_L2;
+    const bool bf16 = dtype == B2_DTYPE_BF16;  // bf16 rows come here for L2 only: one bf16 product, the stored rows are exact
+    const int elem = bf16 ? 2 : 4;
     if (l2 && norms == nullptr) {
         set_error("tensor-core scan: L2 needs the rows' squared norms");
         return B2_ERR_INVALID;
     }
-    const size_t kbytes = (((size_t)d * 4 + kSlice - 1) / kSlice) * kSlice;
-    const int kp = (int)(kbytes / 4);
+    const size_t kbytes = (((size_t)d * elem + kSlice - 1) / kSlice) * kSlice;
+    const int kp = (int)(kbytes / elem);
     ScanTcParams p;
     p.n = (uint32_t)n;
     p.nq = nq;
@@ -481,21 +483,27 @@ static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes
     CUtensorMap tmRows, tmQ, tmQx;
     int promo = 256;
     if (const char* e = getenv("B2_SCAN_TC_L2PROMO")) promo = atoi(e);
-    int rc = make_map(&tmRows, false, kSlice, rows, (uint64_t)(pitch_bytes / 4), (uint64_t)n, pitch_bytes, kTileRows, promo);
-    if (rc == B2_OK) rc = make_map(&tmQ, false, kSlice, Q, (uint64_t)kp, (uint64_t)nqt, kbytes, nqt);
-    if (rc == B2_OK) rc = make_map(&tmQx, false, kSlice, Qx, (uint64_t)kp, (uint64_t)2 * nqt, kbytes, 2 * nqt);
+    int rc = make_map(&tmRows, bf16, kSlice, rows, (uint64_t)(pitch_bytes / elem), (uint64_t)n, pitch_bytes, kTileRows, promo);
+    if (rc == B2_OK) rc = make_map(&tmQ, bf16, kSlice, Q, (uint64_t)kp, (uint64_t)nqt, kbytes, nqt);
+    if (rc == B2_OK) rc = make_map(&tmQx, bf16, kSlice, Qx, (uint64_t)kp, (uint64_t)2 * nqt, kbytes, 2 * nqt);
     if (rc == B2_OK && cudaMemsetAsync(flags, 0, (size_t)(nq + 1) * 4, stream) != cudaSuccess) {
         set_error("tensor-core scan: cudaMemsetAsync failed");
         rc = B2_ERR_CUDA;
     }
-    if (rc == B2_OK) rc = prep_queries(q_dev, nq, d, nqt, kp, 1, false, Q, nullptr, nullptr, stream);
-    if (rc == B2_OK) rc = compute_band(q_dev, nq, d, nqt, kp / 8, false, l2, max_norm_ord, nullptr, band, stream);
+    if (rc == B2_OK) rc = prep_queries(q_dev, nq, d, nqt, kp, 1, bf16, Q, nullptr, nullptr, stream);
     if (rc == B2_OK)
-        rc = nqt == 16 ? launch_scan_tc<1, 16, true>(tmRows, tmQ, p, grid, smem, stream)
-                       : launch_scan_tc<1, 32, true>(tmRows, tmQ, p, grid, smem, stream);
+        rc = compute_band(q_dev, nq, d, nqt, bf16 ? kp / 16 : kp / 8, bf16, l2, max_norm_ord, nullptr, band, stream);
+    if (rc == B2_OK) {
+        if (bf16)
+            rc = nqt == 16 ? launch_scan_tc<0, 16, true>(tmRows, tmQ, p, grid, smem, stream)
+                           : launch_scan_tc<0, 32, true>(tmRows, tmQ, p, grid, smem, stream);
+        else
+            rc = nqt == 16 ? launch_scan_tc<1, 16, true>(tmRows, tmQ, p, grid, smem, stream)
+                           : launch_scan_tc<1, 32, true>(tmRows, tmQ, p, grid, smem, stream);
+    }
     if (rc == B2_OK)
         rc = merge_rescore(p.partial, nq, grid, p.klist, k, metric, D, I, (size_t)k, stream, nullptr, q_dev, d, rows,
-                           pitch_bytes, B2_DTYPE_F32, norms, band, push, flags, l2);
+                           pitch_bytes, dtype, norms, band, push, flags, l2);
     // ---- exact fix-up for the flagged queries (each kernel returns immediately when there is none)
     if (rc == B2_OK && l2) {
         // L2: the FFMA scan (direct form), a pass per 16 queries
@@ -503,7 +511,7 @@ static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes
             const int valid = std::min(16, nq - off);
             uint64_t* part = nullptr;
             int g2 = 0;
-            rc = scan_pass(rows, n, pitch_bytes, d, B2_DTYPE_F32, B2_METRIC_L2, q_dev + (size_t)off * d, valid,
+            rc = scan_pass(rows, n, pitch_bytes, d, dtype, B2_METRIC_L2, q_dev + (size_t)off * d, valid,
                            next_pow2(valid), k, num_sms, stream, &part, &g2, flags + nq);
             if (rc != B2_OK) break;
             PeerPush pp;
@@ -542,10 +550,10 @@ int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int d
     const bool bf16 = dtype == B2_DTYPE_BF16;
     const int elem = bf16 ? 2 : 4;
     static const bool no_approx = getenv("B2_SCAN_TC_EXACT") != nullptr;
-    if (!bf16 && max_norm_ord != nullptr && !no_approx && k <= 64 &&
+    if ((!bf16 || metric == B2_METRIC_L2) && max_norm_ord != nullptr && !no_approx && k <= 64 &&
         (long long)std::min<long long>(num_sms, (n + kTileRows - 1) / kTileRows) * next_pow2(k < 32 ? 32 : k) <= 12288)
         return scan_tc_search_approx(rows, n, pitch_bytes, d, q_dev, nq, k, num_sms, D, I, stream, push, max_norm_ord,
-                                     metric, norms);
+                                     metric, norms, dtype);
     if (metric != B2_METRIC_IP) {
         set_error("tensor-core scan: L2 needs the approximate mode (fp32 rows, k <= 64)");
         return B2_ERR_UNSUPPORTED;

@@ -229,8 +229,8 @@ def test_small_batch_tensor_scan_ties_and_dims():
 
 def test_small_batch_l2_keeps_the_direct_form():
     """L2 below 20 queries: faiss's direct form sum (x - q)^2, so a stored copy of the query is at distance 0.0 exactly.
-    On fp32 rows the tensor-core scan filters with 2 q.x - |x|^2 and the merge re-scores in the direct form; bf16 rows and
-    k > 64 stay on the FFMA scan."""
+    The tensor-core scan filters with 2 q.x - |x|^2 and the merge re-scores in the direct form; k > 64 stays on the FFMA
+    scan."""
     n, d, nq = 10_000, 256, 8
     x, q = _data(n, d, nq, False, seed=31)
     x[77] = q[2]
@@ -244,27 +244,33 @@ def test_small_batch_l2_keeps_the_direct_form():
     assert np.all(np.diff(D, axis=1) >= 0)
     (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, 100))  # k > 64: FFMA scan
     assert launches == 2 and I[2, 0] == 77 and D[2, 0] == 0.0
-    xb = _mk(flat.METRIC_L2, d, "bfloat16")
+    xb = _mk(flat.METRIC_L2, d, "bfloat16")  # bf16 rows: one bf16 product as the filter, same re-scoring
     xb.add(x)
     (D, I), launches = _launched_tensor_kernel(lambda: xb.search(q, 4))
-    assert launches == 2 and I[2, 0] == 77
+    assert launches == 6 and I[2, 0] == 77
+    xr = flat.round_bf16(x)
+    Dr, Ir, _ = flat.search_seq(xr, q, 4, flat.METRIC_L2)
+    assert_parity(D, I, Dr, Ir, xr, q, metric_ip=False)
 
 
+@pytest.mark.parametrize("dtype", ["float32", "bfloat16"])
 @pytest.mark.parametrize("nq,k", [(5, 10), (16, 10), (19, 64), (13, 1)])
-def test_small_batch_l2_on_the_tensor_scan_matches_the_sequential_oracle(nq, k):
+def test_small_batch_l2_on_the_tensor_scan_matches_the_sequential_oracle(nq, k, dtype):
     """Un-normalised rows (norms ~ d), planted copies, ragged d: ids and distances equal the direct-form oracle; more
     near-ties than a CTA list holds take the FFMA fix-up."""
     n, d = 40_000, 200
     x, q = _data(n, d, nq, False, seed=300 + nq)
     x[1234] = q[0]
     x[2000:2090] = q[1]  # 90 copies: overflow -> exact fix-up for that query
-    idx = _mk(flat.METRIC_L2, d)
+    idx = _mk(flat.METRIC_L2, d, dtype)
     idx.add(x)
     D, I = idx.search(q, k)
-    assert I[0, 0] == 1234 and D[0, 0] == 0.0
-    assert np.array_equal(I[1, :min(k, 90)], np.arange(2000, 2000 + min(k, 90))) and np.all(D[1, :min(k, 90)] == 0.0)
-    Dr, Ir, _ = flat.search_seq(x, q, k, flat.METRIC_L2)
-    assert_parity(D, I, Dr, Ir, x, q, metric_ip=False)
+    xr = flat.round_bf16(x) if dtype == "bfloat16" else x
+    assert I[0, 0] == 1234 and np.array_equal(I[1, :min(k, 90)], np.arange(2000, 2000 + min(k, 90)))
+    if dtype == "float32":
+        assert D[0, 0] == 0.0 and np.all(D[1, :min(k, 90)] == 0.0)
+    Dr, Ir, _ = flat.search_seq(xr, q, k, flat.METRIC_L2)
+    assert_parity(D, I, Dr, Ir, xr, q, metric_ip=False)
     assert np.all(np.diff(D, axis=1) >= 0)
 
 
