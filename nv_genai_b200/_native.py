@@ -9,7 +9,8 @@ import ctypes
 import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_PKG, "lib", "libb2flat.so")
+# B2FLAT_SO: load another build of the same ABI (A/B timing of two builds on one box); default = the in-tree build
+SO_PATH = os.environ.get("B2FLAT_SO") or os.path.join(_PKG, "lib", "libb2flat.so")
 
 B2_OK, B2_ERR_INVALID, B2_ERR_CUDA, B2_ERR_OOM, B2_ERR_UNSUPPORTED, B2_ERR_NO_DEVICE = range(6)
 METRIC_INNER_PRODUCT = 0  # same values as faiss.METRIC_INNER_PRODUCT / METRIC_L2

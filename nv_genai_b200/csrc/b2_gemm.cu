@@ -98,12 +98,14 @@ struct GemmParams {
     int mixed;          // fp32 rows: 1 = correction products on the bf16 pipe (see kernel comment), 0 = plain 3xTF32
     int refine;         // 1 = single approximate product; log everything within `band` of the running k-th, exact
                         //     re-scoring happens in merge_rescore_kernel (see "Filter and refine" above)
+    int rcap;           // slots of a query's key reservoir in shared memory (k < rcap <= kMaxRcap, row stride rcap + 1)
     int list_len;       // entries emitted per (query, segment): k, or k + slack when refine
     int only_flagged;   // fix-up launch: process only query groups whose flag is set
     const float* band;  // [nq_pad] refine: 2 x (bound on |approximate key - exact key|), per query
     unsigned long long* stats;  // diagnostics (B2_GEMM_DEBUG): [0] MMA cycles waiting for a free accumulator, [1] for operands,
-                        // [2] epilogue warp 0 cycles waiting for a full accumulator, [3] list insertions, [4] log entries,
-                        // [5] log compactions, [6] MMA warp cycles in total, [7] as [0] but only inside a unit's first item; nullptr = off
+                        // [2] epilogue warp 0 cycles waiting for a full accumulator, [3] reservoir admissions, [4] log entries,
+                        // [5] log compactions, [6] MMA warp cycles in total, [7] as [0] but only inside a unit's first item,
+                        // [8] reservoir selections; nullptr = off
     uint32_t* flags;    // [n_qt] refine: set when a query of the group had more in-band candidates than fit
     const float* norms; // |x|^2 per stored row
     uint64_t* cand;     // [grid][kCandCap][128]
@@ -127,64 +129,78 @@ __device__ __forceinline__ float select32(const float (&v)[32], int c) {
     return (c & 1) ? f1 : f0;
 }
 
-// The running k best keys of a query as an UNSORTED list plus the position of its minimum (kept in registers of the
-// query's lane): the new key overwrites the minimum, then the warp finds the new minimum with one 32-bit redux on the
-// order-preserving integer image of the keys.  About a third of the latency of a sorted insertion (ballots to find the
-// position, shuffles to shift), and the k-th best (= the minimum once the list is full; -inf before) is all the
-// epilogue needs from the list.  Survivors are also appended to the query's candidate log in global memory.
-__device__ __forceinline__ void coop_replace_min(float* __restrict__ A, int k, float x, int wpos, int lane, float& new_min,
-                                                 int& new_pos) {
-    if (lane == 0) A[wpos] = x;
-    __syncwarp();
-    uint32_t mn = 0xffffffffu;
-    int mp = 0;
+// The running k best keys of a query live in a RESERVOIR of `rcap` > k slots in shared memory (the scheme of faiss's
+// ReservoirResultHandler, which faiss itself switches to at k >= 100): a key above the query's threshold is appended
+// by the query's own lane - one shared-memory store, no warp cooperation - and only when the reservoir is full does
+// the warp select the k-th largest of its entries, keep the k best and raise the threshold to the k-th.  The
+// threshold therefore lags the true running k-th by at most rcap - k admissions (10-15 % more admissions than a
+// threshold updated on every insertion), and the cost per admitted key drops from a 400-600 cycle dependent chain
+// (replace the minimum, re-scan k entries for the new one) to a store plus 1 / (rcap - k) of a selection.
+//
+// coop_compact: all 32 lanes; R[0..n) are the reservoir entries of ONE query (n >= k, every entry > -inf).  Finds the
+// k-th largest by bisection on the order-preserving integer image of the keys, two bits per step (three counts packed
+// into one redux), starting below the leading bits all entries share; then moves the k best to R[0..k) (the entries
+// equal to the k-th fill up to exactly k) and returns the k-th largest.
+constexpr int kResPerLane = 6;   // rcap <= 192
+constexpr int kMaxRcap = 32 * kResPerLane;
+__device__ __forceinline__ float coop_compact(float* __restrict__ R, int n, int k, int lane) {
+    uint32_t e[kResPerLane];
+    uint32_t mx = 0u, mn = 0xffffffffu;
 #pragma unroll
-    for (int i = 0; i < kGemmMaxK / 32; ++i) {
+    for (int i = 0; i < kResPerLane; ++i) {
         const int idx = lane + 32 * i;
-        if (idx < k) {
-            const uint32_t u = f2ord(A[idx]);
-            if (u < mn) {
-                mn = u;
-                mp = idx;
-            }
-        }
+        e[i] = idx < n ? f2ord(R[idx]) : 0u;  // images of keys > -inf are > 0: 0 marks "no entry"
+        mx = max(mx, e[i]);
+        if (e[i] != 0u) mn = min(mn, e[i]);
     }
-    const uint32_t umin = __reduce_min_sync(kFull, mn);
-    const int who = __ffs(__ballot_sync(kFull, mn == umin)) - 1;
-    new_pos = __shfl_sync(kFull, mp, who);
-    new_min = ord2f(umin);
-    __syncwarp();
-}
-
-// Up to FOUR replacements at once, one per 8-lane group, into the lists of four different queries (src = the query's lane
-// in this warp, -1 = this group has nothing to do; doit = its key still beats the threshold).  While the thresholds of a
-// cold item settle, every lane has candidates in every chunk, and one insertion at a time was what stalled the tensor
-// pipe (70 % of the accumulator wait at k = 100 fell into each unit's first item).
-__device__ __forceinline__ void coop_replace_min4(float* __restrict__ keys_w, int k, int src, float x, int wpos, bool doit,
-                                                  int lane, float& new_min, int& new_pos) {
-    const int sl = lane & 7;
-    const unsigned gmask = 0xffu << (lane & 24);
-    float* A = keys_w + (size_t)(src < 0 ? 0 : src) * k;
-    if (doit && sl == 0) A[wpos] = x;
-    __syncwarp();
-    uint32_t mn = 0xffffffffu;
-    int mp = 0;
+    mx = __reduce_max_sync(kFull, mx);
+    mn = __reduce_min_sync(kFull, mn);
+    uint32_t prefix = mx;  // all entries equal
+    const uint32_t diff = mx ^ mn;
+    if (diff != 0u) {
+        int bit = 31 - __clz(diff);                               // highest bit in which two entries differ
+        prefix = (bit == 31) ? 0u : (mx & ~((2u << bit) - 1u));   // the bits above it are common to all entries
+        for (; bit >= 1; bit -= 2) {
+            const int sh = bit - 1;
+            const uint32_t c1 = prefix | (1u << sh), c2 = prefix | (2u << sh), c3 = prefix | (3u << sh);
+            uint32_t cnt = 0u;
 #pragma unroll
-    for (int i = 0; i < kGemmMaxK / 8; ++i) {
-        const int idx = sl + 8 * i;
-        if (idx < k) {
-            const uint32_t u = f2ord(A[idx]);
-            if (u < mn) {
-                mn = u;
-                mp = idx;
-            }
+            for (int i = 0; i < kResPerLane; ++i)
+                cnt += (e[i] >= c1 ? 1u : 0u) + (e[i] >= c2 ? (1u << 10) : 0u) + (e[i] >= c3 ? (1u << 20) : 0u);
+            const uint32_t tot = __reduce_add_sync(kFull, cnt);
+            if ((int)(tot >> 20) >= k) prefix = c3;
+            else if ((int)((tot >> 10) & 1023u) >= k) prefix = c2;
+            else if ((int)(tot & 1023u) >= k) prefix = c1;
+        }
+        if (bit == 0) {
+            const uint32_t c1 = prefix | 1u;
+            uint32_t cnt = 0u;
+#pragma unroll
+            for (int i = 0; i < kResPerLane; ++i) cnt += e[i] >= c1 ? 1u : 0u;
+            if ((int)__reduce_add_sync(kFull, cnt) >= k) prefix = c1;
         }
     }
-    const uint32_t umin = __reduce_min_sync(gmask, mn);
-    const int who = __ffs(__ballot_sync(kFull, mn == umin) & gmask) - 1;
-    new_pos = __shfl_sync(kFull, mp, who);
-    new_min = ord2f(umin);
+    // prefix = image of the k-th largest entry.  All entries are in registers: overwrite the row in place.
     __syncwarp();
+    const uint32_t lt = (1u << lane) - 1u;
+    int off = 0;
+#pragma unroll
+    for (int i = 0; i < kResPerLane; ++i) {
+        const bool g = e[i] > prefix;
+        const uint32_t b = __ballot_sync(kFull, g);
+        if (g) R[off + __popc(b & lt)] = ord2f(e[i]);
+        off += __popc(b);
+    }
+#pragma unroll
+    for (int i = 0; i < kResPerLane; ++i) {
+        const bool q = e[i] == prefix;
+        const uint32_t b = __ballot_sync(kFull, q);
+        const int pos = off + __popc(b & lt);
+        if (q && pos < k) R[pos] = ord2f(prefix);
+        off += __popc(b);
+    }
+    __syncwarp();
+    return ord2f(prefix);
 }
 
 // Keep exactly the current top-k of this thread's log, in arrival order: keys above tau, plus the earliest
@@ -293,8 +309,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int S = p.num_stages;
     uint8_t* stages = smem;
     uint8_t* corr_tiles = stages + (size_t)S * STAGE_BYTES;                              // [kCorrSlots][B tile] (fp32 rows)
-    float* heap_s = reinterpret_cast<float*>(corr_tiles + (KIND == 1 ? p.corr_slots * kBTileBytes : 0));  // [128 queries][k] sorted keys
-    float* nrm_s = heap_s + (size_t)p.k * kEpiThreads;                                    // [2][256]
+    float* heap_s = reinterpret_cast<float*>(corr_tiles + (KIND == 1 ? p.corr_slots * kBTileBytes : 0));  // [128 queries][rcap + 1] key reservoirs
+    float* nrm_s = heap_s + (size_t)(p.rcap + 1) * kEpiThreads;                           // [2][256]
     uint64_t* bars = reinterpret_cast<uint64_t*>(nrm_s + 2 * kTileN);
     uint64_t* full_bar = bars;                    // [S] TMA -> MMA / transform
     uint64_t* empty_bar = bars + kMaxStages;      // [S] MMA -> TMA
@@ -587,12 +603,14 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         constexpr float kNegInf = -__builtin_huge_valf();
         const int ql = tid;  // 0..127
         const int k = p.k;
-        float* keys_w = heap_s + (size_t)(warp * 32) * k;  // this warp's 32 key lists (unsorted, minimum tracked), k slots each
+        const int rcap = p.rcap, rstride = p.rcap + 1;       // odd row stride: lane-parallel appends spread over the banks
+        float* keys_w = heap_s + (size_t)(warp * 32) * rstride;  // this warp's 32 key reservoirs
+        float* R = keys_w + (size_t)lane * rstride;              // this lane's (= this query's) reservoir
         uint64_t* log = p.cand + (size_t)blockIdx.x * kCandCap * kEpiThreads + ql;
         const bool l2 = p.metric == B2_METRIC_L2;
         uint32_t tc = 0;
         long long w_full = 0;
-        unsigned n_ins = 0, n_log = 0, n_cmp = 0;
+        unsigned n_ins = 0, n_log = 0, n_cmp = 0, n_sel = 0;
         for (int item = unit; item < p.n_items; item += n_units) {
             if (p.only_flagged && __ldcg(p.flags + item % p.n_qt) == 0u) continue;  // fix-up launch: flagged groups only
             const int qt = (item % p.n_qt) * CG + (int)cta_rank, seg = item / p.n_qt;
@@ -610,9 +628,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             float thr_log = thr0;  // a key is logged if it is above this (== thr unless refine)
             bool overflow = false;
             int cnt = 0;
-            for (int i = lane; i < 32 * k; i += 32) keys_w[i] = kNegInf;
-            float kth_own = kNegInf;  // minimum of this lane's list = its k-th best key once the list is full
-            int wpos = 0;             // where that minimum sits
+            float kth_own = kNegInf;  // k-th best key of this lane's query at its reservoir's last selection (-inf before the first)
+            int rc = 0;               // entries in this lane's reservoir
             __syncwarp();
             for (int t = t0; t < t1; ++t, ++tc) {
                 const uint32_t buf = tc % NBUF, par = (tc / NBUF) & 1u;
@@ -697,90 +714,60 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     const int left = limit - ch * 32;
                     const uint32_t valid = (left >= 32) ? 0xffffffffu : ((left <= 0) ? 0u : ((1u << left) - 1u));
                     ml &= valid;
-                    uint32_t m = 0;  // columns above the insertion threshold (a subset of ml)
+                    uint32_t m = 0;  // columns above the admission threshold that still have to enter the reservoir
                     if (refine) {
                         while (ml) {  // lane-local: log every in-band candidate of this chunk, in row order
                             const int c = __ffs(ml) - 1;
                             ml &= ml - 1u;
                             const float kv = select32(key, c);
-                            if (kv > thr) m |= 1u << c;
                             if (cnt < kCandCap) {
                                 log[(size_t)cnt * kEpiThreads] = pack_cand(kv, row0 + ch * 32 + c);
                                 ++cnt;
                                 ++n_log;
                             }
+                            if (kv > thr) {
+                                if (rc < rcap) {
+                                    R[rc++] = kv;
+                                    ++n_ins;
+                                } else {
+                                    m |= 1u << c;  // reservoir full: after the selection below
+                                }
+                            }
                         }
                     } else {
                         m = ml;  // thr_log == thr
                     }
-                    m &= valid;
-                    // survivors, one (query, column) at a time, each inserted by the whole warp
-                    unsigned pending = __ballot_sync(kFull, m != 0u);
-                    while (pending) {
-                        if (__popc(pending) >= 2) {
-                            // several queries have a survivor: serve up to four of them at once, one per 8-lane group
-                            unsigned pm = pending;
-#pragma unroll
-                            for (int j = 0; j < 3; ++j)
-                                if (j < (lane >> 3)) pm &= pm - 1u;  // group g takes the (g + 1)-th pending lane
-                            const int src4 = pm ? (__ffs(pm) - 1) : -1;
-                            const int ssafe = src4 < 0 ? 0 : src4;
-                            const int c = m ? (__ffs(m) - 1) : 0;
-                            const float kv = select32(key, c);
-                            const float xs = __shfl_sync(kFull, kv, ssafe);
-                            const float ts = __shfl_sync(kFull, thr, ssafe);
-                            const int wp = __shfl_sync(kFull, wpos, ssafe);
-                            const bool doit = src4 >= 0 && xs > ts;  // the threshold may have risen since the mask was built
-                            float nmin;
-                            int npos;
-                            coop_replace_min4(keys_w, k, src4, xs, wp, doit, lane, nmin, npos);
-                            // back to the owners: pending lane number r (in lane order) was served by group r
-                            const int rank = __popc(pending & ((1u << lane) - 1u));
-                            const bool mine = ((pending >> lane) & 1u) != 0u && rank < 4;
-                            const int gl = (rank & 3) * 8;
-                            const float omin = __shfl_sync(kFull, nmin, gl);
-                            const int opos = __shfl_sync(kFull, npos, gl);
-                            const int odid = __shfl_sync(kFull, doit ? 1 : 0, gl);
-                            if (mine) {
-                                if (odid) {
-                                    kth_own = omin;
-                                    wpos = opos;
-                                    ++n_ins;
-                                    if (!refine) {
-                                        log[(size_t)cnt * kEpiThreads] = pack_cand(kv, row0 + ch * 32 + c);
-                                        ++cnt;
-                                    }
-                                    thr = fmaxf(thr0, omin);
-                                    thr_log = fmaxf(thr0, omin - band);
-                                }
-                                m &= m - 1u;
-                            }
-                            pending = __ballot_sync(kFull, m != 0u);
-                            continue;
-                        }
-                        const int src = __ffs(pending) - 1;
-                        const int c = m ? (__ffs(m) - 1) : 0;
-                        const float kv = select32(key, c);
-                        const float xs = __shfl_sync(kFull, kv, src);
-                        const float ts = __shfl_sync(kFull, thr, src);
-                        if (xs > ts) {  // the threshold may have risen since the mask was built
-                            float kth;
-                            int npos;
-                            coop_replace_min(keys_w + (size_t)src * k, k, xs, __shfl_sync(kFull, wpos, src), lane, kth, npos);
+                    // Reservoirs that are full get their k best selected (warp-cooperative, one query at a time; the
+                    // query's threshold rises to its k-th best), then the lanes append what they still hold.
+                    unsigned busy = __ballot_sync(kFull, m != 0u || rc >= rcap);
+                    while (busy) {
+                        unsigned fullm = __ballot_sync(kFull, rc >= rcap);
+                        while (fullm) {
+                            const int src = __ffs(fullm) - 1;
+                            fullm &= fullm - 1u;
+                            const float kth = coop_compact(keys_w + (size_t)src * rstride, rcap, k, lane);
                             if (lane == src) {
+                                rc = k;
                                 kth_own = kth;
-                                wpos = npos;
+                                thr = fmaxf(thr0, kth);
+                                thr_log = fmaxf(thr0, kth - band);
+                                ++n_sel;
+                            }
+                        }
+                        while (m != 0u && rc < rcap) {
+                            const int c = __ffs(m) - 1;
+                            m &= m - 1u;
+                            const float kv = select32(key, c);
+                            if (kv > thr) {  // the threshold may have risen since the mask was built
+                                R[rc++] = kv;
                                 ++n_ins;
                                 if (!refine) {
                                     log[(size_t)cnt * kEpiThreads] = pack_cand(kv, row0 + ch * 32 + c);
                                     ++cnt;
                                 }
-                                thr = fmaxf(thr0, kth);
-                                thr_log = fmaxf(thr0, kth - band);
                             }
                         }
-                        if (lane == src) m &= m - 1u;
-                        pending = __ballot_sync(kFull, m != 0u);
+                        busy = __ballot_sync(kFull, m != 0u);  // whoever still holds survivors filled its reservoir
                     }
                 };
                 if (KIND == 1) {
@@ -819,7 +806,23 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     else mbar_arrive(smem_u32(tempty_bar + buf));
                 }
             }
-            // ---- item done: emit this query's k best of the segment, publish the bound
+            // ---- item done: the exact k-th best of the segment (one last selection where the reservoir holds more than
+            // k keys, or exactly k that were never selected), emit this query's k best, publish the bound
+            {
+                unsigned todo = __ballot_sync(kFull, active && rc >= k && (rc > k || kth_own == kNegInf));
+                while (todo) {
+                    const int src = __ffs(todo) - 1;
+                    todo &= todo - 1u;
+                    const int n_src = __shfl_sync(kFull, rc, src);
+                    const float kth = coop_compact(keys_w + (size_t)src * rstride, n_src, k, lane);
+                    if (lane == src) {
+                        rc = k;
+                        kth_own = kth;
+                        thr_log = fmaxf(thr0, kth - band);
+                        ++n_sel;
+                    }
+                }
+            }
             const float tau = kth_own;
             const bool full = active && tau > kNegInf;
             const int L = p.list_len;
@@ -850,6 +853,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             atomicAdd(p.stats + 3, (unsigned long long)n_ins);
             atomicAdd(p.stats + 4, (unsigned long long)n_log);
             if (lane == 0) atomicAdd(p.stats + 5, (unsigned long long)n_cmp);
+            atomicAdd(p.stats + 8, (unsigned long long)n_sel);
         }
     }
 
@@ -973,11 +977,27 @@ int compute_band(const float* q_dev, int nq, int d, int nq_pad, int steps, bool 
 
 namespace {
 
-size_t gemm_smem_bytes(bool fp32_rows, int na, int swb, int stages, int k, int cg = 1, int corr_slots = 2) {
+// smallest reservoir for k results: room for at least 8 admissions between two selections
+int min_rcap(int k) { return (k + 8 + 7) / 8 * 8; }
+
+// `slots` = floats per query in the key reservoirs: rcap + 1
+size_t gemm_smem_slots(bool fp32_rows, int na, int swb, int stages, int slots, int cg, int corr_slots) {
     const size_t stage = (size_t)na * kTileM * swb + (size_t)(kTileN / cg) * swb;
     const size_t corr = fp32_rows ? (size_t)corr_slots * (kTileN / cg) * swb : 0;
-    return 1024 + stages * stage + corr + (size_t)k * kEpiThreads * 4 + 2 * kTileN * 4 +
+    return 1024 + stages * stage + corr + (size_t)slots * kEpiThreads * 4 + 2 * kTileN * 4 +
            (4 * kMaxStages + kMaxCorrSlots + 4) * 8 + 16;
+}
+// with the smallest reservoir of that k: what the pipeline depth is chosen against
+size_t gemm_smem_bytes(bool fp32_rows, int na, int swb, int stages, int k, int cg = 1, int corr_slots = 2) {
+    return gemm_smem_slots(fp32_rows, na, swb, stages, min_rcap(k) + 1, cg, corr_slots);
+}
+// The largest reservoir (multiple of 8, at most 2k and kMaxRcap) that fits beside an already chosen pipeline: a longer
+// reservoir means fewer selections and a threshold that lags less in relative terms.
+int pick_rcap(bool fp32_rows, int na, int swb, int stages, int k, int cg, int corr_slots) {
+    int rcap = min_rcap(k);
+    const int cap = std::min(kMaxRcap, std::max(32, 2 * k));
+    while (rcap + 8 <= cap && gemm_smem_slots(fp32_rows, na, swb, stages, rcap + 8 + 1, cg, corr_slots) <= 227 * 1024) rcap += 8;
+    return rcap;
 }
 
 template <int KIND, int NA, int SWB, int CG>
@@ -1161,7 +1181,8 @@ static int gemm_search_cg(const void* rows, int64_t n, size_t pitch_bytes, int d
             while (stages > 2 && gemm_smem_bytes(true, na, swb, stages, k, cg, corr_slots) > 227 * 1024) --stages;
         }
     }
-    const size_t smem = gemm_smem_bytes(!bf16, na, swb, stages, k, cg, corr_slots);
+    p.rcap = pick_rcap(!bf16, na, swb, stages, k, cg, corr_slots);
+    const size_t smem = gemm_smem_slots(!bf16, na, swb, stages, p.rcap + 1, cg, corr_slots);
     p.corr_slots = corr_slots;
     if (smem > 227 * 1024) {
         set_error("tensor-core search: k=%d does not fit shared memory", k);
@@ -1285,7 +1306,8 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     }
     const size_t kbytes_x = (((size_t)d * elem + swb_x - 1) / swb_x) * swb_x;
     const int kp_x = (int)(kbytes_x / elem);
-    const size_t smem_x = gemm_smem_bytes(!bf16, 2, swb_x, stages_x, k, cg, corr_x);
+    const int rcap_x = pick_rcap(!bf16, 2, swb_x, stages_x, k, cg, corr_x);
+    const size_t smem_x = gemm_smem_slots(!bf16, 2, swb_x, stages_x, rcap_x + 1, cg, corr_x);
     if (smem_x > 227 * 1024) {
         set_error("tensor-core search: k=%d does not fit shared memory", k);
         return B2_ERR_UNSUPPORTED;
@@ -1379,7 +1401,8 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     if (rc == B2_OK)
         rc = compute_band(q_dev, (int)nq, d, p.nq_pad, abf16 ? kp / 16 : kp / 8, abf16, metric == B2_METRIC_L2, max_norm_ord,
                           approx != nullptr ? approx->err_ord : nullptr, band, stream);
-    const size_t smem = gemm_smem_bytes(false, 1, swb, stages, k, cg, 0);
+    p.rcap = pick_rcap(false, 1, swb, stages, k, cg, 0);
+    const size_t smem = gemm_smem_slots(false, 1, swb, stages, p.rcap + 1, cg, 0);
     static const bool debug_t = std::getenv("B2_GEMM_DEBUG") != nullptr;
     cudaEvent_t dbg_ev0 = nullptr;
     if (debug_t) {
@@ -1410,15 +1433,15 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
         for (uint32_t f : fl) nf += f != 0u;
         std::fprintf(stderr, "[b2 gemm refine] k=%d list_len=%d n_seg=%d n_qt=%d flagged=%d band[0]=%g\n", k, p.list_len,
                      p.n_seg, p.n_qt, nf, bd.empty() ? 0.0 : (double)bd[0]);
-        unsigned long long st[8] = {0};
+        unsigned long long st[9] = {0};
         cudaMemcpy(st, p.stats, sizeof(st), cudaMemcpyDeviceToHost);
         const double units = (double)(grid / cg), lanes = (double)p.nq_pad * p.n_seg;
         std::fprintf(stderr,
                      "[b2 gemm refine] per MMA warp: %.1f Mcycles, waiting for a free accumulator %.1f, for operands %.1f; "
                      "epilogue warp 0 waiting for a full accumulator %.1f (per CTA); per (query, segment): %.1f insertions, "
-                     "%.1f log entries; %.2f compactions per warp-item; accumulator wait inside the first item of each unit %.1f Mcycles\n",
+                     "%.1f log entries, %.2f reservoir selections (rcap %d); %.2f compactions per warp-item; accumulator wait inside the first item of each unit %.1f Mcycles\n",
                      st[6] / units / 1e6, st[0] / units / 1e6, st[1] / units / 1e6, st[2] / (double)grid / 1e6,
-                     st[3] / lanes, st[4] / lanes, st[5] / ((double)p.n_items * cg * 4), st[7] / units / 1e6);
+                     st[3] / lanes, st[4] / lanes, st[8] / lanes, p.rcap, st[5] / ((double)p.n_items * cg * 4), st[7] / units / 1e6);
     }
     if (rc == B2_OK) {  // fix-up: the all-exact kernel over the flagged query groups only (normally none)
         GemmParams px = p;
@@ -1428,6 +1451,7 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
         px.kstages = (int)(kbytes_x / swb_x);
         px.num_stages = stages_x;
         px.corr_slots = corr_x;
+        px.rcap = rcap_x;
         px.mixed = bf16 ? 0 : 1;
         rc = bf16 ? launch_gemm_cg<0, 2, 64>(tmAx, tmBx, px, grid, smem_x, stream, cg)
                   : launch_gemm_cg<1, 2, 64>(tmAx, tmBx, px, grid, smem_x, stream, cg);
