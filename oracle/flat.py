@@ -131,6 +131,12 @@ def round_bf16(x: np.ndarray) -> np.ndarray:
     return y
 
 
+def round_bf16_inplace(x: np.ndarray) -> None:
+    """round_bf16 without the copy (streaming checks over multi-GB blocks)."""
+    assert x.dtype == np.float32 and x.flags.c_contiguous
+    lib().b2o_round_bf16(_f32(x), x.size)
+
+
 # --------------------------------------------------------------------------
 # IndexFlat.search
 # --------------------------------------------------------------------------
