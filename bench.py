@@ -30,14 +30,37 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-METRIC = "queries/sec, exact top-k (IndexFlatIP) over 10M x 1024 fp32"
+UNIT = "queries/s"
+# Seeds of the synthetic corpus / query streams.  The oracle keeps its own copy
+# (oracle/flat.py CORPUS_SEED / QUERY_SEED); tests/test_abi.py checks that the two agree.
+CORPUS_SEED = 0x5EED0001
+QUERY_SEED = 0x5EED0002
+
+# BASELINE.json configs, by name.  cfg4 is the 100M x 1024 bf16 corpus sharded over N >= 2 GPUs; at N = 1 it runs its
+# weak-scaling reference point, the 12.5M-row shard one GPU holds at N = 8 (definition ii).
+CONFIGS = {
+    "cfg1": dict(rows=100_000, batch=1, k=4, dtype="float32", metric="l2", normalize=False,
+                 label="BASELINE.json configs[0]: IndexFlatL2, the 5_mins_rag_no_gpu shape"),
+    "cfg2": dict(rows=10_000_000, batch=1, k=10, dtype="float32", metric="ip", normalize=True,
+                 label="BASELINE.json configs[1], batch 1"),
+    "cfg2b16": dict(rows=10_000_000, batch=16, k=10, dtype="float32", metric="ip", normalize=True,
+                    label="BASELINE.json configs[1], batch 16"),
+    "cfg3": dict(rows=10_000_000, batch=4096, k=100, dtype="float32", metric="ip", normalize=True,
+                 label="BASELINE.json configs[2], fp32 rows"),
+    "cfg3bf16": dict(rows=10_000_000, batch=4096, k=100, dtype="bfloat16", metric="ip", normalize=True,
+                     label="BASELINE.json configs[2], bf16 rows"),
+    "cfg4": dict(rows=100_000_000, batch=1024, k=100, dtype="bfloat16", metric="ip", normalize=True,
+                 label="BASELINE.json configs[3]"),
+    "cfg5": dict(rows=10_000_000, batch=256, k=20, dtype="float32", metric="ip", normalize=True,
+                 label="BASELINE.json configs[4]: the search of max_marginal_relevance_search (fetch_k = 20, batch 256); "
+                       "ingest and the MMR kernel are under extra.cfg5_ingest_and_mmr"),
+}
 
 
 def metric_name(a):
-    if a.rows == 10_000_000 and a.dim == 1024 and a.dtype == "float32":
-        return METRIC
-    return f"queries/sec, exact top-k (IndexFlatIP) over {a.rows} x {a.dim} {a.dtype}"
-UNIT = "queries/s"
+    rows = f"{a.rows // 1_000_000}M" if a.rows % 1_000_000 == 0 else str(a.rows)
+    kind = "IndexFlatIP" if a.metric == "ip" else "IndexFlatL2"
+    return f"queries/sec, exact top-k ({kind}) over {rows} x {a.dim} {'fp32' if a.dtype == 'float32' else 'bf16'}"
 
 
 def parse_args():
@@ -46,21 +69,41 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--rows", type=int, default=10_000_000)
+    ap.add_argument("--config", default="cfg2", choices=sorted(CONFIGS),
+                    help="a BASELINE.json configuration by name (default cfg2 = configs[1], batch 1: the one the metric is "
+                         "quoted on); --rows/--batch/--k/--dtype/--metric override single fields")
+    ap.add_argument("--rows", type=int, default=None)
     ap.add_argument("--dim", type=int, default=1024)
-    ap.add_argument("--batch", type=int, default=1)
-    ap.add_argument("--k", type=int, default=10)
-    ap.add_argument("--dtype", default="float32", choices=["float32", "bfloat16"])
+    ap.add_argument("--batch", type=int, default=None)
+    ap.add_argument("--k", type=int, default=None)
+    ap.add_argument("--dtype", default=None, choices=["float32", "bfloat16"])
+    ap.add_argument("--metric", default=None, choices=["ip", "l2"])
     ap.add_argument("--cpu-sample-rows", type=int, default=1_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-check", action="store_true", help="skip the planted-row / oracle-query check of the results")
     ap.add_argument("--extra", action="store_true",
-                    help="also time batch 16 and BASELINE configs[2] (batch 4096, k=100, fp32 and bf16 rows) under 'extra'")
-    return ap.parse_args()
+                    help="also time the other BASELINE configs (batch 16, configs[2] fp32 and bf16, configs[4], configs[0]) under 'extra'")
+    a = ap.parse_args()
+    preset = dict(CONFIGS[a.config])
+    a.label = preset.pop("label")
+    a.overridden = [kk for kk in ("rows", "batch", "k", "dtype", "metric") if getattr(a, kk) is not None]
+    for kk, v in preset.items():
+        if getattr(a, kk, None) is None:
+            setattr(a, kk, v)
+    if a.config == "cfg4" and a.gpus == 1 and "rows" not in a.overridden:
+        a.rows = 12_500_000
+        a.label += " - weak-scaling reference point: the 12.5M-row shard one GPU holds at 8 GPUs"
+    return a
 
 
 def workload_name(a):
-    return (f"IndexFlatIP over {a.rows}x{a.dim} {a.dtype} normalised synthetic embeddings, "
-            f"query batch {a.batch}, k={a.k} (BASELINE.json configs[1])")
+    kind = "IndexFlatIP" if a.metric == "ip" else "IndexFlatL2"
+    how = "normalised " if a.normalize else ""
+    s = (f"{kind} over {a.rows}x{a.dim} {a.dtype} {how}synthetic embeddings, query batch {a.batch}, k={a.k} "
+         f"(--config {a.config}: {a.label}")
+    if a.overridden:
+        s += "; overridden on the command line: " + ", ".join(a.overridden)
+    return s + ")"
 
 
 # ------------------------------------------------------------------------------------------ clocks

@@ -91,7 +91,11 @@ struct GemmParams {
     int k;
     int kstages;        // K slices per tile
     int metric;
-    int n_qt, n_seg, tiles_per_seg, n_tiles, n_items;
+    int n_qt, n_seg, tiles_per_seg, n_tiles, n_items;  // n_tiles = LOGICAL tiles of this launch (see tile_of)
+    int tile_mul;       // logical tile u -> corpus tile u * tile_mul            (threshold pre-pass: every tile_mul-th tile)
+    int tile_skip;      // != 0: logical tile u -> u + u / (tile_skip - 1) + 1   (main pass: all but every tile_skip-th tile)
+    int n_lists;        // candidate lists per query in `partial`; this launch writes lists list_base .. list_base + n_seg - 1
+    int list_base;
     int num_stages;
     int corr_slots;     // fp32 rows: correction tiles in the ring (2..4)
     int trunc_hi;       // fp32 rows: 1 = leave the raw tile as the hi operand (hardware truncation), 0 = round it in place
@@ -109,7 +113,7 @@ struct GemmParams {
     uint32_t* flags;    // [n_qt] refine: set when a query of the group had more in-band candidates than fit
     const float* norms; // |x|^2 per stored row
     uint64_t* cand;     // [grid][kCandCap][128]
-    uint64_t* partial;  // [nq_pad][n_seg][k]
+    uint64_t* partial;  // [nq_pad][n_lists][list_len]
     uint32_t* tau;      // [nq_pad] ordered image of an exclusive lower bound of the final k-th key
 };
 
@@ -269,6 +273,12 @@ __device__ __forceinline__ void compact_band(uint64_t* __restrict__ log, int& cn
     if (active) cnt = w;
 }
 
+// Corpus tile of a launch's logical tile u.  One launch covers either every tile, or every tile_mul-th tile (the
+// threshold pre-pass over a sample of the rows), or all the others (the main pass after such a pre-pass).
+__device__ __forceinline__ int tile_of(const GemmParams& p, int u) {
+    return p.tile_skip ? u + u / (p.tile_skip - 1) + 1 : u * p.tile_mul;
+}
+
 // ------------------------------------------------------------------ the kernel
 // KIND 0: bf16 rows, kind::f16.  KIND 1: fp32 rows, fp32-faithful (tf32 main + bf16 correction, transform warps).
 // KIND 2: fp32 rows, ONE tf32 product straight from the raw tile (approximate; only with refine).
@@ -367,7 +377,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int qt = (item % p.n_qt) * CG + (int)cta_rank, seg = item / p.n_qt;
             const int t0 = seg * p.tiles_per_seg;
             const int t1 = min(p.n_tiles, t0 + p.tiles_per_seg);
-            for (int t = t0; t < t1; ++t) {
+            for (int u = t0; u < t1; ++u) {
+                const int t = tile_of(p, u);
                 for (int ks = 0; ks < p.kstages; ++ks) {
                     mbar_wait(smem_u32(empty_bar + stage), phase ^ 1u);
                     if (elect_one()) {
@@ -631,13 +642,14 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             float kth_own = kNegInf;  // k-th best key of this lane's query at its reservoir's last selection (-inf before the first)
             int rc = 0;               // entries in this lane's reservoir
             __syncwarp();
-            for (int t = t0; t < t1; ++t, ++tc) {
+            for (int u = t0; u < t1; ++u, ++tc) {
+                const int t = tile_of(p, u);
                 const uint32_t buf = tc % NBUF, par = (tc / NBUF) & 1u;
                 const uint32_t row0 = (uint32_t)t * kTileN;
                 // Every 32 tiles the segments of a query that run at the same time (on other SMs) trade bounds: publish
                 // this list's k-th, pick up the best one published so far.  Without it every segment re-learns its
                 // threshold from -inf (measured at k = 100: 300 insertions per (query, segment) where ~100 suffice).
-                if (((t - t0) & 31) == 31 && active) {
+                if (((u - t0) & 31) == 31 && active) {
                     const float kth_now = kth_own;
                     if (kth_now > kNegInf) atomicMax(p.tau + q, f2ord(refine ? kth_now - band : kth_now) - 1u);
                     thr0 = fmaxf(thr0, ord2f(__ldcg(p.tau + q)));
@@ -835,7 +847,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 if (full) atomicMax(p.tau + q, f2ord(tau) - 1u);
             }
             if (active) {
-                uint64_t* out = p.partial + ((size_t)q * p.n_seg + seg) * L;
+                uint64_t* out = p.partial + ((size_t)q * p.n_lists + p.list_base + seg) * L;
                 for (int i0 = 0; i0 < L; i0 += 8) {
                     uint64_t e[8];
 #pragma unroll
@@ -959,6 +971,72 @@ __global__ void band_kernel(const float* __restrict__ q, int nq, int d, int nq_p
         // at most (|q| + |x|)^2)
         if (l2) b = 2.f * b + 2.f * (xn + qn) * (xn + qn) * (float)d * 5.9604645e-8f;
         band[row] = b;
+    }
+}
+
+// After the threshold pre-pass: tau[q] = an exclusive lower bound of the final k-th key of query q = the k-th largest
+// key among ALL candidates the pre-pass emitted for q (the union of its parts' lists, each of which holds its part's k
+// best), less the band in refine mode.  The k-th best of any subset of the rows bounds the k-th best of all rows
+// from below, so every work item of the main pass starts with a useful threshold instead of -inf: without it each
+// of the items that start cold admits k (1 + ln(rows / k)) keys and runs the slow path of the epilogue for most chunks.
+// One warp per query; the keys are staged in shared memory, bisection on the key bits (two per step).
+constexpr int kUnionWarps = 4;
+__global__ void __launch_bounds__(kUnionWarps * 32)
+tau_union_kernel(const uint64_t* __restrict__ partial, int nq, int n_lists, int list_base, int n_parts, int list_len, int k,
+                 const float* __restrict__ band, uint32_t* __restrict__ tau) {
+    extern __shared__ uint32_t ukeys[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = blockIdx.x * kUnionWarps + warp;
+    if (q >= nq) return;
+    const int n = n_parts * list_len;
+    uint32_t* K = ukeys + (size_t)warp * n;
+    const uint64_t* src = partial + ((size_t)q * n_lists + list_base) * list_len;  // the parts' lists are contiguous
+    int valid = 0;
+    uint32_t mx = 0u, mn = 0xffffffffu;
+    for (int i = lane; i < n; i += 32) {
+        const uint64_t c = src[i];
+        const uint32_t o = (c == B2_SENTINEL) ? 0u : (uint32_t)(c >> 32);  // 0 = no entry (images of real keys are larger)
+        K[i] = o;
+        if (o != 0u) {
+            ++valid;
+            mx = max(mx, o);
+            mn = min(mn, o);
+        }
+    }
+    valid = __reduce_add_sync(kFull, valid);
+    if (valid < k) return;  // fewer than k candidates: no bound (tau keeps its initial value)
+    mx = __reduce_max_sync(kFull, mx);
+    mn = __reduce_min_sync(kFull, mn);
+    __syncwarp();
+    uint32_t prefix = mx;
+    const uint32_t diff = mx ^ mn;
+    if (diff != 0u) {
+        int bit = 31 - __clz(diff);
+        prefix = (bit == 31) ? 0u : (mx & ~((2u << bit) - 1u));
+        for (; bit >= 0; bit -= 2) {
+            const int sh = max(bit - 1, 0);
+            const uint32_t step = (bit >= 1) ? 1u : 0u;  // a last single bit: c1 = c2 = c3 candidates collapse to one
+            const uint32_t c1 = prefix | (1u << sh), c2 = step ? (prefix | (2u << sh)) : 0xffffffffu,
+                           c3 = step ? (prefix | (3u << sh)) : 0xffffffffu;
+            uint32_t n1 = 0, n2 = 0, n3 = 0;
+            for (int i = lane; i < n; i += 32) {
+                const uint32_t o = K[i];
+                n1 += o >= c1;
+                n2 += o >= c2;
+                n3 += o >= c3;
+            }
+            n1 = __reduce_add_sync(kFull, n1);
+            n2 = __reduce_add_sync(kFull, n2);
+            n3 = __reduce_add_sync(kFull, n3);
+            if (step && (int)n3 >= k) prefix = c3;
+            else if (step && (int)n2 >= k) prefix = c2;
+            else if ((int)n1 >= k) prefix = c1;
+        }
+    }
+    if (lane == 0) {
+        const float kth = ord2f(prefix);
+        const float b = band != nullptr ? band[q] : 0.f;
+        atomicMax(tau + q, f2ord(kth - b) - 1u);
     }
 }
 
@@ -1158,6 +1236,10 @@ static int gemm_search_cg(const void* rows, int64_t n, size_t pitch_bytes, int d
     p.tiles_per_seg = (p.n_tiles + best_s - 1) / best_s;
     p.n_seg = (p.n_tiles + p.tiles_per_seg - 1) / p.tiles_per_seg;
     p.n_items = p.n_qt * p.n_seg;
+    p.tile_mul = 1;
+    p.tile_skip = 0;
+    p.n_lists = p.n_seg;
+    p.list_base = 0;
     const int grid = (int)std::min<long long>(grid_max, p.n_items) * cg;
 
     // pipeline depth from the shared-memory budget
@@ -1324,23 +1406,49 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     p.n_tiles = (int)((n + kTileN - 1) / kTileN);
     p.norms = norms;
     const int grid_max = num_sms / cg;
-    int best_s = 1;
-    double best_cost = 1e30;
-    const int max_s = std::max(1, std::min(p.n_tiles / 8, 4 * grid_max));
-    for (int s = 1; s <= max_s; ++s) {
-        const int tps = (p.n_tiles + s - 1) / s;
-        const int s_eff = (p.n_tiles + tps - 1) / tps;
-        const long long items = (long long)p.n_qt * s_eff;
-        const long long waves = (items + grid_max - 1) / grid_max;
-        const double cost = (double)waves * (tps + 6.0);
-        if (cost < best_cost * 0.995) {
-            best_cost = cost;
-            best_s = s_eff;
+    // segments: (query-tile groups x segments) a near multiple of the units that run at once, segments >= 8 tiles
+    auto plan = [&](int tiles, int* tps_out, int* nseg_out) {
+        int best_s = 1;
+        double best_cost = 1e30;
+        const int max_s = std::max(1, std::min(tiles / 8, 4 * grid_max));
+        for (int s = 1; s <= max_s; ++s) {
+            const int tps = (tiles + s - 1) / s;
+            const int s_eff = (tiles + tps - 1) / tps;
+            const long long items = (long long)p.n_qt * s_eff;
+            const long long waves = (items + grid_max - 1) / grid_max;
+            const double cost = (double)waves * (tps + 6.0);
+            if (cost < best_cost * 0.995) {
+                best_cost = cost;
+                best_s = s_eff;
+            }
         }
-    }
-    p.tiles_per_seg = (p.n_tiles + best_s - 1) / best_s;
-    p.n_seg = (p.n_tiles + p.tiles_per_seg - 1) / p.tiles_per_seg;
+        *tps_out = (tiles + best_s - 1) / best_s;
+        *nseg_out = (tiles + *tps_out - 1) / *tps_out;
+    };
+    // Threshold pre-pass (two launches of the same kernel): first every `sstride`-th corpus tile - a sample of the rows
+    // spread over the whole store - split into as many parts as there are idle units per query group; tau_union_kernel
+    // turns the parts' lists into one lower bound of the final k-th key per query; the main launch then covers the
+    // other tiles and every one of its work items starts from that bound.  Without it the items of the first wave start
+    // from -inf, admit k (1 + ln(rows / k)) keys each and keep the epilogue on its slow path for most chunks (measured at
+    // 10M x 1024, 4096 queries, k = 100: 11 of the 14 Mcycles the MMA warp waited for a free accumulator fell into
+    // each unit's first item).  Worth it from k = 32 and a corpus of >= 64 sample tiles per launch wave.
+    const int total_tiles = p.n_tiles;
+    int sstride = 32;
+    if (const char* e = std::getenv("B2_GEMM_SAMPLE")) sstride = atoi(e);  // 0 = single pass; else the sample stride (>= 2)
+    const bool two_pass = sstride >= 2 && k >= 32 && total_tiles >= 64 * sstride;
+    const int n_sample = two_pass ? (total_tiles + sstride - 1) / sstride : 0;
+    int tps_s = 0, nseg_s = 0, tps_m = 0, nseg_m = 0;
+    if (two_pass) plan(n_sample, &tps_s, &nseg_s);
+    plan(total_tiles - n_sample, &tps_m, &nseg_m);
+    p.n_lists = nseg_m + nseg_s;
+    // the main launch (when there is no pre-pass: the only one)
+    p.n_tiles = total_tiles - n_sample;
+    p.tiles_per_seg = tps_m;
+    p.n_seg = nseg_m;
     p.n_items = p.n_qt * p.n_seg;
+    p.tile_mul = 1;
+    p.tile_skip = two_pass ? sstride : 0;
+    p.list_base = 0;
     const int grid = (int)std::min<long long>(grid_max, p.n_items) * cg;
     p.num_stages = stages;
     p.corr_slots = 2;
@@ -1362,8 +1470,8 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     const size_t ax_bytes = al((size_t)2 * p.nq_pad * kbytes_x);
     const size_t qn_bytes = al((size_t)p.nq_pad * 4);
     const size_t fl_bytes = al((size_t)p.n_qt * 4) + 1024;  // + diagnostics counters
-    const size_t part_bytes = al((size_t)p.nq_pad * p.n_seg * p.list_len * 8);
-    const size_t cand_bytes = al((size_t)grid * kCandCap * kEpiThreads * 8);
+    const size_t part_bytes = al((size_t)p.nq_pad * p.n_lists * p.list_len * 8);
+    const size_t cand_bytes = al((size_t)grid_max * cg * kCandCap * kEpiThreads * 8);  // any of the launches below
     char* blk = nullptr;
     B2_CUDA_TRY(cudaMallocAsync(&blk, a_bytes + ax_bytes + 3 * qn_bytes + fl_bytes + part_bytes + cand_bytes, stream));
     char* cur = blk;
@@ -1409,14 +1517,53 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
         cudaEventCreate(&dbg_ev0);
         cudaEventRecord(dbg_ev0, stream);
     }
-    if (rc == B2_OK) {
+    auto launch_approx = [&](const GemmParams& gp, int g) {
         if (abf16)
-            rc = swb == 128 ? launch_gemm_cg<0, 1, 128>(tmA, tmB, p, grid, smem, stream, cg)
-                            : launch_gemm_cg<0, 1, 64>(tmA, tmB, p, grid, smem, stream, cg);
-        else
-            rc = swb == 128 ? launch_gemm_cg<2, 1, 128>(tmA, tmB, p, grid, smem, stream, cg)
-                            : launch_gemm_cg<2, 1, 64>(tmA, tmB, p, grid, smem, stream, cg);
+            return swb == 128 ? launch_gemm_cg<0, 1, 128>(tmA, tmB, gp, g, smem, stream, cg)
+                              : launch_gemm_cg<0, 1, 64>(tmA, tmB, gp, g, smem, stream, cg);
+        return swb == 128 ? launch_gemm_cg<2, 1, 128>(tmA, tmB, gp, g, smem, stream, cg)
+                          : launch_gemm_cg<2, 1, 64>(tmA, tmB, gp, g, smem, stream, cg);
+    };
+    if (rc == B2_OK && two_pass) {
+        GemmParams ps = p;
+        ps.n_tiles = n_sample;
+        ps.tiles_per_seg = tps_s;
+        ps.n_seg = nseg_s;
+        ps.n_items = ps.n_qt * ps.n_seg;
+        ps.tile_mul = sstride;
+        ps.tile_skip = 0;
+        ps.list_base = nseg_m;
+        ps.stats = nullptr;
+        rc = launch_approx(ps, (int)std::min<long long>(grid_max, ps.n_items) * cg);
+        if (rc == B2_OK) {
+            const size_t us = (size_t)kUnionWarps * nseg_s * p.list_len * 4;
+            static std::mutex umu;
+            static size_t uattr[64] = {0};
+            int dev = 0;
+            cudaGetDevice(&dev);
+            {
+                std::lock_guard<std::mutex> lk(umu);
+                if (us > 48 * 1024 && us > uattr[dev & 63]) {
+                    if (cudaFuncSetAttribute(tau_union_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)us) != cudaSuccess) {
+                        cudaGetLastError();
+                        set_error("tensor-core search: shared memory for the threshold union");
+                        rc = B2_ERR_CUDA;
+                    }
+                    uattr[dev & 63] = us;
+                }
+            }
+            if (rc == B2_OK) {
+                tau_union_kernel<<<(unsigned)((nq + kUnionWarps - 1) / kUnionWarps), kUnionWarps * 32, us, stream>>>(
+                    p.partial, (int)nq, p.n_lists, nseg_m, nseg_s, p.list_len, k, band, p.tau);
+                B2_COUNT_LAUNCH();
+                if (cudaGetLastError() != cudaSuccess) {
+                    set_error("tensor-core search: tau_union_kernel launch failed");
+                    rc = B2_ERR_CUDA;
+                }
+            }
+        }
     }
+    if (rc == B2_OK) rc = launch_approx(p, grid);
     static const bool debug = std::getenv("B2_GEMM_DEBUG") != nullptr;
     cudaEvent_t dbg_ev[4] = {nullptr, nullptr, nullptr, nullptr};
     if (debug) {
@@ -1431,8 +1578,8 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
         cudaMemcpy(bd.data(), band, bd.size() * 4, cudaMemcpyDeviceToHost);
         int nf = 0;
         for (uint32_t f : fl) nf += f != 0u;
-        std::fprintf(stderr, "[b2 gemm refine] k=%d list_len=%d n_seg=%d n_qt=%d flagged=%d band[0]=%g\n", k, p.list_len,
-                     p.n_seg, p.n_qt, nf, bd.empty() ? 0.0 : (double)bd[0]);
+        std::fprintf(stderr, "[b2 gemm refine] k=%d list_len=%d n_seg=%d (+%d pre-pass parts, stride %d) n_qt=%d flagged=%d band[0]=%g\n", k, p.list_len,
+                     p.n_seg, nseg_s, two_pass ? sstride : 0, p.n_qt, nf, bd.empty() ? 0.0 : (double)bd[0]);
         unsigned long long st[9] = {0};
         cudaMemcpy(st, p.stats, sizeof(st), cudaMemcpyDeviceToHost);
         const double units = (double)(grid / cg), lanes = (double)p.nq_pad * p.n_seg;
@@ -1448,17 +1595,27 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
         px.refine = 0;
         px.only_flagged = 1;
         px.stats = nullptr;
+        // every corpus tile, spread over all n_lists list slots (slots beyond the last tile get empty lists), so that
+        // the lists of a redone query group are replaced completely
+        px.n_tiles = total_tiles;
+        px.tile_mul = 1;
+        px.tile_skip = 0;
+        px.list_base = 0;
+        px.n_seg = p.n_lists;
+        px.tiles_per_seg = (total_tiles + p.n_lists - 1) / p.n_lists;
+        px.n_items = px.n_qt * px.n_seg;
         px.kstages = (int)(kbytes_x / swb_x);
         px.num_stages = stages_x;
         px.corr_slots = corr_x;
         px.rcap = rcap_x;
         px.mixed = bf16 ? 0 : 1;
-        rc = bf16 ? launch_gemm_cg<0, 2, 64>(tmAx, tmBx, px, grid, smem_x, stream, cg)
-                  : launch_gemm_cg<1, 2, 64>(tmAx, tmBx, px, grid, smem_x, stream, cg);
+        const int grid_x = (int)std::min<long long>(grid_max, px.n_items) * cg;
+        rc = bf16 ? launch_gemm_cg<0, 2, 64>(tmAx, tmBx, px, grid_x, smem_x, stream, cg)
+                  : launch_gemm_cg<1, 2, 64>(tmAx, tmBx, px, grid_x, smem_x, stream, cg);
     }
     if (debug) cudaEventRecord(dbg_ev[2], stream);
     if (rc == B2_OK)
-        rc = merge_rescore(p.partial, (int)nq, p.n_seg, p.list_len, k, metric, D, I, (size_t)k, stream,
+        rc = merge_rescore(p.partial, (int)nq, p.n_lists, p.list_len, k, metric, D, I, (size_t)k, stream,
                            metric == B2_METRIC_L2 ? qn : nullptr, q_dev, d, rows, pitch_bytes, dtype, norms, band, push);
     if (debug) {
         cudaEventRecord(dbg_ev[3], stream);
