@@ -206,98 +206,202 @@ def uses_tensor_path(batch, k, rows):
     return batch >= 20 and k <= 128 and rows >= 4096 and batch > scan_tc_max_queries(k)
 
 
-def ncu_traffic():
-    """dram bytes per scan launch from the committed ncu --set full capture, if one exists."""
+def ncu_traffic(kernel):
+    """(dram bytes per launch, where the figure comes from) for the scan kernel of the default config.  bench.py cannot
+    run ncu on itself: the figure is the one of the committed `ncu --set full` capture of this same command, and is
+    reported only with its source beside it (None when no capture of this kernel exists)."""
     p = os.path.join(ROOT, "profiles", "scan_traffic.json")
     try:
-        return json.load(open(p)).get("dram_bytes_per_launch")
+        j = json.load(open(p))
+        if not str(j.get("kernel", "")).startswith(kernel):
+            return None, None
+        return j.get("dram_bytes_per_launch"), "profiles/scan_traffic.json <- " + str(j.get("source"))
     except Exception:
-        return None
+        return None, None
 
 
 # ------------------------------------------------------------------------------------------ CPU legs
-def cpu_scan_timing(a, budget_s, max_passes, fixed_rows=None):
-    """Time oracle search_seq (faiss threading: OpenMP over queries only) on a row sample.
-    Returns dict(value=QPS scaled to a.rows, cores, sample, t_pass)."""
+def host_mem_available_gb():
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable:"):
+                return int(line.split()[1]) / (1 << 20)
+    except Exception:
+        pass
+    return 0.0
+
+
+def _oracle_metric(a, flat):
+    return flat.METRIC_IP if a.metric == "ip" else flat.METRIC_L2
+
+
+def _oracle_queries(a, flat, n, row0=0):
+    q = flat.synth(row0, n, a.dim, QUERY_SEED)
+    if a.normalize:
+        flat.normalize_L2(q)
+    return q
+
+
+def _oracle_rows(a, flat, row0, n):
+    x = flat.synth(row0, n, a.dim, CORPUS_SEED)
+    if a.normalize:
+        flat.normalize_L2(x)
+    if a.dtype == "bfloat16":
+        flat.round_bf16_inplace(x)  # what a bf16 row store holds
+    return x
+
+
+def _oracle_search(a, flat, x, q):
+    """faiss's dispatch: the sequential routine (OpenMP over queries only) below 20 queries, the BLAS routine above."""
+    if q.shape[0] < flat.BLAS_THRESHOLD:
+        D, I, used = flat.search_seq(x, q, a.k, _oracle_metric(a, flat))
+        return D, I, int(used)
+    D, I = flat.search_blas(x, q, a.k, _oracle_metric(a, flat))
+    return D, I, int(flat.lib().b2o_max_threads())
+
+
+def cpu_full_pass(a, block=1_000_000):
+    """The oracle over ALL rows of the workload for ONE batch of queries, streamed in blocks (the rows are generated
+    block by block, untimed; only the scans are timed).  Returns (cpu_baseline dict, D, I): the timed CPU baseline
+    and, from the same pass, the oracle's answer for the batch, which the caller checks the GPU results against."""
     from oracle import flat
 
-    rows = fixed_rows or min(a.cpu_sample_rows, a.rows)
-    x = flat.synth(0, rows, a.dim, flat.CORPUS_SEED)
-    flat.normalize_L2(x)
-    q = flat.synth(0, a.batch, a.dim, flat.QUERY_SEED)
-    flat.normalize_L2(q)
-    flat.search_seq(x[: min(rows, 20000)], q, a.k, flat.METRIC_IP)  # warm the library
+    q = _oracle_queries(a, flat, a.batch)
+    st = flat.StreamingSearch(q, a.k, _oracle_metric(a, flat))
+    t_scan = 0.0
+    for r0 in range(0, a.rows, block):
+        x = _oracle_rows(a, flat, r0, min(block, a.rows - r0))
+        t0 = time.perf_counter()
+        st.feed(x, r0)
+        t_scan += time.perf_counter() - t0
+    D, I = st.result()
+    cores = min(a.batch, int(flat.lib().b2o_max_threads()))
+    cpu = {"value": a.batch / t_scan, "unit": UNIT, "cores": cores, "kind": "port",
+           "sample": f"all {a.rows} rows x {a.dim}, batch {a.batch}, k={a.k}, one pass in {t_scan:.2f} s of scan time "
+                     f"(rows generated block by block outside the timing); C restatement of faiss IndexFlat "
+                     f"(oracle/flat_oracle.c), OpenMP over queries only as in faiss below 20 queries; host has "
+                     f"{os.cpu_count()} logical cores"}
+    return cpu, D, I
+
+
+def cpu_sample_timing(a, budget_s):
+    """The oracle on a bounded row sample, scaled linearly in rows (a flat scan is linear in rows): the CPU baseline of
+    the configurations whose full pass would take minutes (large batches: faiss's BLAS path on all cores)."""
+    from oracle import flat
+
+    q = _oracle_queries(a, flat, a.batch)
+    rows = min(a.cpu_sample_rows, a.rows)
+    if a.batch >= flat.BLAS_THRESHOLD:
+        rows = min(rows, max(20_000, int(2.0e10 * budget_s / (a.batch * a.dim))))  # ~20 GFMA/s per pass as a first guess
+    x = _oracle_rows(a, flat, 0, rows)
+    _oracle_search(a, flat, x[: min(rows, 20000)], q)  # warm the library
     times, used = [], 1
     t_begin = time.time()
-    while len(times) < max_passes and (time.time() - t_begin < budget_s or not times):
+    while len(times) < 5 and (time.time() - t_begin < budget_s or not times):
         t0 = time.perf_counter()
-        _, _, used = flat.search_seq(x, q, a.k, flat.METRIC_IP)
+        _, _, used = _oracle_search(a, flat, x, q)
         times.append(time.perf_counter() - t0)
     t_pass = statistics.median(times)
     scale = a.rows / rows
-    return {"value": a.batch / (t_pass * scale), "unit": UNIT, "cores": int(used), "kind": "port",
-            "sample": f"{rows} of {a.rows} rows x {a.dim} fp32, batch {a.batch}, k={a.k}, {len(times)} passes, "
-                      f"median pass {t_pass * 1e3:.1f} ms, scaled x{scale:g} (flat scan is linear in rows); "
-                      f"OpenMP over queries only as in faiss below 20 queries; host has {os.cpu_count()} logical cores",
-            "t_pass": t_pass, "rows": rows, "host_cores": os.cpu_count()}
+    path = ("sequential routine, OpenMP over queries only" if a.batch < flat.BLAS_THRESHOLD
+            else "BLAS routine (numpy sgemm blocks + top-k), all cores")
+    out = {"value": a.batch / (t_pass * scale), "unit": UNIT, "cores": min(int(used), max(a.batch, 1)) if a.batch < flat.BLAS_THRESHOLD else int(used),
+           "kind": "port",
+           "sample": f"{rows} of {a.rows} rows x {a.dim}, batch {a.batch}, k={a.k}, {len(times)} passes, median pass "
+                     f"{t_pass * 1e3:.1f} ms, scaled x{scale:g} (a flat scan is linear in rows); faiss's {path}; host has "
+                     f"{os.cpu_count()} logical cores"}
+    if a.batch < flat.BLAS_THRESHOLD:
+        # not faiss behaviour: the same scan with the ROWS split over all cores, as a fairer upper bound for small batches
+        t0 = time.perf_counter()
+        _, _, used_rp = flat.search_seq(x, q, a.k, _oracle_metric(a, flat), rowpar=True)
+        t_rp = time.perf_counter() - t0
+        out["all_cores_row_parallel"] = {"value": a.batch / (t_rp * scale), "unit": UNIT, "cores": int(used_rp),
+                                         "note": "not what faiss does below 20 queries; the same sample, rows split over the cores"}
+    return out
 
 
 def run_reference(a):
     """--impl reference: the reference's CPU path for this workload.  faiss-cpu itself cannot be installed
-    (BASELINE.md section 2), so this is the oracle's restatement of it, timed alone on the host cores."""
+    (BASELINE.md section 2), so this is the oracle's restatement of it, timed alone on the host cores with faiss's own
+    threading.  Every step scans ALL rows when the corpus fits host memory and (warmup + steps) passes fit in about
+    two minutes; otherwise each step scans a bounded sample and the step time is scaled linearly in rows (stated)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from oracle import flat
 
     flat.build()
-    # size the sample so that (warmup + steps) passes finish in about two minutes
-    probe = cpu_scan_timing(a, budget_s=1.0, max_passes=2, fixed_rows=min(100_000, a.rows))
-    per_row = probe["t_pass"] / probe["rows"]
     total_passes = a.steps + a.warmup
-    rows = int(min(a.cpu_sample_rows, a.rows, max(50_000, 120.0 / max(total_passes, 1) / per_row)))
-    x = flat.synth(0, rows, a.dim, flat.CORPUS_SEED)
-    flat.normalize_L2(x)
-    qs = flat.synth(0, a.batch * total_passes, a.dim, flat.QUERY_SEED)
-    flat.normalize_L2(qs)
+    # cost of one pass per row, from a small probe
+    probe_rows = min(50_000, a.rows)
+    qp = _oracle_queries(a, flat, a.batch)
+    xp = _oracle_rows(a, flat, 0, probe_rows)
+    _oracle_search(a, flat, xp[:5000], qp)
+    t0 = time.perf_counter()
+    _oracle_search(a, flat, xp, qp)
+    per_row = (time.perf_counter() - t0) / probe_rows
+    need_gb = a.rows * a.dim * 4 / (1 << 30)
+    budget = 120.0
+    full = per_row * a.rows * total_passes <= budget and host_mem_available_gb() >= need_gb * 1.1 + 4
+    rows = a.rows if full else int(min(a.rows, max(20_000, budget / max(total_passes, 1) / per_row)))
+    del xp
+    x = np_rows_blockwise(a, flat, rows)
+    qs = _oracle_queries(a, flat, a.batch * total_passes)
     used = 1
     for i in range(a.warmup):
-        flat.search_seq(x, qs[i * a.batch:(i + 1) * a.batch], a.k, flat.METRIC_IP)
+        _oracle_search(a, flat, x, qs[i * a.batch:(i + 1) * a.batch])
     t0 = time.perf_counter()
     for i in range(a.warmup, total_passes):
-        _, _, used = flat.search_seq(x, qs[i * a.batch:(i + 1) * a.batch], a.k, flat.METRIC_IP)
+        _, _, used = _oracle_search(a, flat, x, qs[i * a.batch:(i + 1) * a.batch])
     dt = time.perf_counter() - t0
     scale = a.rows / rows
     t_step = dt / a.steps * scale
     value = a.batch / t_step
-    sample = (f"each step scans {rows} of {a.rows} rows (x{scale:g} linear scaling), batch {a.batch}, k={a.k}; "
-              f"C restatement of faiss IndexFlat (oracle/flat_oracle.c), OpenMP over queries only; "
+    path = ("sequential routine, OpenMP over queries only" if a.batch < flat.BLAS_THRESHOLD
+            else "BLAS routine (numpy sgemm blocks + top-k), all cores")
+    cores = min(int(used), a.batch) if a.batch < flat.BLAS_THRESHOLD else int(used)
+    sample = ((f"each step scans all {a.rows} rows" if full else
+               f"each step scans {rows} of {a.rows} rows and the step time is scaled x{scale:g} (linear in rows)") +
+              f", batch {a.batch}, k={a.k}; C restatement of faiss IndexFlat (oracle/flat_oracle.c), faiss's {path}; "
               f"host has {os.cpu_count()} logical cores")
     line = {"impl": "reference", "metric": metric_name(a), "value": value, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
-            "warmup": a.warmup, "ms_per_step": t_step * 1e3, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(a), "rows": a.rows, "dim": a.dim, "batch": a.batch, "k": a.k},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": int(used), "kind": "port", "sample": sample},
+            "warmup": a.warmup, "ms_per_step": t_step * 1e3, "higher_is_better": True,
+            "scaling": "weak" if (a.config == "cfg4" and a.gpus == 1) else "strong",
+            "vs_baseline": None, "dtype": "f32" if a.dtype == "float32" else "bf16 rows, f32 accumulate", "data": "synthetic",
+            "config": {"workload": workload_name(a), "rows": a.rows, "dim": a.dim, "batch": a.batch, "k": a.k,
+                       "rows_scanned_per_step": rows},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
 
+def np_rows_blockwise(a, flat, rows, block=1_000_000):
+    """The first `rows` rows of the workload's corpus as one host array, generated block by block."""
+    import numpy as np
+
+    x = np.empty((rows, a.dim), dtype=np.float32)
+    for r0 in range(0, rows, block):
+        m = min(block, rows - r0)
+        x[r0:r0 + m] = _oracle_rows(a, flat, r0, m)
+    return x
+
+
 # ------------------------------------------------------------------------------------------ GPU arm
 def build_shard(a, device, lo, hi, dtype=None):
-    """Rows [lo, hi) of the synthetic corpus, generated on the device and ingested with the fused normalise."""
+    """Rows [lo, hi) of the synthetic corpus, generated on the device and ingested (with the fused normalise for the
+    inner-product configs)."""
     import torch
 
-    from nv_genai_b200 import IndexFlatIP, synth_fill
-    from oracle import flat  # seeds only
+    from nv_genai_b200 import IndexFlatIP, IndexFlatL2, synth_fill
 
-    idx = IndexFlatIP(a.dim, dtype=dtype or a.dtype, device=device)
+    idx = (IndexFlatIP if a.metric == "ip" else IndexFlatL2)(a.dim, dtype=dtype or a.dtype, device=device)
     chunk = min(1_000_000, max(hi - lo, 1))
     buf = torch.empty((chunk, a.dim), dtype=torch.float32, device=f"cuda:{device}")
     for r0 in range(lo, hi, chunk):
         m = min(chunk, hi - r0)
-        synth_fill(buf[:m], r0, flat.CORPUS_SEED)
-        idx.add(buf[:m], normalize=True)
+        synth_fill(buf[:m], r0, CORPUS_SEED)
+        idx.add(buf[:m], normalize=a.normalize)
     torch.cuda.synchronize(device)
     del buf
     torch.cuda.empty_cache()
@@ -310,14 +414,13 @@ def cfg5(a, device, idx, peak, peak_src):
     import torch
 
     from nv_genai_b200 import IndexFlatIP, synth_fill
-    from oracle import flat  # seeds only
 
     rows = min(1_000_000, a.rows)
     out = {}
     for dtype in ("float32", "bfloat16"):
         tmp = IndexFlatIP(a.dim, dtype=dtype, device=device)
         buf = torch.empty((rows, a.dim), dtype=torch.float32, device=f"cuda:{device}")
-        synth_fill(buf, 0, flat.CORPUS_SEED)
+        synth_fill(buf, 0, CORPUS_SEED)
         reps = 5
         for _ in range(reps):  # grow the row store to its final size first: mapping memory is host work, not the kernel
             tmp.add(buf, normalize=True)
@@ -375,15 +478,14 @@ def cfg1(a, device):
     import torch
 
     from nv_genai_b200 import IndexFlatL2, synth_fill
-    from oracle import flat  # seeds only
 
     n = 100_000
     idx = IndexFlatL2(a.dim, device=device)
     buf = torch.empty((n, a.dim), dtype=torch.float32, device=f"cuda:{device}")
-    synth_fill(buf, 0, flat.CORPUS_SEED)
+    synth_fill(buf, 0, CORPUS_SEED)
     idx.add(buf)
     q = torch.empty((256, a.dim), dtype=torch.float32, device=f"cuda:{device}")
-    synth_fill(q, 0, flat.QUERY_SEED)
+    synth_fill(q, 0, QUERY_SEED)
     qh = q.cpu().numpy()
     for i in range(10):
         idx.search(q[i:i + 1], 4)
@@ -412,12 +514,48 @@ def make_queries(a, device, count, batch):
     import torch
 
     from nv_genai_b200 import normalize_L2, synth_fill
-    from oracle import flat  # seeds only
 
     q = torch.empty((count * batch, a.dim), dtype=torch.float32, device=f"cuda:{device}")
-    synth_fill(q, 0, flat.QUERY_SEED)
-    normalize_L2(q)
+    synth_fill(q, 0, QUERY_SEED)
+    if a.normalize:
+        normalize_L2(q)
     return q.view(count, batch, a.dim)
+
+
+def compare_topk(Dg, Ig, Dr, Ir, rtol=1e-5, atol=1e-6):
+    """The parity rule of tests/parity.py in short: scores within rtol position by position; ids equal except inside
+    runs of scores that tie within the tolerance.  Returns "ok" or what differs."""
+    import numpy as np
+
+    Dg, Ig, Dr, Ir = (np.asarray(v) for v in (Dg, Ig, Dr, Ir))
+    if Dg.shape != Dr.shape or Ig.shape != Ir.shape:
+        return f"shape {Dg.shape} vs {Dr.shape}"
+    tol = atol + rtol * np.abs(Dr.astype(np.float64))
+    if not np.all(np.abs(Dg.astype(np.float64) - Dr.astype(np.float64)) <= tol):
+        return "scores differ beyond 1e-5 relative"
+    for r in range(Ig.shape[0]):
+        for j in np.nonzero(Ig[r] != Ir[r])[0]:
+            pos = np.nonzero(Ir[r] == Ig[r][j])[0]
+            ref = Dr[r][pos[0]] if len(pos) else Dr[r][-1]  # an id from outside must tie the k-th score
+            if abs(float(ref) - float(Dr[r][j])) > atol + 10 * rtol * abs(float(Dr[r][j])):
+                return f"query {r} position {j}: id {int(Ig[r][j])} where the oracle has {int(Ir[r][j])} and the scores do not tie"
+    return "ok"
+
+
+def planted_ids(rows, world):
+    """Eight global ids whose rows are searched for themselves: the ends, the middle and the shard boundaries."""
+    from nv_genai_b200.sharded import shard_bounds
+
+    ids = [0, 1, rows // 2 - 1, rows // 2, rows - 1]
+    for r in range(1, world):
+        lo, _ = shard_bounds(rows, world, r)
+        ids += [lo - 1, lo]
+    ids += [rows // 3, (2 * rows) // 3, rows // 5]
+    out = []
+    for i in ids:
+        if 0 <= i < rows and i not in out:
+            out.append(i)
+    return out[:8]
 
 
 def run_b200(a):
@@ -534,6 +672,7 @@ def run_b200(a):
         clocks = sampler.summary(t0, t1) if sampler is not None else None
         pitch_c = ((a.dim * (2 if dtype == "bfloat16" else 4) + 511) // 512) * 512
         k_avg_ms = k_ms / max(k_n, 1)
+        k_step_ms = k_ms / steps  # all launches of the profiled kernel within one step
         if tensor:
             fp32_rows = dtype != "bfloat16"
             flops = 2.0 * batch * (hi - lo) * a.dim  # algorithmic: one product per (query, row, dim)
@@ -545,27 +684,32 @@ def run_b200(a):
             shadow = fp32_rows and refine and "B2_NO_SHADOW" not in os.environ and "B2_NO_VMM" not in os.environ
             tpeak, tsrc = measured_tensor_peak(fp32_rows and not shadow)
             products = 1 if refine else (3 if fp32_rows else 2)
-            achieved = flops / (k_avg_ms * 1e-3) / 1e12 if k_n else None
+            achieved = flops / (k_step_ms * 1e-3) / 1e12 if k_n else None
             roof = {"bound": "tensor", "achieved": achieved, "peak": tpeak, "unit": "TFLOP/s",
                     "frac": (achieved / tpeak) if achieved else None, "traffic": None,
                     "kernel": "gemm_topk_kernel (%s)" % (("approximate pass of filter-and-refine" +
                                                           (", bf16 shadow of the fp32 rows" if shadow else "")) if refine else "all-exact"),
-                    "algorithmic_flops_per_launch": flops,
+                    "algorithmic_flops_per_step": flops,
+                    "launches_per_step": k_n / steps,
+                    "launch_note": "a search launches the kernel twice when k >= 32: a threshold pre-pass over every 32nd corpus tile, "
+                                   "then the main pass over the other tiles; achieved = algorithmic flop of the step / summed launch time",
                     "mma_products_per_score": products,
                     "issued_mma_tflops": (achieved * products * (-(-batch // 128) * 128) / batch) if achieved else None,
-                    "avg_launch_ms": k_avg_ms, "launches_timed": k_n, "peak_source": tsrc,
-                    "kernel_share_of_step": (k_avg_ms * k_n / ms) if k_n else None}
+                    "kernel_ms_per_step": k_step_ms, "launches_timed": k_n, "peak_source": tsrc,
+                    "kernel_share_of_step": (k_ms / ms) if k_n else None}
         else:
             shard_bytes = (hi - lo) * pitch_c
             achieved = shard_bytes / (k_avg_ms * 1e-3) / 1e9 if k_n else None
             per_step = 1 if batch <= max(16, scan_tc_max_queries(k)) else -(-batch // 16)  # scan passes per step
             roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": (achieved / peak) if achieved else None,
-                    "traffic": ncu_traffic() if (batch == 1 and dtype == "float32" and world == 1) else None,
+                    "traffic": None,
                     "kernel": scan_kernel_name(batch, k, hi - lo, a.dim, dtype),
                     "algorithmic_bytes_per_launch": shard_bytes,
                     "avg_launch_ms": k_avg_ms, "launches_timed": k_n, "peak_source": peak_src,
                     "scan_share_of_step": (k_avg_ms * k_n / ms) if k_n else None, "scan_passes_per_step": per_step}
+            if batch == 1 and dtype == "float32" and world == 1 and a.rows == 10_000_000 and a.metric == "ip":
+                roof["traffic"], roof["traffic_source"] = ncu_traffic(roof["kernel"])
         return {
             "batch": batch, "k": k, "dtype": dtype, "steps": steps, "ms_per_step": ms / steps,
             "value": batch * steps / (ms * 1e-3),
@@ -579,11 +723,11 @@ def run_b200(a):
     if a.extra:
         extra = {}
         keep = ("batch", "k", "dtype", "steps", "value", "ms_per_step", "e2e_value", "roofline")
-        if a.batch != 16:
+        if a.batch != 16 and a.k == 10:
             e = one_config(16)  # the other half of BASELINE configs[1]
             extra["batch16"] = {kk: e[kk] for kk in keep}
-        if a.dtype == "float32" and a.batch != 4096:
-            # BASELINE configs[2]: batch 4096, k = 100, fp32 rows (3xTF32) and bf16 rows, tensor-core path
+        if a.dtype == "float32" and a.batch != 4096 and a.metric == "ip":
+            # BASELINE configs[2]: batch 4096, k = 100, fp32 rows and bf16 rows, tensor-core path
             e = one_config(4096, k=100, steps=max(3, min(a.steps, 5)))
             extra["cfg3_fp32_batch4096_k100"] = {kk: e[kk] for kk in keep}
             idx16 = build_shard(a, local, lo, hi, dtype="bfloat16")
@@ -593,28 +737,71 @@ def run_b200(a):
             extra["bf16_batch1_k10"] = {kk: e[kk] for kk in keep}
             del idx16
             torch.cuda.empty_cache()
-        if world == 1:
+        if world == 1 and a.metric == "ip":
             extra["cfg5_ingest_and_mmr"] = cfg5(a, local, idx, peak, peak_src)
             extra["cfg1_100k_l2_k4_latency"] = cfg1(a, local)
+    elif a.config == "cfg5" and world == 1:
+        extra = {"cfg5_ingest_and_mmr": cfg5(a, local, idx, peak, peak_src)}
     if sampler is not None:
         sampler.stop()
 
-    cpu = None
-    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+    # ---- correctness of what was timed (outside the timed region; every N): planted rows must find themselves, and
+    # the first query batch must equal the oracle's answer over all rows.  The oracle pass is also the CPU baseline.
+    check, cpu = None, None
+    if not a.no_check:
+        ids = planted_ids(a.rows, world)
+        pq = torch.empty((len(ids), a.dim), dtype=torch.float32, device=f"cuda:{local}")
+        from nv_genai_b200 import normalize_L2, synth_fill
+
+        for j, gid in enumerate(ids):
+            synth_fill(pq[j:j + 1], gid, CORPUS_SEED)
+        if a.normalize:
+            normalize_L2(pq)
+        Dp, Ip = (sh.search(pq, a.k, replicated=True) if sh is not None else idx.search(pq, a.k))
+        q0 = make_queries(a, local, 1, a.batch)[0]
+        nchk = a.batch if a.batch < 20 else 4  # large batches: the first four queries of the same batch
+        D0, I0 = (sh.search(q0, a.k, replicated=True) if sh is not None else idx.search(q0, a.k))
+        torch.cuda.synchronize()
+        if rank == 0:
+            Ip_h, Dp_h = Ip.cpu().numpy(), Dp.cpu().numpy()
+            best = 1.0 if a.metric == "ip" else 0.0
+            tol = 1e-2 if a.dtype == "bfloat16" else 1e-4
+            ok = bool((Ip_h[:, 0] == ids).all()) and (not a.normalize or bool((abs(Dp_h[:, 0] - best) <= tol).all()))
+            check = {"planted": "ok" if ok else f"FAILED: ids {Ip_h[:, 0].tolist()} for planted rows {ids}",
+                     "planted_ids": ids}
+    if rank == 0 and not a.no_cpu_baseline:
         from oracle import flat
 
         flat.build()
-        cpu = cpu_scan_timing(a, budget_s=12.0, max_passes=12)
-        for key in ("t_pass", "rows", "host_cores"):
-            cpu.pop(key, None)
+        full_cost_s = a.rows / 1e6 * (1.8 + 0.35 * min(a.batch, 20) / max(1, min(min(a.batch, 20), os.cpu_count() or 1)))
+        if a.no_check or full_cost_s > 60.0:
+            if check is not None:
+                check["oracle_query"] = f"skipped: a full oracle pass over {a.rows} rows would take ~{full_cost_s:.0f} s"
+        else:
+            sub = argparse.Namespace(**vars(a))
+            sub.batch = nchk
+            cpu_full, Dr, Ir = cpu_full_pass(sub)
+            check["oracle_query"] = compare_topk(D0[:nchk].cpu().numpy(), I0[:nchk].cpu().numpy(), Dr, Ir)
+            check["oracle_queries_checked"] = nchk
+            if a.batch < 20 and world == 1:
+                cpu = cpu_full
+        if world == 1 and cpu is None:
+            cpu = cpu_sample_timing(a, budget_s=12.0)
+        elif world == 1 and a.batch < 20:
+            rp = cpu_sample_timing(a, budget_s=2.0)
+            if "all_cores_row_parallel" in rp:
+                cpu["all_cores_row_parallel"] = rp["all_cores_row_parallel"]
+                cpu["all_cores_row_parallel"]["sample"] = rp["sample"]
 
     if rank == 0:
+        weak = a.config == "cfg4" and world == 1
         line = {
             "metric": metric_name(a), "value": main["value"], "unit": UNIT, "n_gpus": world, "steps": a.steps,
-            "warmup": a.warmup, "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": "strong",
+            "warmup": a.warmup, "ms_per_step": main["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak" if weak else "strong",
             "vs_baseline": None, "dtype": "f32" if a.dtype == "float32" else "bf16 rows, f32 accumulate",
             "data": "synthetic",
-            "config": {"workload": workload_name(a), "rows": a.rows, "dim": a.dim, "batch": a.batch, "k": a.k,
+            "config": {"workload": workload_name(a), "name": a.config, "rows": a.rows, "dim": a.dim, "batch": a.batch, "k": a.k,
                        "rows_per_gpu": hi - lo, "partitioning": f"row-sharded x{world}" if world > 1 else "single GPU",
                        "l2_note": "inputs larger than L2: each step streams the whole row store "
                                   f"({(hi - lo) * pitch / 1e9:.2f} GB per GPU) against a 126 MB L2"},
@@ -622,13 +809,39 @@ def run_b200(a):
                     "d2h_bytes_per_step": main["d2h"], "ms_per_step": main["e2e_ms_per_step"]},
             "gpu_launches": main["launches"], "clocks": main["clocks"], "roofline": main["roofline"],
         }
+        if check is not None:
+            line["check"] = check
         if cpu is not None:
             line["cpu_baseline"] = cpu
+        if a.config == "cfg4":
+            line["cfg4_efficiency"] = cfg4_efficiency(world, main["value"], main["ms_per_step"])
         if extra is not None:
             line["extra"] = extra
         print(json.dumps(line), flush=True)
     if dist is not None:
+        dist.barrier()
         dist.destroy_process_group()
+
+
+def cfg4_efficiency(world, qps, ms):
+    """(i) strong scaling against the smallest feasible point, QPS(G) / (QPS(2) G / 2); (ii) weak scaling,
+    t1(12.5M rows on one GPU) / t8(100M rows on eight).  The other points come from the lines of earlier runs kept under
+    profiles/r02_bench_cfg4_n<N>.json (this run's own line is what the caller saves there)."""
+    out = {"definition_i": None, "definition_ii": None}
+    def load(n):
+        try:
+            return json.load(open(os.path.join(ROOT, "profiles", f"r02_bench_cfg4_n{n}.json")))
+        except Exception:
+            return None
+    two, one = load(2), load(1)
+    if world >= 2:
+        q2 = qps if world == 2 else (two or {}).get("value")
+        if q2:
+            out["definition_i"] = {"eff": qps / (q2 * world / 2), "qps_2gpu": q2, "formula": "QPS(G) / (QPS(2) * G / 2)"}
+    if world == 8 and one:
+        out["definition_ii"] = {"eff": one["ms_per_step"] / ms, "t1_ms_12.5M_rows": one["ms_per_step"], "t8_ms": ms,
+                                "formula": "t1(12.5M rows, 1 GPU) / t8(100M rows, 8 GPUs)"}
+    return out
 
 
 def main():

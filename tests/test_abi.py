@@ -76,3 +76,18 @@ def test_product_package_never_imports_the_oracle():
                 text = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", text, re.M), f
                 assert "flat_oracle" not in text.replace("oracle/flat_oracle.c b2o_synth_fill", ""), f
+
+
+def test_bench_and_oracle_use_the_same_synthetic_streams():
+    """bench.py keeps its own copy of the two seeds (its GPU arm does not import the oracle)."""
+    import importlib.util
+    import os
+
+    from oracle import flat
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("_bench", os.path.join(root, "bench.py"))
+    b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(b)
+    assert b.CORPUS_SEED == flat.CORPUS_SEED and b.QUERY_SEED == flat.QUERY_SEED
+    assert set(b.CONFIGS) >= {"cfg1", "cfg2", "cfg2b16", "cfg3", "cfg3bf16", "cfg4", "cfg5"}
