@@ -1405,6 +1405,14 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     p.n_qt = p.nq_pad / (kTileM * cg);
     p.n_tiles = (int)((n + kTileN - 1) / kTileN);
     p.norms = norms;
+    // Room for the in-band candidates of a segment beyond its k best.  Their number grows with k (about
+    // k * z * band / sigma for scores with a Gaussian tail: ~0.4 k on 1024-d unit vectors with bf16 queries); a
+    // segment that overflows the list is flagged and redone by the exact fix-up launch, so this is a speed knob only.
+    int slack = std::max(48, 32 + 5 * k / 4);
+    if (approx != nullptr) slack = std::max(64, 32 + 3 * k);  // the band also covers the rows' bf16 rounding: ~2.3x wider
+    if (const char* e = std::getenv("B2_GEMM_LIST_SLACK")) slack = std::max(8, std::min(1024 - k - 8, atoi(e)));
+    p.list_len = ((k + slack) + 7) / 8 * 8;
+
     const int grid_max = num_sms / cg;
     // segments: (query-tile groups x segments) a near multiple of the units that run at once, segments >= 8 tiles
     auto plan = [&](int tiles, int* tps_out, int* nseg_out) {
@@ -1440,14 +1448,19 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     int tps_s = 0, nseg_s = 0, tps_m = 0, nseg_m = 0;
     if (two_pass) plan(n_sample, &tps_s, &nseg_s);
     plan(total_tiles - n_sample, &tps_m, &nseg_m);
-    p.n_lists = nseg_m + nseg_s;
+    // merge_rescore's fast kernel holds all candidates of a query in registers (<= 12288): when the pre-pass lists do
+    // not fit beside the main ones, the main launch covers the sample tiles again (3 % more products) and the pre-pass
+    // lists only feed the threshold union
+    const bool keep_sample_lists = two_pass && (size_t)(nseg_m + nseg_s) * p.list_len <= 12288;
+    if (two_pass && !keep_sample_lists) plan(total_tiles, &tps_m, &nseg_m);
+    p.n_lists = keep_sample_lists ? nseg_m + nseg_s : nseg_m;  // what merge_rescore reads
     // the main launch (when there is no pre-pass: the only one)
-    p.n_tiles = total_tiles - n_sample;
+    p.n_tiles = keep_sample_lists ? total_tiles - n_sample : total_tiles;
     p.tiles_per_seg = tps_m;
     p.n_seg = nseg_m;
     p.n_items = p.n_qt * p.n_seg;
     p.tile_mul = 1;
-    p.tile_skip = two_pass ? sstride : 0;
+    p.tile_skip = keep_sample_lists ? sstride : 0;
     p.list_base = 0;
     const int grid = (int)std::min<long long>(grid_max, p.n_items) * cg;
     p.num_stages = stages;
@@ -1456,14 +1469,6 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     p.mixed = 0;
     p.refine = 1;
     p.only_flagged = 0;
-    // Room for the in-band candidates of a segment beyond its k best.  Their number grows with k (about
-    // k * z * band / sigma for scores with a Gaussian tail: ~0.4 k on 1024-d unit vectors with bf16 queries); a
-    // segment that overflows the list is flagged and redone by the exact fix-up launch, so this is a speed knob only.
-    int slack = std::max(48, 32 + 5 * k / 4);
-    if (approx != nullptr) slack = std::max(64, 32 + 3 * k);  // the band also covers the rows' bf16 rounding: ~2.3x wider
-    if (const char* e = std::getenv("B2_GEMM_LIST_SLACK")) slack = std::max(8, std::min(1024 - k - 8, atoi(e)));
-    p.list_len = ((k + slack) + 7) / 8 * 8;
-
     // scratch: [A (1 part)][A exact (2 parts)][qn][tau][band][flags][partial][candidate logs]
     auto al = [](size_t v) { return (v + 1023) / 1024 * 1024; };
     const size_t a_bytes = al((size_t)p.nq_pad * kbytes);
@@ -1471,9 +1476,10 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     const size_t qn_bytes = al((size_t)p.nq_pad * 4);
     const size_t fl_bytes = al((size_t)p.n_qt * 4) + 1024;  // + diagnostics counters
     const size_t part_bytes = al((size_t)p.nq_pad * p.n_lists * p.list_len * 8);
+    const size_t spart_bytes = (two_pass && !keep_sample_lists) ? al((size_t)p.nq_pad * nseg_s * p.list_len * 8) : 0;
     const size_t cand_bytes = al((size_t)grid_max * cg * kCandCap * kEpiThreads * 8);  // any of the launches below
     char* blk = nullptr;
-    B2_CUDA_TRY(cudaMallocAsync(&blk, a_bytes + ax_bytes + 3 * qn_bytes + fl_bytes + part_bytes + cand_bytes, stream));
+    B2_CUDA_TRY(cudaMallocAsync(&blk, a_bytes + ax_bytes + 3 * qn_bytes + fl_bytes + part_bytes + spart_bytes + cand_bytes, stream));
     char* cur = blk;
     void* A = cur;
     cur += a_bytes;
@@ -1491,6 +1497,8 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     cur += fl_bytes;
     p.partial = reinterpret_cast<uint64_t*>(cur);
     cur += part_bytes;
+    uint64_t* spartial = reinterpret_cast<uint64_t*>(cur);  // pre-pass lists that are not merged (see keep_sample_lists)
+    cur += spart_bytes;
     p.cand = reinterpret_cast<uint64_t*>(cur);
     p.band = band;
 
@@ -1532,7 +1540,11 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
         ps.n_items = ps.n_qt * ps.n_seg;
         ps.tile_mul = sstride;
         ps.tile_skip = 0;
-        ps.list_base = nseg_m;
+        ps.list_base = keep_sample_lists ? nseg_m : 0;
+        if (!keep_sample_lists) {
+            ps.partial = spartial;
+            ps.n_lists = nseg_s;
+        }
         ps.stats = nullptr;
         rc = launch_approx(ps, (int)std::min<long long>(grid_max, ps.n_items) * cg);
         if (rc == B2_OK) {
@@ -1554,7 +1566,7 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
             }
             if (rc == B2_OK) {
                 tau_union_kernel<<<(unsigned)((nq + kUnionWarps - 1) / kUnionWarps), kUnionWarps * 32, us, stream>>>(
-                    p.partial, (int)nq, p.n_lists, nseg_m, nseg_s, p.list_len, k, band, p.tau);
+                    ps.partial, (int)nq, ps.n_lists, ps.list_base, nseg_s, p.list_len, k, band, p.tau);
                 B2_COUNT_LAUNCH();
                 if (cudaGetLastError() != cudaSuccess) {
                     set_error("tensor-core search: tau_union_kernel launch failed");
