@@ -7,8 +7,11 @@ chain-server request is one `index.search(1 x d, k)` (chains.py:122-123).  On th
 the same HBM time for 1 query as for 16 (the kernels are bandwidth-bound), so searches that arrive within a short
 window are worth running as ONE batched `b2_index_search`.  `BatchingIndex` wraps an index object, keeps its
 faiss-shaped interface, and funnels concurrent `search(x[1, d], k)` calls through one worker thread that groups up
-to `max_batch` of them (waiting at most `max_wait_us` for company) into a single call; each caller gets exactly the
-rows it would have got alone (top-k is a prefix of top-k_max under the engine's deterministic tie rule).
+to `max_batch` of them (waiting at most `max_wait_us` for company) into a single call; each caller gets the rows of
+its own query cut at its own k (top-k is a prefix of top-k_max under the engine's deterministic tie rule).  A
+coalesced batch may be scored by another kernel than a lone query (the tensor-core scan from 5 queries on fp32
+rows, 3 on bf16 rows): scores then agree within the engine's 1e-5 relative parity tolerance, and ids inside a run of
+scores that tie within that tolerance may swap.
 Calls that already carry a batch, and every other method, go straight to the wrapped index.
 """
 from __future__ import annotations
@@ -75,9 +78,19 @@ class BatchingIndex:
             f"search: dimension {a.shape[1]} does not match the index dimension {self._index.d}"
         slot = _Slot(np.ascontiguousarray(a), k)
         with self._cv:
-            self._pending.append(slot)
-            self._cv.notify_all()
-        slot.event.wait()
+            closed = self._closed  # read under the lock: after close() nobody serves the queue any more
+            if not closed:
+                self._pending.append(slot)
+                self._cv.notify_all()
+        if closed:
+            return self._index.search(a, k)
+        while not slot.event.wait(1.0):
+            if not self._thread.is_alive():  # the worker died without serving this slot: search directly
+                with self._cv:
+                    if slot in self._pending:
+                        self._pending.remove(slot)
+                if not slot.event.is_set():
+                    return self._index.search(a, k)
         if slot.exc is not None:
             raise slot.exc
         return slot.D, slot.I

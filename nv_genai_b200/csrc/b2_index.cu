@@ -258,9 +258,15 @@ static int ensure_norms(b2_index* h, int64_t n, cudaStream_t stream) {
     float* np = nullptr;
     B2_CUDA_TRY(cudaMalloc(&np, (size_t)ncap * sizeof(float)));
     if (h->norms != nullptr) {
+        cudaError_t e = cudaSuccess;
         if (h->ntotal > 0)
-            B2_CUDA_TRY(cudaMemcpyAsync(np, h->norms, (size_t)h->ntotal * sizeof(float), cudaMemcpyDeviceToDevice, stream));
-        B2_CUDA_TRY(cudaStreamSynchronize(stream));
+            e = cudaMemcpyAsync(np, h->norms, (size_t)h->ntotal * sizeof(float), cudaMemcpyDeviceToDevice, stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess) {
+            cudaFree(np);  // the old array stays in place
+            set_error("growing the norm array failed: %s", cudaGetErrorString(e));
+            return B2_ERR_CUDA;
+        }
         cudaFree(h->norms);
     }
     h->norms = np;
@@ -838,8 +844,9 @@ int b2_index_remove_ids(b2_index* h, int64_t n, const int64_t* ids, int64_t* n_r
         set_error("b2_index_remove_ids: bad arguments");
         return B2_ERR_INVALID;
     }
-    if (n == 0 || h->ntotal == 0) return B2_OK;
-    std::unique_lock<std::shared_mutex> lk(h->mu);
+    if (n == 0) return B2_OK;
+    std::unique_lock<std::shared_mutex> lk(h->mu);  // ntotal is only read under the writer lock: an add may be running
+    if (h->ntotal == 0) return B2_OK;
     DeviceGuard g(h->device);
     const int64_t nt = h->ntotal;
     std::vector<uint8_t> drop((size_t)nt, 0);
@@ -892,8 +899,10 @@ int b2_index_merge_from(b2_index* dst, b2_index* src) {
                   src->d, dst->dtype, src->dtype, dst->metric, src->metric);
         return B2_ERR_INVALID;
     }
-    std::unique_lock<std::shared_mutex> l1(dst->mu);
-    std::unique_lock<std::shared_mutex> l2(src->mu);
+    // both writer locks, taken together without an order: merge(a, b) next to merge(b, a) must not deadlock
+    std::unique_lock<std::shared_mutex> l1(dst->mu, std::defer_lock);
+    std::unique_lock<std::shared_mutex> l2(src->mu, std::defer_lock);
+    std::lock(l1, l2);
     const int64_t n = src->ntotal;
     if (n == 0) return B2_OK;
     if (dst->ntotal + n >= (int64_t)0xfffffff0ll) {

@@ -31,6 +31,21 @@ except Exception:  # ModuleNotFoundError in this image
             for k, v in kwargs.items():
                 setattr(self, k, v)
 
+        def __setstate__(self, state: Any) -> None:
+            """Also accepts what langchain's own Document pickles: langchain-core 0.1.x documents are pydantic-v1 models
+            whose state is {'__dict__': fields, '__fields_set__': ..., '__private_attribute_values__': ...} (an
+            `index.pkl` written by the reference's apps, e.g.
+            /root/reference/experimental/oran-chatbot-multimodal/vectorstore/vectorstore_updater.py:220); pydantic-v2
+            documents add '__pydantic_*__' keys around the same '__dict__'."""
+            if isinstance(state, tuple) and len(state) == 2:  # (dict state, slots state)
+                state = state[0] or {}
+            if isinstance(state, dict) and isinstance(state.get("__dict__"), dict):
+                state = state["__dict__"]
+            self.__dict__.update(state)
+            self.__dict__.setdefault("page_content", "")
+            if self.__dict__.get("metadata") is None:
+                self.__dict__["metadata"] = {}
+
         def __eq__(self, other: object) -> bool:
             return (isinstance(other, Document) and self.page_content == other.page_content
                     and self.metadata == other.metadata)

@@ -30,7 +30,7 @@ from typing import Any, Callable, Dict, Iterable, List, Optional, Sized, Tuple, 
 import numpy as np
 
 from . import index as _ix
-from .documents import DistanceStrategy, Document, Embeddings, InMemoryDocstore
+from .documents import HAVE_LANGCHAIN, DistanceStrategy, Document, Embeddings, InMemoryDocstore
 from .io import read_index, write_index
 
 logger = logging.getLogger(__name__)
@@ -569,13 +569,25 @@ class FAISS:
         return await cls.afrom_texts(texts, embedding, metadatas=metadatas, **kwargs)
 
     # ------------------------------------------------------------------ persistence
-    def save_local(self, folder_path: str, index_name: str = "index") -> None:
-        """`<index_name>.faiss` in faiss's own IndexFlat file format + `<index_name>.pkl` (docstore, id map)."""
+    def save_local(self, folder_path: str, index_name: str = "index", compat: Optional[str] = None) -> None:
+        """`<index_name>.faiss` in faiss's own IndexFlat file format + `<index_name>.pkl` (docstore, id map).
+
+        `compat="langchain"` writes the pickle under LangChain's class paths
+        (`langchain_community.docstore.in_memory.InMemoryDocstore`, `langchain_core.documents.base.Document` with the
+        pydantic-v1 state langchain-core 0.1.x uses), so that the folder loads with upstream
+        `FAISS.load_local` + faiss-cpu as well - the way back for the stores the reference's apps keep on disk
+        (/root/reference/experimental/oran-chatbot-multimodal/vectorstore/vectorstore_updater.py:184,216,220,
+        /root/reference/examples/5_mins_rag_no_gpu/main.py:78-79,93-94).  The default keeps this package's own classes."""
+        if compat not in (None, "langchain"):
+            raise ValueError("compat must be None or 'langchain'")
         path = Path(folder_path)
         path.mkdir(exist_ok=True, parents=True)
         write_index(getattr(self.index, "wrapped", self.index), str(path / f"{index_name}.faiss"))
         with open(path / f"{index_name}.pkl", "wb") as f:
-            pickle.dump((self.docstore, self.index_to_docstore_id), f)
+            if compat == "langchain" and not HAVE_LANGCHAIN:
+                f.write(_dumps_as_langchain(self.docstore, self.index_to_docstore_id))
+            else:  # with langchain installed the docstore already holds its classes
+                pickle.dump((self.docstore, self.index_to_docstore_id), f)
 
     @classmethod
     def load_local(cls, folder_path: str, embeddings: Embeddings, index_name: str = "index", *,
@@ -658,6 +670,46 @@ def _mmr_on_rows(index: _ix.IndexFlat, query: np.ndarray, rows: np.ndarray, k: i
 
 async def _run_in_executor(func: Callable, *args: Any, **kwargs: Any) -> Any:
     return await asyncio.get_running_loop().run_in_executor(None, functools.partial(func, *args, **kwargs))
+
+
+def _dumps_as_langchain(docstore: Any, index_to_docstore_id: Dict[int, str]) -> bytes:
+    """pickle of (docstore, id map) that names LangChain's classes instead of this package's stand-ins.  pickle stores
+    classes by reference (module + name) and checks that the name resolves to the very class being pickled, so the
+    stand-in modules exist in sys.modules only for the duration of the dump."""
+    import sys
+    import types
+
+    doc_cls = type("Document", (), {
+        "__module__": "langchain_core.documents.base",
+        # the state a pydantic-v1 BaseModel pickles: BaseModel.__setstate__ reads exactly these three keys
+        "__getstate__": lambda self: {"__dict__": dict(self._fields), "__fields_set__": set(self._fields),
+                                      "__private_attribute_values__": {}},
+    })
+    store_cls = type("InMemoryDocstore", (), {"__module__": "langchain_community.docstore.in_memory"})
+    store = store_cls.__new__(store_cls)
+    store._dict = {}
+    for key, doc in getattr(docstore, "_dict", {}).items():
+        d = doc_cls.__new__(doc_cls)
+        fields = {"page_content": doc.page_content, "metadata": dict(doc.metadata or {}), "type": "Document"}
+        object.__setattr__(d, "_fields", fields)
+        store._dict[key] = d
+    names = {"langchain_core": None, "langchain_core.documents": None, "langchain_core.documents.base": doc_cls,
+             "langchain_community": None, "langchain_community.docstore": None,
+             "langchain_community.docstore.in_memory": store_cls}
+    saved = {n: sys.modules.get(n) for n in names}
+    try:
+        for n, cls in names.items():
+            mod = types.ModuleType(n)
+            if cls is not None:
+                setattr(mod, cls.__name__, cls)
+            sys.modules[n] = mod
+        return pickle.dumps((store, dict(index_to_docstore_id)), protocol=4)
+    finally:
+        for n, old in saved.items():
+            if old is None:
+                sys.modules.pop(n, None)
+            else:
+                sys.modules[n] = old
 
 
 class _CompatUnpickler(pickle.Unpickler):

@@ -152,3 +152,25 @@ def test_concurrent_single_vector_searches_are_coalesced_into_batched_scans():
     for a, b in zip(got, want):
         assert [d.page_content for d, _ in a] == [d.page_content for d, _ in b]
         np.testing.assert_allclose([float(s) for _, s in a], [float(s) for _, s in b], rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("name", ["flat_l2_3x4.faiss", "flat_ip_2x3.faiss"])
+def test_read_index_loads_a_hand_assembled_faiss_file_and_writes_it_back(tmp_path, name):
+    """tests/golden/*.faiss: assembled from faiss's header layout outside io.py (make_faiss_fixture.py)."""
+    import os
+    import sys
+
+    from nv_genai_b200.io import read_index, write_index
+
+    golden = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    sys.path.insert(0, golden)
+    import make_faiss_fixture as fx
+
+    rows = fx.L2_ROWS if "l2" in name else fx.IP_ROWS
+    idx = read_index(os.path.join(golden, name))
+    assert idx.ntotal == len(rows) and idx.d == len(rows[0])
+    assert idx.metric_type == (1 if "l2" in name else 0)
+    assert np.array_equal(idx.reconstruct_n(0, idx.ntotal), np.array(rows, dtype=np.float32))
+    out = tmp_path / name
+    write_index(idx, str(out))
+    assert out.read_bytes() == open(os.path.join(golden, name), "rb").read()

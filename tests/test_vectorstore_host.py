@@ -2,6 +2,7 @@
 with a deterministic fake Embeddings and an oracle-backed index (the arithmetic is not under test here;
 the GPU tests run the same scenarios through the CUDA index)."""
 import asyncio
+import os
 import pickle
 import struct
 import warnings
@@ -452,3 +453,101 @@ def test_search_batch_with_filter_and_thresholds_returns_counts():
     assert Ct.tolist() == [4] and It[0, :4].tolist() == I0[0, :4].tolist()
     with pytest.raises(ValueError):
         vs.search_batch(X, 4, filter=lambda m: True)
+
+
+# ------------------------------------------------------------------ on-disk formats pinned from outside io.py
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.mark.parametrize("name,metric,rows", [
+    ("flat_l2_3x4.faiss", METRIC_L2, [[1.0, 0.0, -0.5, 2.0], [0.25, 0.75, 3.0, -1.0], [0.0, 0.0, 0.0, 8.0]]),
+    ("flat_ip_2x3.faiss", METRIC_INNER_PRODUCT, [[0.5, -0.5, 0.125], [4.0, 1.0, -2.0]]),
+])
+def test_write_index_reproduces_the_hand_assembled_faiss_file(tmp_path, name, metric, rows):
+    """tests/golden/*.faiss were assembled byte by byte from faiss's header layout (make_faiss_fixture.py)."""
+    want = open(os.path.join(GOLDEN, name), "rb").read()
+    idx = OracleIndex(len(rows[0]), metric)
+    idx.add(np.array(rows, dtype=np.float32))
+    p = tmp_path / name
+    write_index(idx, str(p))
+    assert p.read_bytes() == want
+
+
+class _PydanticV1Doc:
+    """What langchain-core 0.1.29's Document does when pickled and unpickled (pydantic v1 BaseModel)."""
+
+    def __getstate__(self):
+        return {"__dict__": self.__dict__.copy(), "__fields_set__": set(self.__dict__),
+                "__private_attribute_values__": {}}
+
+    def __setstate__(self, state):
+        assert set(state) == {"__dict__", "__fields_set__", "__private_attribute_values__"}
+        object.__setattr__(self, "__dict__", state["__dict__"])
+
+
+class _PlainDocstore:
+    def __init__(self, d):
+        self._dict = d
+
+
+def _with_stub_langchain(fn):
+    """Run fn() with importable stand-ins for langchain's two classes under their upstream module paths."""
+    import sys
+    import types
+
+    doc = type("Document", (_PydanticV1Doc,), {"__module__": "langchain_core.documents.base"})
+    store = type("InMemoryDocstore", (_PlainDocstore,), {"__module__": "langchain_community.docstore.in_memory"})
+    mods = {"langchain_core": None, "langchain_core.documents": None, "langchain_core.documents.base": doc,
+            "langchain_community": None, "langchain_community.docstore": None,
+            "langchain_community.docstore.in_memory": store}
+    try:
+        for n, cls in mods.items():
+            m = types.ModuleType(n)
+            if cls is not None:
+                setattr(m, cls.__name__, cls)
+            sys.modules[n] = m
+        return fn(doc, store)
+    finally:
+        for n in mods:
+            sys.modules.pop(n, None)
+
+
+def test_langchain_written_index_pkl_loads_without_langchain(tmp_path):
+    """a pydantic-v1 Document pickle must come back with page_content and metadata."""
+    def write(doc, store):
+        d1, d2 = doc.__new__(doc), doc.__new__(doc)
+        d1.__dict__.update(page_content="alpha", metadata={"source": "a.pdf"}, type="Document")
+        d2.__dict__.update(page_content="beta", metadata={}, type="Document")
+        return pickle.dumps((store({"id-1": d1, "id-2": d2}), {0: "id-1", 1: "id-2"}))
+
+    blob = _with_stub_langchain(write)
+    assert b"langchain_core.documents.base" in blob and b"langchain_community.docstore.in_memory" in blob
+    import io as _io
+
+    from nv_genai_b200.vectorstore import _CompatUnpickler
+
+    docstore, id_map = _CompatUnpickler(_io.BytesIO(blob)).load()
+    assert id_map == {0: "id-1", 1: "id-2"}
+    got = docstore.search("id-1")
+    assert got.page_content == "alpha" and got.metadata == {"source": "a.pdf"}
+    assert docstore.search("id-2").page_content == "beta" and docstore.search("id-2").metadata == {}
+
+
+def test_save_local_compat_langchain_loads_upstream(tmp_path):
+    """The way back: a store saved here with compat="langchain" unpickles under langchain's own class paths."""
+    vs, emb = make_store(texts=TEXTS[:5], metadatas=[{"n": i} for i in range(5)])
+    vs.save_local(str(tmp_path), compat="langchain")
+    raw = (tmp_path / "index.pkl").read_bytes()
+    assert b"nv_genai_b200" not in raw and b"langchain_core.documents.base" in raw
+
+    def load(doc, store):
+        docstore, id_map = pickle.loads(raw)  # plain pickle, as upstream FAISS.load_local does
+        assert type(docstore) is store and all(type(v) is doc for v in docstore._dict.values())
+        return {k: (v.page_content, v.metadata) for k, v in docstore._dict.items()}, id_map
+
+    docs, id_map = _with_stub_langchain(load)
+    assert id_map == vs.index_to_docstore_id
+    assert docs == {k: (v.page_content, v.metadata) for k, v in vs.docstore._dict.items()}
+    assert (tmp_path / "index.faiss").read_bytes()[:4] == b"IxF2"
+    with pytest.raises(ValueError):
+        vs.save_local(str(tmp_path), compat="nope")
