@@ -72,18 +72,18 @@ def full():
             s[name].feed(x, r0)
     assert ip.ntotal == N and l2.ntotal == N and ip16.ntotal == N
     out = {name: st.result() for name, st in s.items()}
-    out.update(q16=q16, q_all=q_all, q32=q32, q16_l2=q16_l2, ip=ip, l2=l2, ip16=ip16)
+    out.update(q16=q16, q_all=q_all, q32=q32, q16_l2=q16_l2, idx_ip=ip, idx_l2=l2, idx_bf16=ip16)
     return out
 
 
 @pytest.fixture(scope="module")
 def big(full):
-    return full["ip"]
+    return full["idx_ip"]
 
 
 @pytest.fixture(scope="module")
 def big_bf16(full):
-    return full["ip16"]
+    return full["idx_bf16"]
 
 
 @pytest.fixture(scope="module")
@@ -171,7 +171,7 @@ def test_cfg2_bf16_rows_match_the_oracle_on_rounded_rows(big_bf16, oracle_full, 
 
 # ------------------------------------------------------------------ IndexFlatL2 at full size
 def test_l2_full_size_with_a_planted_copy(oracle_full):
-    idx = oracle_full["l2"]
+    idx = oracle_full["idx_l2"]
     Dr, Ir = oracle_full["l2_16"]
     q = oracle_full["q16_l2"]
     assert Ir[PLANT_QUERY, 0] == PLANT_ROW and Dr[PLANT_QUERY, 0] == 0.0
