@@ -236,6 +236,19 @@ B2_API int b2_merge_shard_lists_wait(int metric, int64_t nq, int k, int nparts, 
                               int64_t part_stride_bytes, const uint32_t* flags, int64_t flag_stride, uint32_t epoch,
                               const int64_t* id_bases, float* D, int64_t* I, int device, void* stream);
 
+/* Row-sharded search, query distribution over the same peer memory (no counterpart in the reference; it takes the
+ * place of the ncclBroadcast SURVEY.md 8e names as step 1 of a sharded search).  The rank that owns the query batch
+ * calls b2_query_push: one CTA per rank stores the nbytes of q_dev into peer_bufs[g] (rank g's receive buffer, mapped
+ * into this process; the entry for the calling rank is its own local buffer) and then releases *peer_flags[g] = epoch
+ * system-wide.  Every rank queues b2_flag_wait(its own flag, epoch) before the search that reads its receive buffer:
+ * a one-warp kernel that returns when the flag shows the epoch (traps after ~20 s).  Both are asynchronous on
+ * `stream`.  The caller alternates between two buffer / flag sets from one search to the next, as for the lists.
+ * nbytes: a multiple of 16, at most B2_QUERY_PUSH_MAX_BYTES (larger batches amortise a collective); <= 16 ranks. */
+#define B2_QUERY_PUSH_MAX_BYTES (256 * 1024)
+B2_API int b2_query_push(const float* q_dev, int64_t nbytes, int nparts, void* const* peer_bufs, uint32_t* const* peer_flags,
+                  uint32_t epoch, int device, void* stream);
+B2_API int b2_flag_wait(const uint32_t* flag, uint32_t epoch, int device, void* stream);
+
 /* faiss.normalize_L2(x) on a caller-owned device array (n x d fp32, in place). */
 B2_API int b2_normalize_l2(float* x, int64_t n, int d, int device, void* stream);
 

@@ -1094,6 +1094,44 @@ int b2_index_search_push(b2_index* h, int64_t nq, const float* q_dev, int k, int
     return search_device(h, nq, q_dev, k, nullptr, nullptr, stream, &push);
 }
 
+int b2_query_push(const float* q_dev, int64_t nbytes, int nparts, void* const* peer_bufs, uint32_t* const* peer_flags,
+                  uint32_t epoch, int device, void* stream_) {
+    if (q_dev == nullptr || nbytes <= 0 || nbytes % 16 != 0 || nparts <= 0 || peer_bufs == nullptr || peer_flags == nullptr ||
+        (reinterpret_cast<uintptr_t>(q_dev) & 15) != 0) {
+        set_error("b2_query_push: bad arguments (nbytes=%lld must be a positive multiple of 16, 16-byte aligned source)",
+                  (long long)nbytes);
+        return B2_ERR_INVALID;
+    }
+    if (nparts > kMaxPushPeers || nbytes > B2_QUERY_PUSH_MAX_BYTES) {
+        set_error("b2_query_push: at most %d peers and %d bytes", kMaxPushPeers, B2_QUERY_PUSH_MAX_BYTES);
+        return B2_ERR_UNSUPPORTED;
+    }
+    for (int g = 0; g < nparts; ++g)
+        if (peer_bufs[g] == nullptr || peer_flags[g] == nullptr) {
+            set_error("b2_query_push: null peer pointer for part %d", g);
+            return B2_ERR_INVALID;
+        }
+    DeviceGuard g(device);
+    if (!g.ok) {
+        set_error("cannot select device %d", device);
+        return B2_ERR_CUDA;
+    }
+    return query_push(q_dev, (size_t)nbytes, nparts, peer_bufs, peer_flags, epoch, static_cast<cudaStream_t>(stream_));
+}
+
+int b2_flag_wait(const uint32_t* flag, uint32_t epoch, int device, void* stream_) {
+    if (flag == nullptr) {
+        set_error("b2_flag_wait: null flag");
+        return B2_ERR_INVALID;
+    }
+    DeviceGuard g(device);
+    if (!g.ok) {
+        set_error("cannot select device %d", device);
+        return B2_ERR_CUDA;
+    }
+    return flag_wait(flag, epoch, static_cast<cudaStream_t>(stream_));
+}
+
 int b2_merge_shard_lists_wait(int metric, int64_t nq, int k, int nparts, const void* blocks, int64_t part_stride_bytes,
                               const uint32_t* flags, int64_t flag_stride, uint32_t epoch, const int64_t* id_bases,
                               float* D, int64_t* I, int device, void* stream_) {

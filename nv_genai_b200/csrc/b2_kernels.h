@@ -65,6 +65,11 @@ int merge_shards_wait(int metric, int nq, int k, int nparts, const char* blocks,
                       const uint32_t* flags, size_t flag_stride_elems, uint32_t epoch, const int64_t* id_bases, float* D,
                       int64_t* I, cudaStream_t stream);
 
+// query block -> every rank's receive buffer + flag (peer mappings), and the wait for it on the receiving stream
+int query_push(const float* q_dev, size_t nbytes, int nparts, void* const* bufs, uint32_t* const* flags, uint32_t epoch,
+               cudaStream_t stream);
+int flag_wait(const uint32_t* flag, uint32_t epoch, cudaStream_t stream);
+
 // b2_filter.cu -------------------------------------------------------------
 // langchain's post-search selection (metadata filter as a row bitmask, raw / relevance thresholds, cut at k) over
 // device results [nq][fetch_k] -> [nq][k] + counts[nq]; see include/b2_flat.h: b2_index_search_filtered.

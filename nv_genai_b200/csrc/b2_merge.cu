@@ -566,6 +566,52 @@ static int merge_shards_impl(int metric, int nq, int k, int nparts, const float*
     return B2_OK;
 }
 
+// ---------------------------------------------------------------- query distribution over peer memory
+// One CTA per destination: copies the query block into that rank's receive buffer (an NVLink peer mapping, or local
+// memory for the sending rank itself), makes it visible system-wide and releases the rank's flag.
+struct QueryPushDst {
+    float4* buf[kMaxPushPeers];
+    uint32_t* flag[kMaxPushPeers];
+};
+__global__ void __launch_bounds__(1024) query_push_kernel(const float4* __restrict__ q, size_t n16, const QueryPushDst dst,
+                                                          uint32_t epoch) {
+    float4* out = dst.buf[blockIdx.x];
+    for (size_t i = threadIdx.x; i < n16; i += blockDim.x) out[i] = q[i];
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) st_release_sys(dst.flag[blockIdx.x], epoch);
+}
+// The receiving side: returns once the flag shows this epoch, so that the kernels queued behind it on the stream read
+// the delivered block.
+__global__ void flag_wait_kernel(const uint32_t* __restrict__ flag, uint32_t epoch) {
+    if (threadIdx.x == 0) {
+        const unsigned long long t0 = clock64();
+        while (ld_acquire_sys(flag) != epoch) {
+            __nanosleep(32);
+            if (clock64() - t0 > 40000000000ull) __trap();  // ~20 s: the sender never delivered
+        }
+        __threadfence_system();
+    }
+}
+
+int query_push(const float* q_dev, size_t nbytes, int nparts, void* const* bufs, uint32_t* const* flags, uint32_t epoch,
+               cudaStream_t stream) {
+    QueryPushDst dst;
+    for (int g = 0; g < kMaxPushPeers; ++g) {
+        dst.buf[g] = g < nparts ? static_cast<float4*>(bufs[g]) : nullptr;
+        dst.flag[g] = g < nparts ? flags[g] : nullptr;
+    }
+    query_push_kernel<<<nparts, nbytes >= 16384 ? 1024 : 256, 0, stream>>>(reinterpret_cast<const float4*>(q_dev), nbytes / 16, dst, epoch);
+    B2_AFTER_LAUNCH();
+    return B2_OK;
+}
+
+int flag_wait(const uint32_t* flag, uint32_t epoch, cudaStream_t stream) {
+    flag_wait_kernel<<<1, 32, 0, stream>>>(flag, epoch);
+    B2_AFTER_LAUNCH();
+    return B2_OK;
+}
+
 int merge_shards(int metric, int nq, int k, int nparts, const float* D_parts, const int64_t* I_parts, float* D,
                  int64_t* I, cudaStream_t stream, size_t d_stride_bytes, size_t i_stride_bytes,
                  const int64_t* id_bases) {

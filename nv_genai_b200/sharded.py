@@ -35,6 +35,7 @@ class _PeerExchange:
 
     MAX_RESULTS = 1 << 17  # nq * k per search (12 B each -> 1.5 MB blocks)
     MAX_NQ = 4096
+    MAX_Q_BYTES = 256 * 1024  # query blocks up to this size travel through peer memory (B2_QUERY_PUSH_MAX_BYTES)
 
     def __init__(self, torch, dist, group, device, world: int, rank: int):
         import torch.distributed._symmetric_memory as symm
@@ -43,7 +44,10 @@ class _PeerExchange:
         self.blk = self.MAX_RESULTS * 12
         self.slot_bytes = world * self.blk
         self.flag_off = 2 * self.slot_bytes
-        total = self.flag_off + 2 * world * self.MAX_NQ * 4
+        # after the list flags: two query receive buffers and their two flag words (one cache line each)
+        self.q_off = self.flag_off + 2 * world * self.MAX_NQ * 4
+        self.qflag_off = self.q_off + 2 * self.MAX_Q_BYTES
+        total = self.qflag_off + 2 * 128
         self.buf = symm.empty(total, dtype=torch.uint8, device=device)
         self.buf.zero_()
         torch.cuda.synchronize(device)
@@ -55,6 +59,15 @@ class _PeerExchange:
 
     def fits(self, nq: int, k: int) -> bool:
         return nq <= self.MAX_NQ and nq * k <= self.MAX_RESULTS
+
+    def query_slot(self, epoch: int):
+        """(receive-buffer pointers on every rank, flag pointers on every rank, local view of this rank's buffer,
+        local flag pointer) of the query block of search `epoch`."""
+        slot = epoch & 1
+        bufs = [p + self.q_off + slot * self.MAX_Q_BYTES for p in self.ptrs]
+        flags = [p + self.qflag_off + slot * 128 for p in self.ptrs]
+        lo = self.q_off + slot * self.MAX_Q_BYTES
+        return bufs, flags, self.buf[lo: lo + self.MAX_Q_BYTES], self.ptrs[self.rank] + self.qflag_off + slot * 128
 
     def next_slot(self):
         """(epoch, push block pointers, push flag pointers, local blocks, local flags) of the next search."""
@@ -150,11 +163,35 @@ class ShardedFlatIndex:
         return self.bases[-1]
 
     # ------------------------------------------------------------------ search
-    def search(self, q, k: int, replicated: bool = True, src: int = 0):
-        """Global top-k on every rank.  q: [nq, d] tensor on the communication device; if not
-        `replicated`, rank `src` broadcasts it first.  Returns (D [nq, k] fp32, I [nq, k] int64 global ids)."""
+    def search(self, q, k: int, replicated: bool = True, src: int = 0, out=None):
+        """Global top-k on every rank.  q: [nq, d] tensor on the communication device; if not `replicated`, rank `src`
+        owns the batch and the other ranks' `q` is only a receive buffer of the same shape: small batches travel through
+        NVLink peer memory (one store kernel on `src`, a flag wait on every rank, no collective), large ones by
+        broadcast.  `out` (CUDA path): a uint8 tensor of nq * k * 12 bytes that receives the packed result
+        [I: nq x k int64 | D: nq x k fp32], so a caller can bring both back with ONE device-to-host copy.
+        Returns (D [nq, k] fp32, I [nq, k] int64 global ids) (views into `out` when given)."""
         t, dist = self._torch, self._dist
-        if not replicated:
+        pushed = False
+        if (not replicated and self._peer is not None and self._fast and isinstance(q, t.Tensor) and q.is_cuda
+                and q.dim() == 2 and q.dtype == t.float32 and q.is_contiguous()
+                and q.numel() * 4 <= self._peer.MAX_Q_BYTES and (q.numel() * 4) % 16 == 0
+                and self._peer.fits(q.shape[0], k)):
+            # the query block goes where the lists go: into every rank's symmetric block, flag-released
+            from . import _native as N
+            from .index import _stream_for
+
+            e = (self._peer.epoch + 1) & 0xFFFFFFFF or 1  # the epoch next_slot() hands out below
+            bufs, flags, local, lflag = self._peer.query_slot(e)
+            w, dev = self.world, q.device.index
+            stream = _stream_for(dev)
+            nbytes = q.numel() * 4
+            if self.rank == src:
+                N.check(N.lib.b2_query_push(q.data_ptr(), nbytes, w, (ctypes.c_void_p * w)(*bufs),
+                                            (ctypes.c_void_p * w)(*flags), e, dev, stream))
+            N.check(N.lib.b2_flag_wait(lflag, e, dev, stream))
+            q = local[:nbytes].view(t.float32).view(q.shape)
+            pushed = True
+        if not replicated and not pushed:
             dist.broadcast(q, src=src, group=self.group)
         if self._fast and isinstance(q, t.Tensor) and q.is_cuda:
             # CUDA path: the local search writes (I, D) straight into the block that is all-gathered, ids stay
@@ -177,8 +214,13 @@ class ShardedFlatIndex:
                 qc = q if (q.dtype == t.float32 and q.is_contiguous()) else q.to(t.float32).contiguous()
                 N.check(N.lib.b2_index_search_push(self.local._h, nq, qc.data_ptr(), k, w, (ctypes.c_void_p * w)(*blocks),
                                                    (ctypes.c_void_p * w)(*flags), e, stream))
-                D = t.empty((nq, k), dtype=t.float32, device=q.device)
-                I = t.empty((nq, k), dtype=t.int64, device=q.device)
+                if out is not None:
+                    assert out.is_cuda and out.dtype == t.uint8 and out.is_contiguous() and out.numel() == nres * 12
+                    I = out[: nres * 8].view(t.int64).view(nq, k)
+                    D = out[nres * 8:].view(t.float32).view(nq, k)
+                else:
+                    D = t.empty((nq, k), dtype=t.float32, device=q.device)
+                    I = t.empty((nq, k), dtype=t.int64, device=q.device)
                 bases = (ctypes.c_int64 * w)(*[int(b) for b in self.bases[:w]])
                 N.check(N.lib.b2_merge_shard_lists_wait(self.metric, nq, k, w, lblocks, self._peer.blk, lflags,
                                                         self._peer.MAX_NQ, e, bases, D.data_ptr(), I.data_ptr(), dev,
@@ -196,7 +238,11 @@ class ShardedFlatIndex:
             D_loc = packed[nres * 8:].view(t.float32).view(nq, k)
             self.local.search_into(q, k, D_loc, I_loc)
             dist.all_gather_into_tensor(gathered, packed, group=self.group)
-            return merge_shard_lists_packed(self.metric, gathered, nq, k, self.bases)
+            D, I = merge_shard_lists_packed(self.metric, gathered, nq, k, self.bases)
+            if out is not None:
+                out[: nres * 8].view(t.int64).view(nq, k).copy_(I)
+                out[nres * 8:].view(t.float32).view(nq, k).copy_(D)
+            return D, I
         D_loc, I_loc = self.local.search(q, k)
         if not isinstance(D_loc, t.Tensor):
             D_loc, I_loc = t.from_numpy(D_loc), t.from_numpy(I_loc)
