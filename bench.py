@@ -12,8 +12,10 @@ A "step" is one pass of the hot path (index.search) over one batch of synthetic 
             measured live with CUDA events on the launching stream, against MEASURED_PEAKS.json
   cpu_baseline  the oracle's C restatement of faiss IndexFlat (OpenMP over queries only, like faiss below 20
             queries) timed on this box's host cores on a bounded row sample, scaled linearly in rows
-N > 1: the fixed 10M-row corpus is row-sharded over the ranks (strong scaling), rank 0 broadcasts each query
-batch, every rank scans its shard, ONE all-gather exchanges the per-shard (score, id) lists, every rank merges.
+N > 1: the fixed corpus is row-sharded over the ranks (strong scaling), rank 0's query batch reaches the other ranks
+through NVLink peer memory, every rank scans its shard and stores its (score, id) lists into every rank's receive block
+from inside its merge kernel, every rank merges (nv_genai_b200/sharded.py; NCCL broadcast / all-gather where there is
+no peer access).
 `--impl reference` times the CPU restatement alone (the reference's own implementation, faiss-cpu, is not
 installable here: BASELINE.md section 2).
 """
@@ -613,6 +615,8 @@ def run_b200(a):
         q_host.copy_(q_dev.cpu())
         q_np = q_host.numpy()
         stage = torch.empty((batch, a.dim), dtype=torch.float32, device=f"cuda:{local}")
+        packed = torch.empty(batch * k * 12, dtype=torch.uint8, device=f"cuda:{local}")
+        out_host = torch.empty(batch * k * 12, dtype=torch.uint8).pin_memory()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         tensor = uses_tensor_path(batch, k, hi - lo)
         kern = _native.PROF_GEMM if tensor else _native.PROF_SCAN
@@ -629,9 +633,9 @@ def run_b200(a):
                 return index.search(q_np[i], k)  # host buffers in, host buffers out, through b2_index_search
             if rank == 0:
                 stage.copy_(q_host[i], non_blocking=True)  # H2D from pinned memory
-            D, I = shx.search(stage, k, replicated=False, src=0)
+            D, I = shx.search(stage, k, replicated=False, src=0, out=packed)
             if rank == 0:
-                return D.cpu(), I.cpu()  # D2H of the merged result
+                out_host.copy_(packed)  # ONE D2H of the merged result, packed [I | D]; synchronises
             return D, I
 
         def timed(step_fn, with_prof):
