@@ -10,6 +10,9 @@ verbatim from the notebook at run time (nothing is copied into this repository),
 it on seeded synthetic embeddings with no positives and an infinite mining threshold — which
 reduces it to exactly "top-k by inner product" — and stores the resulting index SETS
 (argpartition leaves the order unspecified) in tests/golden/ip_topk_reference.json.
+On the normalised cases the same sets also pin IndexFlatL2 (the reference's default index,
+/root/reference/RetrievalAugmentedGeneration/common/utils.py:217): for unit vectors the squared
+L2 distance is 2 - 2 q.x, so the k nearest rows are the k rows of largest inner product.
 
 /root/reference does not exist on the GPU box, so only the JSON travels; tests regenerate
 the inputs from the recorded seeds with the integer-exact synthetic generator.
@@ -35,6 +38,11 @@ CASES = [
     ("u_5000x1024_k4", 5000, 4, 1024, 4, True),
     ("raw_3000x96_k25", 3000, 6, 96, 25, False),
     ("u_1500x384_k100", 1500, 5, 384, 100, True),
+    # the tensor-core paths' shapes: >= 20 queries (faiss's BLAS routine; here the GEMM kernel), k = 100, and a corpus
+    # long enough for the threshold pre-pass of the GEMM kernel (>= 2048 tiles of 256 rows)
+    ("u_200000x1024_k100_q24", 200_000, 24, 1024, 100, True),
+    ("u_600000x256_k100_q32", 600_000, 32, 256, 100, True),
+    ("u_200000x1024_k10_q8", 200_000, 8, 1024, 10, True),
 ]
 
 

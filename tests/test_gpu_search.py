@@ -180,6 +180,12 @@ def test_golden_reference_sets_on_the_cuda_path():
         _, I = idx.search(Q, c["k"])
         for r in range(c["nq"]):
             assert sorted(I[r].tolist()) == c["topk_sets"][r], c["name"]
+        if c["normalize"]:  # unit vectors: the same sets pin IndexFlatL2 (2 - 2 q.x)
+            idx2 = _mk(flat.METRIC_L2, c["d"])
+            idx2.add(P)
+            _, I2 = idx2.search(Q, c["k"])
+            for r in range(c["nq"]):
+                assert sorted(I2[r].tolist()) == c["topk_sets"][r], c["name"] + " (L2)"
 
 
 def test_bf16_row_store_recall_and_scores():

@@ -38,6 +38,12 @@ def test_golden_ip_topk_sets_from_reference_notebook():
         for r in range(c["nq"]):
             assert sorted(I[r].tolist()) == c["topk_sets"][r], c["name"]
         assert np.all(np.diff(D, axis=1) <= 0)  # IP descending
+        if c["normalize"]:
+            # unit vectors: |x - q|^2 = 2 - 2 q.x, so the same sets pin IndexFlatL2 (the reference's default index)
+            D2, I2 = flat.search(P, Q, c["k"], flat.METRIC_L2)
+            for r in range(c["nq"]):
+                assert sorted(I2[r].tolist()) == c["topk_sets"][r], c["name"] + " (L2)"
+            assert np.all(np.diff(D2, axis=1) >= 0)  # L2 ascending
 
 
 @pytest.mark.parametrize("metric", [flat.METRIC_IP, flat.METRIC_L2])
