@@ -243,11 +243,34 @@ B2_API int b2_merge_shard_lists_wait(int metric, int64_t nq, int k, int nparts, 
  * system-wide.  Every rank queues b2_flag_wait(its own flag, epoch) before the search that reads its receive buffer:
  * a one-warp kernel that returns when the flag shows the epoch (traps after ~20 s).  Both are asynchronous on
  * `stream`.  The caller alternates between two buffer / flag sets from one search to the next, as for the lists.
- * nbytes: a multiple of 16, at most B2_QUERY_PUSH_MAX_BYTES (larger batches amortise a collective); <= 16 ranks. */
-#define B2_QUERY_PUSH_MAX_BYTES (256 * 1024)
+ * nbytes: a multiple of 16, at most B2_QUERY_PUSH_MAX_BYTES (1024 queries of 1024 fp32); <= 16 ranks. */
+#define B2_QUERY_PUSH_MAX_BYTES (4 * 1024 * 1024)
 B2_API int b2_query_push(const float* q_dev, int64_t nbytes, int nparts, void* const* peer_bufs, uint32_t* const* peer_flags,
                   uint32_t epoch, int device, void* stream);
 B2_API int b2_flag_wait(const uint32_t* flag, uint32_t epoch, int device, void* stream);
+
+/* A flat index sharded by rows over several GPUs of THIS process (b2_shard_group_create /
+ * b2_shard_search; no counterpart in the reference, whose index lives on one host - the role of faiss.IndexShards
+ * over per-GPU flat indexes).  Shard g lives on devices[g] (a device may appear more than once) and holds the
+ * contiguous id range after shard g - 1's: rows are appended to shard g until it holds rows_per_shard rows, then to
+ * shard g + 1; the last shard takes whatever follows.  Ids are faiss's implicit positions, results equal the single
+ * index's bit for bit (same kernels per row, lowest id first among equal scores).  devices[0] is the ROOT: device
+ * inputs / outputs of add and search live there.  Every pair of distinct devices needs peer access.  A search runs
+ * the peer-memory protocol described above (query push, per-shard search with its lists stored into the root's
+ * receive blocks, flag-waiting merge) on one stream per shard; calls on one group are enqueued one at a time.
+ * b2_shard_group_remove_ids takes GLOBAL ids and renumbers like faiss (rows after a removed one move down). */
+typedef struct b2_shard_group b2_shard_group;
+B2_API int b2_shard_group_create(int ndev, const int* devices, int d, int metric, int dtype, int64_t rows_per_shard,
+                          b2_shard_group** out);
+B2_API void b2_shard_group_destroy(b2_shard_group* g);
+B2_API int64_t b2_shard_group_ntotal(const b2_shard_group* g);
+B2_API int b2_shard_group_nshards(const b2_shard_group* g);
+B2_API int64_t b2_shard_group_shard_ntotal(const b2_shard_group* g, int shard);
+B2_API int b2_shard_group_add(b2_shard_group* g, int64_t n, const float* x, int x_where, unsigned flags);
+B2_API int b2_shard_group_remove_ids(b2_shard_group* g, int64_t n, const int64_t* ids, int64_t* n_removed);
+B2_API int b2_shard_group_reset(b2_shard_group* g);
+B2_API int b2_shard_search(b2_shard_group* g, int64_t nq, const float* q, int q_where, int k, float* D, int64_t* I,
+                    int out_where, void* stream);
 
 /* faiss.normalize_L2(x) on a caller-owned device array (n x d fp32, in place). */
 B2_API int b2_normalize_l2(float* x, int64_t n, int d, int device, void* stream);

@@ -12,7 +12,7 @@ from .documents import DistanceStrategy, Document, Embeddings, InMemoryDocstore
 from .index import (METRIC_INNER_PRODUCT, METRIC_L2, IndexFlat, IndexFlatIP, IndexFlatL2, merge_shard_lists,
                     normalize_L2, synth_fill)
 from .io import read_index, write_index
-from .sharded import ShardedFlatIndex, shard_bounds
+from .sharded import ShardedFlatIndex, ShardGroup, shard_bounds
 from .vectorstore import FAISS, VectorStoreRetriever
 
 B200FlatStore = FAISS  # the working name used in SURVEY.md 8b
@@ -20,6 +20,6 @@ B200FlatStore = FAISS  # the working name used in SURVEY.md 8b
 __all__ = [
     "FAISS", "B200FlatStore", "VectorStoreRetriever", "IndexFlat", "IndexFlatL2", "IndexFlatIP",
     "METRIC_INNER_PRODUCT", "METRIC_L2", "normalize_L2", "read_index", "write_index", "Document", "Embeddings",
-    "InMemoryDocstore", "DistanceStrategy", "ShardedFlatIndex", "BatchingIndex", "shard_bounds", "merge_shard_lists", "synth_fill",
+    "InMemoryDocstore", "DistanceStrategy", "ShardedFlatIndex", "ShardGroup", "BatchingIndex", "shard_bounds", "merge_shard_lists", "synth_fill",
 ]
 __version__ = "0.1.0"

@@ -35,7 +35,7 @@ class _PeerExchange:
 
     MAX_RESULTS = 1 << 17  # nq * k per search (12 B each -> 1.5 MB blocks)
     MAX_NQ = 4096
-    MAX_Q_BYTES = 256 * 1024  # query blocks up to this size travel through peer memory (B2_QUERY_PUSH_MAX_BYTES)
+    MAX_Q_BYTES = 4 * 1024 * 1024  # query blocks up to this size travel through peer memory (B2_QUERY_PUSH_MAX_BYTES)
 
     def __init__(self, torch, dist, group, device, world: int, rank: int):
         import torch.distributed._symmetric_memory as symm
@@ -258,3 +258,77 @@ class ShardedFlatIndex:
         I_parts = gathered[:, :nb_i].contiguous().view(t.int64).reshape(self.world, nq, k)
         D_parts = gathered[:, nb_i:].contiguous().view(t.float32).reshape(self.world, nq, k)
         return self._merge(self.metric, D_parts, I_parts)
+
+
+class ShardGroup:
+    """A flat index sharded by rows over several GPUs of THIS process: a thin caller of the C ABI's shard group
+    (b2_shard_group_create / b2_shard_search in include/b2_flat.h).  Same faiss-shaped surface as
+    IndexFlat (`d`, `ntotal`, `add`, `search -> (D, I)`, `remove_ids`, `reset`); `devices[0]` is the root device, where
+    CUDA-tensor inputs and outputs live.  `rows_per_shard` rows go to one shard before the next one receives any."""
+
+    def __init__(self, d: int, metric: int, devices, rows_per_shard: int, dtype: str = "float32"):
+        from . import _native as N
+        from .index import _DTYPES
+
+        self._N = N
+        self.devices = [int(v) for v in devices]
+        self._d, self.metric_type = int(d), int(metric)
+        self._h = ctypes.c_void_p()
+        arr = (ctypes.c_int * len(self.devices))(*self.devices)
+        N.check(N.lib.b2_shard_group_create(len(self.devices), arr, self._d, self.metric_type, _DTYPES[dtype],
+                                            int(rows_per_shard), ctypes.byref(self._h)))
+        self.is_trained = True
+
+    d = property(lambda self: self._d)
+    ntotal = property(lambda self: int(self._N.lib.b2_shard_group_ntotal(self._h)))
+
+    def shard_ntotal(self, shard: int) -> int:
+        return int(self._N.lib.b2_shard_group_shard_ntotal(self._h, int(shard)))
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and h.value:
+            try:
+                self._N.lib.b2_shard_group_destroy(h)
+            except Exception:
+                pass
+            h.value = None
+
+    def add(self, x, normalize: bool = False) -> None:
+        from .index import _Buf
+
+        b = _Buf(x, self._d, self.devices[0], "add")
+        N = self._N
+        N.check(N.lib.b2_shard_group_add(self._h, b.n, b.ptr, b.where, N.ADD_NORMALIZE if normalize else 0))
+
+    def search(self, x, k: int):
+        import numpy as np
+
+        from .index import _Buf, _stream_for, _torch
+
+        b = _Buf(x, self._d, self.devices[0], "search")
+        k = int(k)
+        assert k > 0, "k must be positive"
+        N = self._N
+        stream = _stream_for(self.devices[0])
+        if b.is_tensor:
+            t = _torch()
+            D = t.empty((b.n, k), dtype=t.float32, device=b.obj.device)
+            I = t.empty((b.n, k), dtype=t.int64, device=b.obj.device)
+            N.check(N.lib.b2_shard_search(self._h, b.n, b.ptr, N.DEVICE, k, D.data_ptr(), I.data_ptr(), N.DEVICE, stream))
+            return D, I
+        D = np.empty((b.n, k), dtype=np.float32)
+        I = np.empty((b.n, k), dtype=np.int64)
+        N.check(N.lib.b2_shard_search(self._h, b.n, b.ptr, b.where, k, D.ctypes.data, I.ctypes.data, N.HOST, stream))
+        return D, I
+
+    def remove_ids(self, ids) -> int:
+        import numpy as np
+
+        a = np.ascontiguousarray(np.asarray(ids, dtype=np.int64).reshape(-1))
+        removed = ctypes.c_int64(0)
+        self._N.check(self._N.lib.b2_shard_group_remove_ids(self._h, a.size, a.ctypes.data, ctypes.byref(removed)))
+        return int(removed.value)
+
+    def reset(self) -> None:
+        self._N.check(self._N.lib.b2_shard_group_reset(self._h))

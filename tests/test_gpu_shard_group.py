@@ -1,0 +1,97 @@
+"""GPU: the C-ABI shard group (b2_shard_group_* / b2_shard_search) against one index holding the same rows and against
+the oracle.  Shards may share a device, so the whole protocol - query push, per-shard search storing its lists into the
+root's receive blocks, flag-waiting merge with shard bases - runs on a single GPU; with more GPUs visible the same
+test spreads the shards over them."""
+import numpy as np
+import pytest
+
+from oracle import flat
+from parity import assert_parity
+
+pytestmark = pytest.mark.gpu
+
+
+def _devices(n):
+    import torch
+
+    g = torch.cuda.device_count()
+    return [i % g for i in range(n)]
+
+
+@pytest.mark.parametrize("metric", [flat.METRIC_IP, flat.METRIC_L2])
+@pytest.mark.parametrize("dtype", ["float32", "bfloat16"])
+def test_shard_group_equals_single_index_and_oracle(metric, dtype):
+    from nv_genai_b200 import IndexFlat, ShardGroup
+
+    n, d, per = 50_000, 256, 16_000  # 4 shards: 16k, 16k, 16k, 2k
+    x = flat.synth(0, n, d, 21)
+    flat.normalize_L2(x)
+    q = flat.synth(0, 40, d, 22)
+    flat.normalize_L2(q)
+    q[5] = x[15_999]  # planted on a shard boundary
+    q[6] = x[16_000]
+    grp = ShardGroup(d, metric, _devices(4), per, dtype=dtype)
+    grp.add(x[:30_000])
+    grp.add(x[30_000:])
+    assert grp.ntotal == n and [grp.shard_ntotal(i) for i in range(4)] == [16_000, 16_000, 16_000, 2_000]
+    one = IndexFlat(d, metric, dtype)
+    one.add(x)
+    xs = flat.round_bf16(x) if dtype == "bfloat16" else x
+    for nq, k in ((1, 4), (16, 10), (40, 100)):
+        D, I = grp.search(q[:nq], k)
+        D1, I1 = one.search(q[:nq], k)
+        assert np.array_equal(I, I1) and np.array_equal(D, D1), (nq, k)
+        Dr, Ir = flat.search(xs, q[:nq], k, metric)
+        assert_parity(D, I, Dr, Ir, xs, q[:nq], metric_ip=metric == flat.METRIC_IP)
+    if metric == flat.METRIC_IP:
+        D, I = grp.search(q[:16], 10)
+        assert I[5, 0] == 15_999 and I[6, 0] == 16_000
+
+
+def test_shard_group_device_tensors_many_queries_and_mutation():
+    import torch
+
+    from nv_genai_b200 import IndexFlatIP, ShardGroup
+
+    n, d = 30_000, 128
+    x = flat.synth(0, n, d, 31)
+    q = flat.synth(0, 5000, d, 32)  # more than one pass of 4096 queries
+    grp = ShardGroup(d, flat.METRIC_IP, _devices(3), 10_000)
+    dev = f"cuda:{grp.devices[0]}"
+    grp.add(torch.from_numpy(x).to(dev), normalize=True)
+    one = IndexFlatIP(d, device=grp.devices[0])
+    one.add(x, normalize=True)
+    qt = torch.from_numpy(q).to(dev)
+    D, I = grp.search(qt, 7)
+    D1, I1 = one.search(qt, 7)
+    assert torch.equal(I, I1) and torch.equal(D, D1)
+    # two searches back to back on different streams
+    s1 = torch.cuda.Stream(device=dev)
+    with torch.cuda.stream(s1):
+        Da, Ia = grp.search(qt[:8], 5)
+    Db, Ib = grp.search(qt[8:16], 5)
+    torch.cuda.synchronize()
+    assert torch.equal(Ia, I1[:8, :5]) and torch.equal(Ib, I1[8:16, :5])
+    # remove_ids takes global ids and renumbers like faiss
+    drop = [0, 9_999, 10_000, 25_000]
+    assert grp.remove_ids(drop) == 4 and one.remove_ids(drop) == 4
+    assert grp.ntotal == n - 4 and [grp.shard_ntotal(i) for i in range(3)] == [9_998, 9_999, 9_999]
+    D, I = grp.search(q[:16], 7)
+    D1, I1 = one.search(q[:16], 7)
+    assert np.array_equal(I, I1) and np.array_equal(D, D1)
+    grp.reset()
+    assert grp.ntotal == 0
+    D, I = grp.search(q[:2], 3)
+    assert np.all(I == -1)
+
+
+def test_shard_group_argument_errors():
+    from nv_genai_b200 import ShardGroup
+
+    with pytest.raises(ValueError):
+        ShardGroup(64, flat.METRIC_IP, [], 100)
+    with pytest.raises(ValueError):
+        ShardGroup(64, flat.METRIC_IP, [0], 0)
+    grp = ShardGroup(64, flat.METRIC_IP, [0, 0], 100)
+    with pytest.raises(AssertionError):
+        grp.search(np.zeros((1, 32), np.float32), 3)
