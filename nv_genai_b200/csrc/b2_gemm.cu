@@ -956,22 +956,9 @@ __global__ void band_kernel(const float* __restrict__ q, int nq, int d, int nq_p
         ss += __shfl_xor_sync(kFull, ss, s);
         se += __shfl_xor_sync(kFull, se, s);
     }
-    if (lane == 0) {
-        float xn = sqrtf(fmaxf(ord2f(*max_norm_ord), 0.f)) * 1.0001f;
-        const float qn = sqrtf(ss) * 1.0001f, qe = sqrtf(se) * 1.0001f;
-        // rows replaced by a rounded copy x~ (bf16 shadow of fp32 rows): |q.x - q~.x~| <= |q~| |x - x~| + |q - q~| |x~|
-        const float xe = row_err_ord != nullptr ? sqrtf(fmaxf(ord2f(*row_err_ord), 0.f)) * 1.0001f : 0.f;
-        xn += xe;
-        float err = qe * xn + qn * xe;
-        if (KIND != 0) err += qn * xn * 0.0009765625f;               // the row operand is truncated to tf32: 2^-10
-        err += (float)steps * 4.76837158e-7f * qn * xn;              // accumulation: steps x 2^-21
-        float b = 2.f * err * 1.001f + 1e-30f;
-        // L2 keys are 2 q.x - |x|^2: twice the product error, plus the rounding of the stored squared norm and of the
-        // fp32 distance the candidates are finally ranked by (sums of d squares: relative error below d * 2^-24 of
-        // at most (|q| + |x|)^2)
-        if (l2) b = 2.f * b + 2.f * (xn + qn) * (xn + qn) * (float)d * 5.9604645e-8f;
-        band[row] = b;
-    }
+    if (lane == 0)
+        band[row] = band_from_sums(ss, se, KIND != 0, steps, l2 != 0, d, ord2f(*max_norm_ord),
+                                   row_err_ord != nullptr ? ord2f(*row_err_ord) : 0.f);
 }
 
 // After the threshold pre-pass: tau[q] = an exclusive lower bound of the final k-th key of query q = the k-th largest

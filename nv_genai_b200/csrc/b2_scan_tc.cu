@@ -383,6 +383,48 @@ int launch_scan_tc(const CUtensorMap& tmRows, const CUtensorMap& tmQ, const Scan
     return B2_OK;
 }
 
+// Everything the approximate scan needs from the queries, in ONE launch (it used to be a memset and three kernels:
+// at one query the fixed cost of the launch chain, not the row stream, is what a 5 GB shard notices): the rounded
+// query operand Q (tf32 on fp32 rows, bf16 on bf16 rows), the two-part operand Qx of the exact fix-up scan (fp32
+// rows: tf32 hi | x - hi), the error band, and the overflow flags cleared.  One warp per row of the query tile.
+template <bool BF16>
+__global__ void scan_tc_prep_kernel(const float* __restrict__ q, int nq, int d, int nqt, int kp, void* __restrict__ Q,
+                                    float* __restrict__ Qx, int steps, int l2, const uint32_t* __restrict__ max_norm_ord,
+                                    float* __restrict__ band, uint32_t* __restrict__ flags) {
+    const int lane = threadIdx.x & 31;
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (blockIdx.x == 0)
+        for (int i = threadIdx.x; i <= nq; i += blockDim.x) flags[i] = 0u;
+    if (row >= nqt) return;
+    float ss = 0.f, se = 0.f;
+    for (int c = lane; c < kp; c += 32) {
+        const float x = (row < nq && c < d) ? q[(size_t)row * d + c] : 0.f;
+        float h;
+        if (BF16) {
+            const __nv_bfloat16 hb = __float2bfloat16_rn(x);
+            static_cast<__nv_bfloat16*>(Q)[(size_t)row * kp + c] = hb;
+            h = __bfloat162float(hb);
+        } else {
+            uint32_t u;
+            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+            h = __uint_as_float(u);
+            static_cast<float*>(Q)[(size_t)row * kp + c] = h;
+            if (Qx != nullptr) {
+                Qx[(size_t)row * kp + c] = h;
+                Qx[((size_t)nqt + row) * kp + c] = x - h;
+            }
+        }
+        ss = fmaf(h, h, ss);
+        se = fmaf(x - h, x - h, se);
+    }
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) {
+        ss += __shfl_xor_sync(kFull, ss, s);
+        se += __shfl_xor_sync(kFull, se, s);
+    }
+    if (lane == 0) band[row] = band_from_sums(ss, se, !BF16, steps, l2 != 0, d, ord2f(*max_norm_ord), 0.f);
+}
+
 }  // namespace
 
 bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t nq, bool approx) {
@@ -400,7 +442,8 @@ bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t n
     // query) the FFMA scan's two launches win until the FP32 pipe falls behind (5 queries fp32, 3 bf16).
     // (fp32 rows with k > 64 run the all-exact variant, 7.3 ms: the small thresholds stay)
     int min_nq = (dtype == B2_DTYPE_BF16) ? 3 : 5;
-    if ((double)n * d * elem >= 8e9 && (dtype == B2_DTYPE_BF16 || k <= 64)) min_nq = 1;
+    static const double min_bytes = getenv("B2_SCAN_TC_MIN_BYTES") ? atof(getenv("B2_SCAN_TC_MIN_BYTES")) : 8e9;
+    if ((double)n * d * elem >= min_bytes && (dtype == B2_DTYPE_BF16 || k <= 64)) min_nq = 1;
     if (const char* e = getenv("B2_SCAN_TC_MIN_NQ")) min_nq = atoi(e);
     // up to 32 queries ride along in one pass when k is small (gemm path at 20..128 queries: 10-11.6 ms fp32,
     // 5.9-6.7 ms bf16 at 10M x 1024, against the 5.8 / 3.1 ms it takes to stream the rows once)
@@ -486,13 +529,20 @@ static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes
     int rc = make_map(&tmRows, bf16, kSlice, rows, (uint64_t)(pitch_bytes / elem), (uint64_t)n, pitch_bytes, kTileRows, promo);
     if (rc == B2_OK) rc = make_map(&tmQ, bf16, kSlice, Q, (uint64_t)kp, (uint64_t)nqt, kbytes, nqt);
     if (rc == B2_OK) rc = make_map(&tmQx, bf16, kSlice, Qx, (uint64_t)kp, (uint64_t)2 * nqt, kbytes, 2 * nqt);
-    if (rc == B2_OK && cudaMemsetAsync(flags, 0, (size_t)(nq + 1) * 4, stream) != cudaSuccess) {
-        set_error("tensor-core scan: cudaMemsetAsync failed");
-        rc = B2_ERR_CUDA;
+    if (rc == B2_OK) {
+        const int steps = bf16 ? kp / 16 : kp / 8;
+        if (bf16)
+            scan_tc_prep_kernel<true><<<(nqt + 7) / 8, 256, 0, stream>>>(q_dev, nq, d, nqt, kp, Q, nullptr, steps, l2 ? 1 : 0,
+                                                                        max_norm_ord, band, flags);
+        else
+            scan_tc_prep_kernel<false><<<(nqt + 7) / 8, 256, 0, stream>>>(q_dev, nq, d, nqt, kp, Q, l2 ? nullptr : static_cast<float*>(Qx),
+                                                                         steps, l2 ? 1 : 0, max_norm_ord, band, flags);
+        B2_COUNT_LAUNCH();
+        if (cudaGetLastError() != cudaSuccess) {
+            set_error("tensor-core scan: query preparation launch failed");
+            rc = B2_ERR_CUDA;
+        }
     }
-    if (rc == B2_OK) rc = prep_queries(q_dev, nq, d, nqt, kp, 1, bf16, Q, nullptr, nullptr, stream);
-    if (rc == B2_OK)
-        rc = compute_band(q_dev, nq, d, nqt, bf16 ? kp / 16 : kp / 8, bf16, l2, max_norm_ord, nullptr, band, stream);
     if (rc == B2_OK) {
         if (bf16)
             rc = nqt == 16 ? launch_scan_tc<0, 16, true>(tmRows, tmQ, p, grid, smem, stream)
@@ -527,8 +577,7 @@ static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes
         cudaFreeAsync(blk, stream);
         return rc;
     }
-    if (rc == B2_OK) rc = prep_queries(q_dev, nq, d, nqt, kp, 2, false, Qx, nullptr, nullptr, stream);
-    if (rc == B2_OK) {
+    if (rc == B2_OK) {  // Qx was written by scan_tc_prep_kernel
         ScanTcParams px = p;
         px.klist = k;
         px.sps = 1;

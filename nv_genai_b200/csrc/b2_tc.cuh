@@ -187,6 +187,28 @@ __device__ __forceinline__ void umma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, u
         ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(acc)
         : "memory");
 }
+// band = 2 x a rigorous bound on |approximate key - exact key| over all stored rows for one-product tensor-core
+// scoring of a query (see band_kernel in b2_gemm.cu for the terms): ss = |q~|^2 and se = |q - q~|^2 of the rounded
+// query q~, max_norm = largest squared row norm, row_err = largest |x - x~|^2 when the rows are read through a rounded
+// copy (0 otherwise), steps = accumulation steps of the tensor core (its accumulate truncates: <= 2^-21 |q||x| per
+// step, measured ~2^-24), tf32_rows = the row operand is truncated to tf32 by the tensor core (2^-10 relative).
+__device__ __forceinline__ float band_from_sums(float ss, float se, bool tf32_rows, int steps, bool l2, int d, float max_norm,
+                                                float row_err) {
+    float xn = sqrtf(fmaxf(max_norm, 0.f)) * 1.0001f;
+    const float qn = sqrtf(ss) * 1.0001f, qe = sqrtf(se) * 1.0001f;
+    // rows replaced by a rounded copy x~ (bf16 shadow of fp32 rows): |q.x - q~.x~| <= |q~| |x - x~| + |q - q~| |x~|
+    const float xe = sqrtf(fmaxf(row_err, 0.f)) * 1.0001f;
+    xn += xe;
+    float err = qe * xn + qn * xe;
+    if (tf32_rows) err += qn * xn * 0.0009765625f;               // the row operand is truncated to tf32: 2^-10
+    err += (float)steps * 4.76837158e-7f * qn * xn;              // accumulation: steps x 2^-21
+    float b = 2.f * err * 1.001f + 1e-30f;
+    // L2 keys are 2 q.x - |x|^2: twice the product error, plus the rounding of the stored squared norm and of the
+    // fp32 distance the candidates are finally ranked by (sums of d squares: relative error below d * 2^-24 of
+    // at most (|q| + |x|)^2)
+    if (l2) b = 2.f * b + 2.f * (xn + qn) * (xn + qn) * (float)d * 5.9604645e-8f;
+    return b;
+}
 #endif  // __CUDACC__
 
 // ------------------------------------------------------------------ host side: TMA tensor maps
