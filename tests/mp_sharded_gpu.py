@@ -67,11 +67,21 @@ def main():
                     if rank == 0 and rep == 0:
                         report["cases"].append({"dtype": dtype, "peer": use_peer, "peer_active": peer_active,
                                                 "nq": nq, "k": k, "equal": same_all})
-            # non-replicated queries: rank 0 owns the batch
-            qq = q[:5].contiguous() if rank == 0 else torch.zeros((5, d), dtype=torch.float32, device=dev)
-            D, I = sh.search(qq, 10, replicated=False, src=0)
-            Dw, Iw = whole.search(q[:5].contiguous(), 10)
-            ok = ok and bool(torch.equal(I, Iw)) and bool(torch.equal(D, Dw))
+            # non-replicated queries: rank 0 owns the batch (through peer memory when the exchange is active, else by
+            # broadcast); several in a row so that both buffer sets are used, and into a packed output block
+            for rep in range(5):
+                nq1 = (5, 1, 16, 2, 64)[rep]
+                qq = q[rep:rep + nq1].contiguous() if rank == 0 else torch.zeros((nq1, d), dtype=torch.float32, device=dev)
+                packed = torch.empty(nq1 * 10 * 12, dtype=torch.uint8, device=dev) if rep % 2 == 0 else None
+                D, I = sh.search(qq, 10, replicated=False, src=0, out=packed)
+                Dw, Iw = whole.search(q[rep:rep + nq1].contiguous(), 10)
+                same = bool(torch.equal(I, Iw)) and bool(torch.equal(D, Dw))
+                if packed is not None:
+                    same = same and bool(torch.equal(packed[: nq1 * 80].view(torch.int64).view(nq1, 10), Iw))
+                    same = same and bool(torch.equal(packed[nq1 * 80:].view(torch.float32).view(nq1, 10), Dw))
+                if rank == 0:
+                    report["cases"].append({"dtype": dtype, "peer": use_peer, "non_replicated_nq": nq1, "equal": same})
+                ok = ok and same
             if use_peer and not peer_active and rank == 0:
                 report["peer_error"] = getattr(sh, "_peer_error", "disabled")
             del sh
