@@ -32,12 +32,22 @@ def _adversarial(d, nq, seed):
     return np.ascontiguousarray(x, dtype=np.float32), np.ascontiguousarray(q, dtype=np.float32)
 
 
-def _check(I, x_stored, q, k, metric_ip):
-    x64, q64 = x_stored.astype(np.float64), q.astype(np.float64)
-    s = q64 @ x64.T if metric_ip else -((q64 ** 2).sum(1)[:, None] + (x64 ** 2).sum(1)[None, :] - 2.0 * (q64 @ x64.T))
-    d = x_stored.shape[1]
-    qn, xn = np.linalg.norm(q64, axis=1), np.linalg.norm(x64, axis=1).max()
-    for r in range(q.shape[0]):
+def _scores64(x_stored, q, metric_ip):
+    """float64 keys (larger = better) of every (query, row) pair, plus |q| per query and the largest |x|."""
+    q64 = q.astype(np.float64)
+    s = np.empty((q.shape[0], x_stored.shape[0]), dtype=np.float64)
+    xn2 = np.empty(x_stored.shape[0], dtype=np.float64)
+    for r0 in range(0, x_stored.shape[0], 20_000):  # blockwise: the float64 copy of all rows would be 3 GB at d = 4096
+        xb = x_stored[r0:r0 + 20_000].astype(np.float64)
+        s[:, r0:r0 + 20_000] = q64 @ xb.T
+        xn2[r0:r0 + 20_000] = (xb ** 2).sum(1)
+    if not metric_ip:
+        s = -((q64 ** 2).sum(1)[:, None] + xn2[None, :] - 2.0 * s)
+    return s, np.linalg.norm(q64, axis=1), np.sqrt(xn2.max())
+
+
+def _check(I, s, qn, xn, d, k, metric_ip):
+    for r in range(I.shape[0]):
         # fp32 re-scoring noise of a d-term dot product whose terms are as large as |q||x| / sqrt(d)
         tol = 8.0 * np.sqrt(d) * 2.0 ** -24 * qn[r] * xn * (1.0 if metric_ip else 4.0)
         kth = np.partition(s[r], -k)[-k]
@@ -47,7 +57,6 @@ def _check(I, x_stored, q, k, metric_ip):
         must = np.nonzero(s[r] > kth + tol)[0]
         missing = set(must.tolist()) - set(got.tolist())
         assert not missing, (r, sorted(missing)[:5], kth, tol)
-    return s
 
 
 @pytest.mark.parametrize("d", [1024, 4096])
@@ -67,6 +76,7 @@ def test_band_covers_cancelling_partial_sums(d, mode, metric_ip):
         idx.set_option("bf16_shadow", 0)
     idx.add(x)
     stored = flat.round_bf16(x) if mode == "bf16" else x
+    s, qn, xn = _scores64(stored, q, metric_ip)
     for nq, k in ((64, 10), (64, 100), (16, 10), (5, 10)):  # GEMM filter-and-refine, tensor-core scan (approximate)
         D, I = idx.search(q[:nq], k)
-        _check(I, stored, q[:nq], k, metric_ip)
+        _check(I, s[:nq], qn, xn, d, k, metric_ip)
