@@ -577,7 +577,9 @@ def run_b200(a):
         import torch.distributed as dist
 
         if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
+            # rank 0 prints ONE JSON line on stdout: NCCL's own lines (its version banner) go to the debug file
+            os.environ["NCCL_DEBUG"] = "WARN"
+            os.environ.setdefault("NCCL_DEBUG_FILE", os.devnull)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     assert world == a.gpus, f"--gpus {a.gpus} but WORLD_SIZE={world}: launch N>1 with torchrun"
 

@@ -7,6 +7,7 @@
 #include <mutex>
 #include <shared_mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "b2_common.cuh"
@@ -246,6 +247,61 @@ struct b2_index {
     std::shared_mutex mu;
 };
 
+// ------------------------------------------------------------------ host ingest: library-owned pinned staging ring
+// A caller of the reference API hands over pageable numpy rows (np.array(embeddings, dtype=np.float32) in
+// langchain's FAISS.__add).  A cudaMemcpyAsync from pageable memory is staged by the driver through a small pinned
+// buffer by one thread and does not overlap anything; here the rows are copied by a few host threads into a ring of
+// pinned slots owned by the library (one ring per device, allocated by the first large pageable add), each slot is
+// sent by DMA on a copy stream as soon as it is full, and the ingest kernel of chunk i runs on the caller's stream
+// while chunk i + 1 is on the wire.  Pinned (or registered) sources skip the ring and are sent from where they are.
+namespace {
+struct PinnedRing {
+    static constexpr int kSlots = 4;
+    static constexpr size_t kSlotBytes = (size_t)32 << 20;
+    std::mutex mu;  // one host add per device stages through the ring at a time
+    char* slot[kSlots] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t drained[kSlots] = {nullptr, nullptr, nullptr, nullptr};  // the DMA out of the slot has finished
+    bool tried = false, ok = false;
+    bool ensure() {  // with the ring's device current
+        if (tried) return ok;
+        tried = true;
+        ok = true;
+        for (int i = 0; i < kSlots && ok; ++i) {
+            ok = cudaHostAlloc(reinterpret_cast<void**>(&slot[i]), kSlotBytes, cudaHostAllocPortable) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&drained[i], cudaEventDisableTiming) == cudaSuccess;
+        }
+        if (!ok) {
+            cudaGetLastError();
+            for (int i = 0; i < kSlots; ++i) {
+                if (slot[i]) cudaFreeHost(slot[i]);
+                if (drained[i]) cudaEventDestroy(drained[i]);
+                slot[i] = nullptr;
+                drained[i] = nullptr;
+            }
+        }
+        return ok;
+    }
+};
+PinnedRing g_rings[64];
+
+void parallel_copy(char* dst, const char* src, size_t bytes) {
+    static const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const unsigned T = bytes < ((size_t)4 << 20) ? 1u : std::min(4u, hw);
+    if (T == 1) {
+        memcpy(dst, src, bytes);
+        return;
+    }
+    std::thread th[4];
+    const size_t part = ((bytes / T) + 4095) & ~(size_t)4095;
+    for (unsigned t = 1; t < T; ++t) {
+        const size_t off = std::min(bytes, part * t), len = std::min(bytes - off, part);
+        th[t] = std::thread([=] { if (len) memcpy(dst + off, src + off, len); });
+    }
+    memcpy(dst, src, std::min(bytes, part));
+    for (unsigned t = 1; t < T; ++t) th[t].join();
+}
+}  // namespace
+
 static size_t row_pitch_bytes(int d, int dtype) {
     const size_t raw = (size_t)d * (dtype == B2_DTYPE_BF16 ? 2 : 4);
     return ((raw + 511) / 512) * 512;
@@ -445,40 +501,94 @@ int b2_index_add(b2_index* h, int64_t n, const float* x, int x_where, unsigned f
     if (x_where == B2_DEVICE) {
         B2_TRY(ingest_rows(x, n, h->d, dst, h->pitch, h->dtype, normalize, nrm, stream));
     } else {
-        // host rows: staged through two device buffers so the copy of chunk i+1 can be queued
-        // while chunk i is converted (pinned sources make the copies truly asynchronous)
         const size_t row_bytes = (size_t)h->d * sizeof(float);
-        int64_t chunk = std::max<int64_t>(1, (int64_t)(((size_t)64 << 20) / row_bytes));
-        chunk = std::min(chunk, n);
-        float* stage[2] = {nullptr, nullptr};
-        B2_CUDA_TRY(cudaMallocAsync(&stage[0], (size_t)chunk * row_bytes, stream));
-        if (n > chunk) {
-            cudaError_t e = cudaMallocAsync(&stage[1], (size_t)chunk * row_bytes, stream);
-            if (e != cudaSuccess) {
-                cudaFreeAsync(stage[0], stream);
-                set_error("b2_index_add: staging allocation failed: %s", cudaGetErrorString(e));
-                return B2_ERR_OOM;
-            }
-        }
-        int rc = B2_OK;
-        int which = 0;
-        for (int64_t off = 0; off < n && rc == B2_OK; off += chunk) {
-            const int64_t m = std::min(chunk, n - off);
-            float* sb = stage[which];
-            cudaError_t e = cudaMemcpyAsync(sb, x + (size_t)off * h->d, (size_t)m * row_bytes, cudaMemcpyHostToDevice, stream);
+        const size_t total_bytes = (size_t)n * row_bytes;
+        if (total_bytes <= ((size_t)8 << 20) || row_bytes > PinnedRing::kSlotBytes) {
+            // a few documents at a time (the usual langchain add): one staged copy on the caller's stream
+            float* sb = nullptr;
+            B2_CUDA_TRY(cudaMallocAsync(&sb, total_bytes, stream));
+            cudaError_t e = cudaMemcpyAsync(sb, x, total_bytes, cudaMemcpyHostToDevice, stream);
+            int rc = B2_OK;
             if (e != cudaSuccess) {
                 set_error("b2_index_add: H2D copy failed: %s", cudaGetErrorString(e));
                 rc = B2_ERR_CUDA;
-                break;
+            } else {
+                rc = ingest_rows(sb, n, h->d, dst, h->pitch, h->dtype, normalize, nrm, stream);
             }
-            rc = ingest_rows(sb, m, h->d, dst + (size_t)off * h->pitch, h->pitch, h->dtype, normalize, nrm + off, stream);
-            if (stage[1] != nullptr) which ^= 1;
+            cudaFreeAsync(sb, stream);
+            if (rc != B2_OK) return rc;
+            B2_CUDA_TRY(cudaStreamSynchronize(stream));  // the caller may reuse its host buffer as soon as we return
+        } else {
+            // bulk load: chunks of one ring slot, copy stream + compute stream, two device staging buffers
+            cudaPointerAttributes pa;
+            bool pinned_src = cudaPointerGetAttributes(&pa, x) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+            cudaGetLastError();
+            PinnedRing& ring = g_rings[h->device & 63];
+            std::unique_lock<std::mutex> ring_lk(ring.mu, std::defer_lock);
+            bool use_ring = false;
+            if (!pinned_src && getenv("B2_NO_PINNED_RING") == nullptr) {
+                ring_lk.lock();
+                use_ring = ring.ensure();
+                if (!use_ring) ring_lk.unlock();  // no pinned memory to be had: the driver's own staging
+            }
+            const int64_t chunk = std::max<int64_t>(1, (int64_t)(PinnedRing::kSlotBytes / row_bytes));
+            float* stage[2] = {nullptr, nullptr};
+            cudaEvent_t copied[2] = {nullptr, nullptr}, consumed[2] = {nullptr, nullptr}, ready = nullptr;
+            cudaStream_t cs = nullptr;
+            int rc = B2_OK;
+            auto cu = [&](cudaError_t e, const char* what) {
+                if (e != cudaSuccess && rc == B2_OK) {
+                    set_error("b2_index_add: %s: %s", what, cudaGetErrorString(e));
+                    rc = e == cudaErrorMemoryAllocation ? B2_ERR_OOM : B2_ERR_CUDA;
+                }
+                return e == cudaSuccess;
+            };
+            cu(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking), "copy stream");
+            for (int b = 0; b < 2 && rc == B2_OK; ++b) {
+                cu(cudaMallocAsync(&stage[b], (size_t)chunk * row_bytes, stream), "staging allocation");
+                cu(cudaEventCreateWithFlags(&copied[b], cudaEventDisableTiming), "event");
+                cu(cudaEventCreateWithFlags(&consumed[b], cudaEventDisableTiming), "event");
+            }
+            if (rc == B2_OK) {  // the copy stream may touch the staging buffers once their allocation is ordered
+                cu(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming), "event");
+                if (rc == B2_OK) cu(cudaEventRecord(ready, stream), "event record");
+                if (rc == B2_OK) cu(cudaStreamWaitEvent(cs, ready, 0), "stream wait");
+            }
+            int64_t c = 0;
+            for (int64_t off = 0; off < n && rc == B2_OK; off += chunk, ++c) {
+                const int64_t m = std::min(chunk, n - off);
+                const size_t bytes = (size_t)m * row_bytes;
+                const int b = (int)(c & 1);
+                const char* src = reinterpret_cast<const char*>(x) + (size_t)off * row_bytes;
+                if (c >= 2) cu(cudaStreamWaitEvent(cs, consumed[b], 0), "stream wait");  // chunk c - 2 has been ingested
+                if (use_ring) {
+                    const int sl = (int)(c % PinnedRing::kSlots);
+                    if (c >= PinnedRing::kSlots) cu(cudaEventSynchronize(ring.drained[sl]), "ring wait");
+                    parallel_copy(ring.slot[sl], src, bytes);
+                    cu(cudaMemcpyAsync(stage[b], ring.slot[sl], bytes, cudaMemcpyHostToDevice, cs), "H2D copy");
+                    cu(cudaEventRecord(ring.drained[sl], cs), "event record");
+                } else {
+                    cu(cudaMemcpyAsync(stage[b], src, bytes, cudaMemcpyHostToDevice, cs), "H2D copy");
+                }
+                cu(cudaEventRecord(copied[b], cs), "event record");
+                cu(cudaStreamWaitEvent(stream, copied[b], 0), "stream wait");
+                if (rc == B2_OK)
+                    rc = ingest_rows(stage[b], m, h->d, dst + (size_t)off * h->pitch, h->pitch, h->dtype, normalize, nrm + off, stream);
+                cu(cudaEventRecord(consumed[b], stream), "event record");
+            }
+            // the caller may reuse its host buffer as soon as we return; the staging buffers are freed in stream order
+            if (cs) cudaStreamSynchronize(cs);
+            const cudaError_t es = cudaStreamSynchronize(stream);
+            for (int b = 0; b < 2; ++b) {
+                if (stage[b]) cudaFreeAsync(stage[b], stream);
+                if (copied[b]) cudaEventDestroy(copied[b]);
+                if (consumed[b]) cudaEventDestroy(consumed[b]);
+            }
+            if (ready) cudaEventDestroy(ready);
+            if (cs) cudaStreamDestroy(cs);
+            if (rc != B2_OK) return rc;
+            B2_CUDA_TRY(es);
         }
-        cudaFreeAsync(stage[0], stream);
-        if (stage[1]) cudaFreeAsync(stage[1], stream);
-        if (rc != B2_OK) return rc;
-        // the caller may reuse its host buffer as soon as we return
-        B2_CUDA_TRY(cudaStreamSynchronize(stream));
     }
     B2_TRY(update_max_norm(nrm, n, h->max_norm_ord, stream));
     h->ntotal += n;

@@ -128,3 +128,30 @@ def test_save_load_and_pickle_roundtrip(tmp_path):
         assert back.metric_type == metric and back.ntotal == 1234 and np.array_equal(back.reconstruct_n(), x)
         again = pickle.loads(pickle.dumps(idx))
         assert again.metric_type == metric and np.array_equal(again.reconstruct_n(), x)
+
+
+def test_bulk_host_add_through_the_pinned_ring_and_from_pinned_memory():
+    """More than 8 MB of host rows take the pipelined path of b2_index_add: pageable rows through the library's pinned
+    ring (several slots, chunks that do not divide the input), pinned rows straight from where they are.  Both must
+    store exactly what the one-copy path and the device path store."""
+    import torch
+
+    from nv_genai_b200 import IndexFlatIP
+
+    n, d = 70_001, 768  # 215 MB: seven 32 MB chunks and a ragged tail; rows of 3 KB do not divide a chunk evenly
+    x = flat.synth(0, n, d, 77)
+    ref = IndexFlatIP(d)
+    ref.add(torch.from_numpy(x).cuda(), normalize=True)  # device rows
+    want = ref.reconstruct_n(0, n)
+    a = IndexFlatIP(d)
+    a.add(x, normalize=True)  # pageable numpy
+    assert np.array_equal(a.reconstruct_n(0, n), want)
+    pinned = torch.from_numpy(x).pin_memory()
+    b = IndexFlatIP(d, dtype="bfloat16")
+    b.add(pinned.numpy(), normalize=True)
+    ref16 = IndexFlatIP(d, dtype="bfloat16")
+    ref16.add(torch.from_numpy(x).cuda(), normalize=True)
+    assert np.array_equal(b.reconstruct_n(0, n), ref16.reconstruct_n(0, n))
+    # a second bulk add reuses the ring
+    a.add(x[:40_000], normalize=False)
+    assert a.ntotal == n + 40_000 and np.array_equal(a.reconstruct_n(n, 40_000), x[:40_000])
