@@ -454,7 +454,18 @@ def cfg5(a, device, idx, peak, peak_src):
             dt = time.perf_counter() - t0
             out["ingest_e2e_pinned_host_float32"] = {"rows_per_s": rows / dt, "h2d_gbs": rows * a.dim * 4 / dt / 1e9,
                                                      "note": "PCIe-bound: host rows -> device staging -> fused normalise"}
-            del tmp, host
+            # what a langchain caller passes: pageable numpy rows (np.array(embeddings, dtype=np.float32)); they go
+            # through the library's pinned ring (b2_index_add)
+            pageable = host.numpy().copy()
+            tmp.reset()
+            tmp.add(pageable[:1000], normalize=True)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            tmp.add(pageable, normalize=True)
+            dt = time.perf_counter() - t0
+            out["ingest_e2e_pageable_host_float32"] = {"rows_per_s": rows / dt, "h2d_gbs": rows * a.dim * 4 / dt / 1e9,
+                                                       "note": "pageable numpy rows -> pinned ring (4 host threads) -> DMA -> fused normalise"}
+            del tmp, host, pageable
         del buf
         torch.cuda.empty_cache()
     nq = 256
