@@ -113,15 +113,22 @@ B2_API int b2_index_search(b2_index* h, int64_t nq, const float* q, int q_where,
  *   - limit: query tile (nq rounded up to a power of two) x CTAs launched x k must not exceed
  *     256 Ki candidates, otherwise B2_ERR_UNSUPPORTED (on a 148-SM B200: nq = 16 with k = 100
  *     and nq = 1 with k = 10 fit; nq = 1 with k = 1024 does not).
- *   - the first call on each device looks up the array's device address and the kernel's
- *     launch attributes; make that call before starting any stream capture.
+ *   - set-up happens inside the first calls, not at load time: the first call on each device looks up the
+ *     array's device address (cudaGetSymbolAddress, cached per device), and the first call of each SHAPE - query
+ *     tile (nq rounded up to a power of two), k and d, per metric and row type - makes the CUDA runtime load that
+ *     kernel variant and sets its shared-memory limit (cudaFuncSetAttribute, an occupancy query).  Loading a
+ *     kernel may itself take device memory and synchronise.  So run every shape the service will use once during
+ *     start-up - before the memory is handed over and before any stream capture - or start the process with
+ *     CUDA_MODULE_LOADING=EAGER; after that a call touches neither the allocator nor the module loader.
  *   - all calls share the one array and it keeps the last call's contents.  Nothing in it has
  *     to start at zero (every slot a call reads, the same call has written first), but two
  *     calls whose kernels overlap on the GPU (different streams, or threads) race on it:
  *     serialise them.
- * It always runs the FFMA scan kernel: results are bit-identical to b2_index_search whenever that runs the same
- * kernel (L2; inner product on a row store under 8 GB with up to 4 queries on fp32 rows, 2 on bf16 rows) and
- * within the 1e-5 relative score tolerance where b2_index_search uses the tensor-core scan instead. */
+ * It always runs the FFMA scan kernel.  Results are bit-identical to b2_index_search whenever that runs the same
+ * kernel: on a row store under 8 GB, up to 4 queries on fp32 rows (2 on bf16 rows), or k > 64.  From 5 queries (3 on
+ * bf16 rows) with k <= 64, and for any batch on a store of 8 GB and more, b2_index_search uses the tensor-core scan
+ * for both metrics (re-scored in fp32): the two then agree within the 1e-5 relative score tolerance, and ids inside
+ * a run of scores that tie within it may swap. */
 B2_API int b2_index_search_static(b2_index* h, int64_t nq, const float* q_dev, int k, float* D_dev, int64_t* I_dev,
                            void* stream);
 

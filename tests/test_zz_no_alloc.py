@@ -7,8 +7,10 @@ extra entry point that keeps the scan kernel's per-CTA partial lists in a fixed 
 inside the library image instead of taking them from cudaMallocAsync.
 
 This file checks, through the C ABI only, that the entry point returns what b2_index_search
-returns, on two calls in a row — the second call reuses the array with the first call's
-contents still in it — and that it refuses sizes beyond its fixed scratch with a clear error.
+returns (and what the CPU oracle returns), on two calls in a row — the second call reuses the
+array with the first call's contents still in it — that a call really leaves the device's
+memory pool and free memory untouched, and that it refuses sizes beyond its fixed scratch
+with a clear error.
 The entry point always runs the FFMA scan kernel; b2_index_search runs the same kernel for
 very small batches on a small index (then the comparison is bit for bit) and the tensor-core
 scan for 5..16 queries (3..16 on bf16 rows), where the two agree within the 1e-5 relative
@@ -20,9 +22,44 @@ import ctypes
 import numpy as np
 import pytest
 
+from oracle import flat
 from parity import assert_parity
 
 pytestmark = pytest.mark.gpu
+
+
+class _Pool:
+    """The device's default stream-ordered memory pool (where cudaMallocAsync takes its memory from), read through the
+    CUDA runtime that torch has already loaded."""
+
+    USED_CURRENT, USED_HIGH = 7, 8  # cudaMemPoolAttrUsedMemCurrent / cudaMemPoolAttrUsedMemHigh
+
+    def __init__(self, device=0):
+        self.rt = None
+        for name in ("libcudart.so.12", "libcudart.so"):
+            try:
+                self.rt = ctypes.CDLL(name)
+                break
+            except OSError:
+                continue
+        if self.rt is None:
+            pytest.skip("CUDA runtime library not loadable by name")
+        self.pool = ctypes.c_void_p()
+        assert self.rt.cudaDeviceGetDefaultMemPool(ctypes.byref(self.pool), device) == 0
+
+    def get(self, attr):
+        v = ctypes.c_uint64(0)
+        assert self.rt.cudaMemPoolGetAttribute(self.pool, attr, ctypes.byref(v)) == 0
+        return int(v.value)
+
+    def reset_high(self):
+        v = ctypes.c_uint64(0)
+        assert self.rt.cudaMemPoolSetAttribute(self.pool, self.USED_HIGH, ctypes.byref(v)) == 0
+
+    def free_bytes(self):
+        free, total = ctypes.c_size_t(0), ctypes.c_size_t(0)
+        assert self.rt.cudaMemGetInfo(ctypes.byref(free), ctypes.byref(total)) == 0
+        return int(free.value)
 
 
 def _dev_ptr(t):
@@ -64,6 +101,13 @@ def test_static_scratch_search_equals_the_allocating_search_twice_in_a_row(metri
         N.check(N.lib.b2_synth_fill(_dev_ptr(q), 0, 16, d, 0x5EED0002, 0, None))
         N.check(N.lib.b2_normalize_l2(_dev_ptr(q), 16, d, 0, None))
         torch.cuda.synchronize()
+        # the rows as the index holds them, for the oracle
+        rows = torch.empty((n, d), dtype=torch.float32, device=dev)
+        ids = torch.arange(n, dtype=torch.int64, device=dev)
+        N.check(N.lib.b2_index_reconstruct_batch(h, n, _dev_ptr(ids), N.DEVICE, _dev_ptr(rows), N.DEVICE, None))
+        torch.cuda.synchronize()
+        x_host, q_host = rows.cpu().numpy(), q.cpu().numpy()
+        del rows, ids
 
         # first call: 16 queries, k = 10 (BASELINE config 2 shape); second call: other queries, other k,
         # smaller tile, so it reads a differently shaped region of the array the first call filled
@@ -77,11 +121,56 @@ def test_static_scratch_search_equals_the_allocating_search_twice_in_a_row(metri
                 assert np.array_equal(I0, I1) and np.array_equal(D0, D1), (nq, k)  # bit for bit
             else:
                 assert_parity(D1, I1, D0, I0, metric_ip=(metric_name == "ip"))  # 1e-5 relative, ties may swap
+            # and against the CPU oracle on the stored rows
+            Dr, Ir, _ = flat.search_seq(x_host, q_host[first:first + nq], k,
+                                        flat.METRIC_IP if metric_name == "ip" else flat.METRIC_L2)
+            assert_parity(D1, I1, Dr, Ir, x_host, q_host[first:first + nq], metric_ip=(metric_name == "ip"))
             assert (I1 >= 0).all() and (I1 < n).all()
             if metric_name == "ip":
                 assert np.all(np.diff(D1, axis=1) <= 0)
             else:
                 assert np.all(np.diff(D1, axis=1) >= 0)
+    finally:
+        N.lib.b2_index_destroy(h)
+
+
+def test_static_scratch_search_leaves_the_memory_pool_and_free_memory_untouched():
+    """The property the entry point exists for, observed from outside: across a call of a shape that has run once
+    before, the pool's high-water mark of used bytes does not rise and the device's free memory does not change.
+    b2_index_search over the same queries does raise the mark, which shows that the probe sees such allocations."""
+    import torch
+
+    from nv_genai_b200 import _native as N
+
+    dev = torch.device("cuda", 0)
+    n, d, nq, k = 40_000, 512, 4, 10
+    h = ctypes.c_void_p()
+    N.check(N.lib.b2_index_create(d, N.METRIC_INNER_PRODUCT, N.DTYPE_F32, 0, ctypes.byref(h)))
+    try:
+        x = torch.empty((n, d), dtype=torch.float32, device=dev)
+        N.check(N.lib.b2_synth_fill(_dev_ptr(x), 0, n, d, 0x5EED0001, 0, None))
+        N.check(N.lib.b2_index_add(h, n, _dev_ptr(x), N.DEVICE, N.ADD_NORMALIZE, None))
+        q = torch.empty((nq, d), dtype=torch.float32, device=dev)
+        N.check(N.lib.b2_synth_fill(_dev_ptr(q), 0, nq, d, 0x5EED0002, 0, None))
+        D = torch.empty((nq, k), dtype=torch.float32, device=dev)
+        I = torch.empty((nq, k), dtype=torch.int64, device=dev)
+        # once before: the first call of a shape loads the kernels and sets their launch attributes
+        N.check(N.lib.b2_index_search_static(h, nq, _dev_ptr(q), k, _dev_ptr(D), _dev_ptr(I), None))
+        N.check(N.lib.b2_index_search(h, nq, _dev_ptr(q), N.DEVICE, k, _dev_ptr(D), _dev_ptr(I), N.DEVICE, None))
+        torch.cuda.synchronize()
+        pool = _Pool(0)
+        used0, free0 = pool.get(pool.USED_CURRENT), pool.free_bytes()
+        pool.reset_high()
+        for _ in range(3):
+            N.check(N.lib.b2_index_search_static(h, nq, _dev_ptr(q), k, _dev_ptr(D), _dev_ptr(I), None))
+        torch.cuda.synchronize()
+        assert pool.get(pool.USED_HIGH) <= used0, "b2_index_search_static took memory from the pool"
+        assert pool.get(pool.USED_CURRENT) == used0 and pool.free_bytes() == free0
+        # the allocating entry point is visible to the same probe
+        pool.reset_high()
+        N.check(N.lib.b2_index_search(h, nq, _dev_ptr(q), N.DEVICE, k, _dev_ptr(D), _dev_ptr(I), N.DEVICE, None))
+        torch.cuda.synchronize()
+        assert pool.get(pool.USED_HIGH) > used0
     finally:
         N.lib.b2_index_destroy(h)
 
