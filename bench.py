@@ -464,7 +464,7 @@ def cfg5(a, device, idx, peak, peak_src):
             tmp.add(pageable, normalize=True)
             dt = time.perf_counter() - t0
             out["ingest_e2e_pageable_host_float32"] = {"rows_per_s": rows / dt, "h2d_gbs": rows * a.dim * 4 / dt / 1e9,
-                                                       "note": "pageable numpy rows -> pinned ring (4 host threads) -> DMA -> fused normalise"}
+                                                       "note": "pageable numpy rows -> pinned ring (up to 8 host threads) -> DMA -> fused normalise"}
             del tmp, host, pageable
         del buf
         torch.cuda.empty_cache()

@@ -250,7 +250,7 @@ struct b2_index {
 // ------------------------------------------------------------------ host ingest: library-owned pinned staging ring
 // A caller of the reference API hands over pageable numpy rows (np.array(embeddings, dtype=np.float32) in
 // langchain's FAISS.__add).  A cudaMemcpyAsync from pageable memory is staged by the driver through a small pinned
-// buffer by one thread and does not overlap anything; here the rows are copied by a few host threads into a ring of
+// buffer by one thread and does not overlap anything; here the rows are copied by up to 8 host threads into a ring of
 // pinned slots owned by the library (one ring per device, allocated by the first large pageable add), each slot is
 // sent by DMA on a copy stream as soon as it is full, and the ingest kernel of chunk i runs on the caller's stream
 // while chunk i + 1 is on the wire.  Pinned (or registered) sources skip the ring and are sent from where they are.
@@ -286,12 +286,12 @@ PinnedRing g_rings[64];
 
 void parallel_copy(char* dst, const char* src, size_t bytes) {
     static const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-    const unsigned T = bytes < ((size_t)4 << 20) ? 1u : std::min(4u, hw);
+    const unsigned T = bytes < ((size_t)4 << 20) ? 1u : std::min(8u, std::max(1u, hw / 2));
     if (T == 1) {
         memcpy(dst, src, bytes);
         return;
     }
-    std::thread th[4];
+    std::thread th[8];
     const size_t part = ((bytes / T) + 4095) & ~(size_t)4095;
     for (unsigned t = 1; t < T; ++t) {
         const size_t off = std::min(bytes, part * t), len = std::min(bytes - off, part);

@@ -556,9 +556,12 @@ static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes
                            pitch_bytes, dtype, norms, band, push, flags, l2);
     // ---- exact fix-up for the flagged queries (each kernel returns immediately when there is none)
     if (rc == B2_OK && l2) {
-        // L2: the FFMA scan (direct form), a pass per 16 queries
-        for (int off = 0; off < nq && rc == B2_OK; off += 16) {
-            const int valid = std::min(16, nq - off);
+        // L2: the FFMA scan (direct form), a pass per query tile: 16 queries, or fewer when rows are so long that 16
+        // query rows do not fit its shared memory (d = 4096: 8)
+        int tmax = 16;
+        while (tmax > 1 && scan_smem_bytes(tmax, (int)(pitch_bytes / 512), bf16, next_pow2(k < 32 ? 32 : k)) > 200 * 1024) tmax >>= 1;
+        for (int off = 0; off < nq && rc == B2_OK; off += tmax) {
+            const int valid = std::min(tmax, nq - off);
             uint64_t* part = nullptr;
             int g2 = 0;
             rc = scan_pass(rows, n, pitch_bytes, d, dtype, B2_METRIC_L2, q_dev + (size_t)off * d, valid,
