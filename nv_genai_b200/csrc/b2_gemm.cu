@@ -1137,7 +1137,7 @@ static int gemm_search_cg(const void* rows, int64_t n, size_t pitch_bytes, int d
 static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric,
                               const float* norms, const uint32_t* max_norm_ord, const float* q_dev, int64_t nq, int k,
                               int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push, int cg,
-                              const ApproxRows* approx);
+                              const ApproxRows* approx, const ResidualRows* resid);
 
 bool gemm_uses_refine(int query_parts, const uint32_t* max_norm_ord) {
     bool refine = max_norm_ord != nullptr && query_parts == 0 && getenv("B2_GEMM_QUERY_PARTS") == nullptr;
@@ -1147,20 +1147,26 @@ bool gemm_uses_refine(int query_parts, const uint32_t* max_norm_ord) {
 
 int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* norms,
                 const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream,
-                const PeerPush* push, int query_parts, const uint32_t* max_norm_ord, const ApproxRows* approx) {
+                const PeerPush* push, int query_parts, const uint32_t* max_norm_ord, const ApproxRows* approx,
+                const ResidualRows* resid) {
     // Filter and refine (default): one approximate product on the tensor cores, exact re-scoring of the few
     // candidates near the cut.  An explicit number of query parts (option / environment) selects the all-exact
     // tensor-core arithmetic instead, as does B2_GEMM_REFINE=0.
     const bool refine = gemm_uses_refine(query_parts, max_norm_ord);
     if (dtype == B2_DTYPE_BF16) approx = nullptr;
+    if (dtype != B2_DTYPE_BF16) resid = nullptr;
+    if (resid != nullptr && !refine) {
+        set_error("tensor-core search: rows with a residual plane need the filter-and-refine mode");
+        return B2_ERR_UNSUPPORTED;
+    }
     if (refine) {
         int cgr = (num_sms % 2 == 0) ? 2 : 1;
         if (const char* e = getenv("B2_GEMM_CTA_GROUP")) cgr = (atoi(e) == 2 && num_sms % 2 == 0) ? 2 : 1;
         int rc = gemm_search_refine(rows, n, pitch_bytes, d, dtype, metric, norms, max_norm_ord, q_dev, nq, k, num_sms, D,
-                                    I, stream, push, cgr, approx);
+                                    I, stream, push, cgr, approx, resid);
         if (rc == B2_ERR_UNSUPPORTED && cgr == 2)
             rc = gemm_search_refine(rows, n, pitch_bytes, d, dtype, metric, norms, max_norm_ord, q_dev, nq, k, num_sms,
-                                    D, I, stream, push, 1, approx);
+                                    D, I, stream, push, 1, approx, resid);
         return rc;
     }
     // CTA pairs (cta_group::2) for bf16 rows when the SM count is even.  Measured at 10M x 1024, nq = 4096, k = 100:
@@ -1335,7 +1341,7 @@ static int launch_gemm_cg(const CUtensorMap& tmA, const CUtensorMap& tmB, const 
 static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric,
                               const float* norms, const uint32_t* max_norm_ord, const float* q_dev, int64_t nq, int k,
                               int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push, int cg,
-                              const ApproxRows* approx) {
+                              const ApproxRows* approx, const ResidualRows* resid) {
     const bool bf16 = dtype == B2_DTYPE_BF16;
     const int elem = bf16 ? 2 : 4;
     // the approximate pass reads bf16 operands when the rows are bf16 or a bf16 shadow of the fp32 rows exists
@@ -1396,7 +1402,7 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     // k * z * band / sigma for scores with a Gaussian tail: ~0.4 k on 1024-d unit vectors with bf16 queries); a
     // segment that overflows the list is flagged and redone by the exact fix-up launch, so this is a speed knob only.
     int slack = std::max(48, 32 + 5 * k / 4);
-    if (approx != nullptr) slack = std::max(64, 32 + 3 * k);  // the band also covers the rows' bf16 rounding: ~2.3x wider
+    if (approx != nullptr || resid != nullptr) slack = std::max(64, 32 + 3 * k);  // the band also covers the rows' bf16 rounding: ~2.3x wider
     if (const char* e = std::getenv("B2_GEMM_LIST_SLACK")) slack = std::max(8, std::min(1024 - k - 8, atoi(e)));
     p.list_len = ((k + slack) + 7) / 8 * 8;
 
@@ -1503,7 +1509,7 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     if (rc == B2_OK) rc = prep_queries(q_dev, (int)nq, d, p.nq_pad, kp_x, 2, bf16, Ax, nullptr, nullptr, stream, bf16 ? 0 : swb_x / 4);
     if (rc == B2_OK)
         rc = compute_band(q_dev, (int)nq, d, p.nq_pad, abf16 ? kp / 16 : kp / 8, abf16, metric == B2_METRIC_L2, max_norm_ord,
-                          approx != nullptr ? approx->err_ord : nullptr, band, stream);
+                          approx != nullptr ? approx->err_ord : (resid != nullptr ? resid->err_ord : nullptr), band, stream);
     p.rcap = pick_rcap(false, 1, swb, stages, k, cg, 0);
     const size_t smem = gemm_smem_slots(false, 1, swb, stages, p.rcap + 1, cg, 0);
     static const bool debug_t = std::getenv("B2_GEMM_DEBUG") != nullptr;
@@ -1589,7 +1595,22 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
                      st[6] / units / 1e6, st[0] / units / 1e6, st[1] / units / 1e6, st[2] / (double)grid / 1e6,
                      st[3] / lanes, st[4] / lanes, st[8] / lanes, p.rcap, st[5] / ((double)p.n_items * cg * 4), st[7] / units / 1e6);
     }
-    if (rc == B2_OK) {  // fix-up: the all-exact kernel over the flagged query groups only (normally none)
+    if (rc == B2_OK && resid != nullptr) {
+        // Rows with a residual plane have no all-exact tensor arithmetic (it would score against the main plane alone):
+        // if a list overflowed - dense score ties, normally never - the caller redoes the batch with the two-plane
+        // FFMA scan.  Costs one synchronisation per search in this mode.
+        std::vector<uint32_t> fl((size_t)p.n_qt);
+        cudaError_t e = cudaMemcpyAsync(fl.data(), p.flags, fl.size() * 4, cudaMemcpyDeviceToHost, stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess) {
+            set_error("tensor-core search: reading the overflow flags failed: %s", cudaGetErrorString(e));
+            rc = B2_ERR_CUDA;
+        } else {
+            for (uint32_t f : fl)
+                if (f != 0u) rc = B2_INTERNAL_REDO_EXACT;
+        }
+    }
+    if (rc == B2_OK && resid == nullptr) {  // fix-up: the all-exact kernel over the flagged query groups only (normally none)
         GemmParams px = p;
         px.refine = 0;
         px.only_flagged = 1;
@@ -1615,7 +1636,8 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     if (debug) cudaEventRecord(dbg_ev[2], stream);
     if (rc == B2_OK)
         rc = merge_rescore(p.partial, (int)nq, p.n_lists, p.list_len, k, metric, D, I, (size_t)k, stream,
-                           metric == B2_METRIC_L2 ? qn : nullptr, q_dev, d, rows, pitch_bytes, dtype, norms, band, push);
+                           metric == B2_METRIC_L2 ? qn : nullptr, q_dev, d, rows, pitch_bytes, dtype, norms, band, push, nullptr,
+                           false, resid != nullptr ? resid->rows : nullptr);
     if (debug) {
         cudaEventRecord(dbg_ev[3], stream);
         cudaStreamSynchronize(stream);

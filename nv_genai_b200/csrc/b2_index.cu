@@ -244,8 +244,17 @@ struct b2_index {
     int shadow_enabled = 1;            // option "bf16_shadow"
     int64_t shadow_refused_rows = 0;   // last size the device had no room for (do not retry until the index changes)
     std::mutex shadow_mu;
+    // bf16 rows with a residual plane (option "bf16_residual", set on an empty bf16 index): a second bf16 plane of the
+    // same pitch holds lo = bf16(x - bf16(x)), the row the index stands for is hi + lo (about 16 mantissa bits).  The
+    // tensor-core passes read the main plane only - the scan streams 2 bytes per element as on a plain bf16 store - and
+    // every returned score is re-computed against hi + lo, with the band widened by the residual's norm.
+    RowStore resid;
+    int residual_enabled = 0;
+    uint32_t* resid_err_ord = nullptr;  // device: ordered image of max |lo|^2 over the rows
     std::shared_mutex mu;
 };
+
+static const void* resid_base(const b2_index* h) { return h->residual_enabled ? h->resid.base() : nullptr; }
 
 // ------------------------------------------------------------------ host ingest: library-owned pinned staging ring
 // A caller of the reference API hands over pageable numpy rows (np.array(embeddings, dtype=np.float32) in
@@ -343,6 +352,7 @@ int index_view_lock_shared(b2_index* h, IndexView* v) {
     B2_TRY(check_handle(h));
     h->mu.lock_shared();
     v->rows = h->store.base();
+    v->resid = resid_base(h);
     v->ntotal = h->ntotal;
     v->pitch = h->pitch;
     v->d = h->d;
@@ -441,14 +451,16 @@ int b2_index_create(int d, int metric, int dtype, int device, b2_index** out) {
     } else {
         h->shadow_enabled = 0;
     }
-    if (cudaMalloc(&h->max_norm_ord, 2 * sizeof(uint32_t)) != cudaSuccess ||
-        cudaMemset(h->max_norm_ord, 0, 2 * sizeof(uint32_t)) != cudaSuccess) {  // 0 orders below every float
+    h->resid.init(device);
+    if (cudaMalloc(&h->max_norm_ord, 3 * sizeof(uint32_t)) != cudaSuccess ||
+        cudaMemset(h->max_norm_ord, 0, 3 * sizeof(uint32_t)) != cudaSuccess) {  // 0 orders below every float
         cudaGetLastError();
         delete h;
         set_error("out of device memory");
         return B2_ERR_OOM;
     }
     h->shadow_err_ord = h->max_norm_ord + 1;
+    h->resid_err_ord = h->max_norm_ord + 2;
     *out = h;
     return B2_OK;
 }
@@ -460,6 +472,7 @@ int b2_index_destroy(b2_index* h) {
         cudaDeviceSynchronize();
         h->store.release();
         h->shadow.release();
+        h->resid.release();
         if (h->shadow_ev) cudaEventDestroy(h->shadow_ev);
         if (h->norms) cudaFree(h->norms);
         if (h->max_norm_ord) cudaFree(h->max_norm_ord);
@@ -494,12 +507,15 @@ int b2_index_add(b2_index* h, int64_t n, const float* x, int x_where, unsigned f
         return B2_ERR_CUDA;
     }
     B2_TRY(h->store.ensure((size_t)(h->ntotal + n) * h->pitch, stream));
+    if (h->residual_enabled) B2_TRY(h->resid.ensure((size_t)(h->ntotal + n) * h->pitch, stream));
     B2_TRY(ensure_norms(h, h->ntotal + n, stream));
     const bool normalize = (flags & B2_ADD_NORMALIZE) != 0;
     char* dst = h->store.base() + (size_t)h->ntotal * h->pitch;
+    char* rdst = h->residual_enabled ? h->resid.base() + (size_t)h->ntotal * h->pitch : nullptr;  // advanced like dst
+    uint32_t* rerr = h->residual_enabled ? h->resid_err_ord : nullptr;
     float* nrm = h->norms + h->ntotal;
     if (x_where == B2_DEVICE) {
-        B2_TRY(ingest_rows(x, n, h->d, dst, h->pitch, h->dtype, normalize, nrm, stream));
+        B2_TRY(ingest_rows(x, n, h->d, dst, h->pitch, h->dtype, normalize, nrm, stream, rdst, rerr));
     } else {
         const size_t row_bytes = (size_t)h->d * sizeof(float);
         const size_t total_bytes = (size_t)n * row_bytes;
@@ -513,7 +529,7 @@ int b2_index_add(b2_index* h, int64_t n, const float* x, int x_where, unsigned f
                 set_error("b2_index_add: H2D copy failed: %s", cudaGetErrorString(e));
                 rc = B2_ERR_CUDA;
             } else {
-                rc = ingest_rows(sb, n, h->d, dst, h->pitch, h->dtype, normalize, nrm, stream);
+                rc = ingest_rows(sb, n, h->d, dst, h->pitch, h->dtype, normalize, nrm, stream, rdst, rerr);
             }
             cudaFreeAsync(sb, stream);
             if (rc != B2_OK) return rc;
@@ -573,7 +589,8 @@ int b2_index_add(b2_index* h, int64_t n, const float* x, int x_where, unsigned f
                 cu(cudaEventRecord(copied[b], cs), "event record");
                 cu(cudaStreamWaitEvent(stream, copied[b], 0), "stream wait");
                 if (rc == B2_OK)
-                    rc = ingest_rows(stage[b], m, h->d, dst + (size_t)off * h->pitch, h->pitch, h->dtype, normalize, nrm + off, stream);
+                    rc = ingest_rows(stage[b], m, h->d, dst + (size_t)off * h->pitch, h->pitch, h->dtype, normalize, nrm + off, stream,
+                                     rdst ? rdst + (size_t)off * h->pitch : nullptr, rerr);
                 cu(cudaEventRecord(consumed[b], stream), "event record");
             }
             // the caller may reuse its host buffer as soon as we return; the staging buffers are freed in stream order
@@ -675,15 +692,24 @@ static int search_device(b2_index* h, int64_t nq, const float* q_dev, int k, flo
         return B2_OK;
     }
     const bool tc_approx = h->gemm_query_parts == 0 && h->max_norm_ord != nullptr;
-    if (scan_tc_supported(h->ntotal, h->d, h->dtype, h->metric, k, nq, tc_approx))
+    // bf16 rows with a residual plane: the tensor-core paths only in their filter-and-refine form (the all-exact
+    // tensor arithmetic would score against the main plane alone); everything else runs the two-plane FFMA scan below
+    ResidualRows rr;
+    rr.rows = resid_base(h);
+    rr.err_ord = h->resid_err_ord;
+    const ResidualRows* resid = h->residual_enabled ? &rr : nullptr;
+    const bool tc_ok = resid == nullptr || (tc_approx && k <= 64 && scan_tc_approx_feasible(h->ntotal, k, h->num_sms));
+    if (tc_ok && scan_tc_supported(h->ntotal, h->d, h->dtype, h->metric, k, nq, tc_approx, resid != nullptr))
         return scan_tc_search(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, q_dev, (int)nq, k, h->num_sms,
-                              D_dev, I_dev, stream, push, tc_approx ? h->max_norm_ord : nullptr, h->metric, h->norms);
-    if (gemm_path_supported(h->ntotal, h->d, h->dtype, k, nq)) {
+                              D_dev, I_dev, stream, push, tc_approx ? h->max_norm_ord : nullptr, h->metric, h->norms, resid);
+    if (gemm_path_supported(h->ntotal, h->d, h->dtype, k, nq) &&
+        (resid == nullptr || gemm_uses_refine(h->gemm_query_parts, h->max_norm_ord))) {
         ApproxRows approx;
         const bool shadowed = gemm_uses_refine(h->gemm_query_parts, h->max_norm_ord) && ensure_shadow(h, stream, &approx);
-        return gemm_search(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, h->metric, h->norms, q_dev, nq, k,
-                           h->num_sms, D_dev, I_dev, stream, push, h->gemm_query_parts, h->max_norm_ord,
-                           shadowed ? &approx : nullptr);
+        const int rc = gemm_search(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, h->metric, h->norms, q_dev, nq, k,
+                                   h->num_sms, D_dev, I_dev, stream, push, h->gemm_query_parts, h->max_norm_ord,
+                                   shadowed ? &approx : nullptr, resid);
+        if (rc != B2_INTERNAL_REDO_EXACT) return rc;
     }
     const int kpad = next_pow2(k < 32 ? 32 : k);
     const int tmax = max_query_tile(h, kpad);
@@ -698,7 +724,7 @@ static int search_device(b2_index* h, int64_t nq, const float* q_dev, int k, flo
         uint64_t* partial = nullptr;
         int grid = 0;
         B2_TRY(scan_pass(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, h->metric, q_dev + (size_t)off * h->d,
-                         valid, tile, k, h->num_sms, stream, &partial, &grid));
+                         valid, tile, k, h->num_sms, stream, &partial, &grid, nullptr, resid_base(h)));
         PeerPush pp;
         if (push != nullptr) {
             pp = *push;
@@ -933,7 +959,7 @@ int b2_index_reconstruct_batch(b2_index* h, int64_t n, const int64_t* ids, int i
         B2_CUDA_TRY(cudaMallocAsync(&out_tmp, (size_t)n * h->d * 4, stream));
         out_dev = out_tmp;
     }
-    int rc = gather_rows(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, ids_dev, n, out_dev, stream);
+    int rc = gather_rows(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, ids_dev, n, out_dev, stream, resid_base(h));
     if (rc == B2_OK && out_where == B2_HOST) {
         cudaError_t e = cudaMemcpyAsync(out, out_dev, (size_t)n * h->d * 4, cudaMemcpyDeviceToHost, stream);
         if (e != cudaSuccess) {
@@ -985,6 +1011,8 @@ int b2_index_remove_ids(b2_index* h, int64_t n, const int64_t* ids, int64_t* n_r
             rc = B2_ERR_CUDA;
         } else {
             rc = compact_rows(h->store.base(), h->pitch, h->norms, src_dev, (int64_t)src.size(), first, stream);
+            if (rc == B2_OK && h->residual_enabled)
+                rc = compact_rows(h->resid.base(), h->pitch, nullptr, src_dev, (int64_t)src.size(), first, stream);
         }
         cudaFreeAsync(src_dev, stream);
     }
@@ -1004,9 +1032,11 @@ int b2_index_merge_from(b2_index* dst, b2_index* src) {
         set_error("b2_index_merge_from: cannot merge an index into itself");
         return B2_ERR_INVALID;
     }
-    if (dst->d != src->d || dst->dtype != src->dtype || dst->metric != src->metric) {
-        set_error("b2_index_merge_from: indexes are not compatible (d %d vs %d, dtype %d vs %d, metric %d vs %d)", dst->d,
-                  src->d, dst->dtype, src->dtype, dst->metric, src->metric);
+    if (dst->d != src->d || dst->dtype != src->dtype || dst->metric != src->metric ||
+        dst->residual_enabled != src->residual_enabled) {
+        set_error("b2_index_merge_from: indexes are not compatible (d %d vs %d, dtype %d vs %d, metric %d vs %d, residual "
+                  "plane %d vs %d)", dst->d, src->d, dst->dtype, src->dtype, dst->metric, src->metric,
+                  dst->residual_enabled, src->residual_enabled);
         return B2_ERR_INVALID;
     }
     // both writer locks, taken together without an order: merge(a, b) next to merge(b, a) must not deadlock
@@ -1023,6 +1053,22 @@ int b2_index_merge_from(b2_index* dst, b2_index* src) {
     cudaStream_t stream = nullptr;
     B2_TRY(dst->store.ensure((size_t)(dst->ntotal + n) * dst->pitch, stream));
     B2_TRY(ensure_norms(dst, dst->ntotal + n, stream));
+    if (dst->residual_enabled) {
+        B2_TRY(dst->resid.ensure((size_t)(dst->ntotal + n) * dst->pitch, stream));
+        char* rto = dst->resid.base() + (size_t)dst->ntotal * dst->pitch;
+        if (dst->device == src->device)
+            B2_CUDA_TRY(cudaMemcpyAsync(rto, src->resid.base(), (size_t)n * dst->pitch, cudaMemcpyDeviceToDevice, stream));
+        else
+            B2_CUDA_TRY(cudaMemcpyPeerAsync(rto, dst->device, src->resid.base(), src->device, (size_t)n * dst->pitch, stream));
+        // the destination's error bound must cover the rows it receives
+        uint32_t e_src = 0, e_dst = 0;
+        {
+            DeviceGuard gs(src->device);
+            B2_CUDA_TRY(cudaMemcpy(&e_src, src->resid_err_ord, 4, cudaMemcpyDeviceToHost));
+        }
+        B2_CUDA_TRY(cudaMemcpy(&e_dst, dst->resid_err_ord, 4, cudaMemcpyDeviceToHost));
+        if (e_src > e_dst) B2_CUDA_TRY(cudaMemcpy(dst->resid_err_ord, &e_src, 4, cudaMemcpyHostToDevice));
+    }
     char* to = dst->store.base() + (size_t)dst->ntotal * dst->pitch;
     if (dst->device == src->device) {
         B2_CUDA_TRY(cudaMemcpyAsync(to, src->store.base(), (size_t)n * dst->pitch, cudaMemcpyDeviceToDevice, stream));
@@ -1053,6 +1099,21 @@ int b2_index_set_option(b2_index* h, const char* name, int64_t value) {
             return B2_ERR_INVALID;
         }
         h->gemm_query_parts = (int)value;
+        return B2_OK;
+    }
+    if (strcmp(name, "bf16_residual") == 0) {
+        if (value != 0 && value != 1) {
+            set_error("b2_index_set_option: bf16_residual must be 0 or 1");
+            return B2_ERR_INVALID;
+        }
+        std::unique_lock<std::shared_mutex> lk(h->mu);
+        if ((int)value == h->residual_enabled) return B2_OK;
+        if (h->dtype != B2_DTYPE_BF16 || h->ntotal != 0) {
+            set_error("b2_index_set_option: bf16_residual can only be changed on an EMPTY bf16 index (dtype %d, %lld rows)",
+                      h->dtype, (long long)h->ntotal);
+            return B2_ERR_INVALID;
+        }
+        h->residual_enabled = (int)value;
         return B2_OK;
     }
     if (strcmp(name, "bf16_shadow") == 0) {
@@ -1140,7 +1201,7 @@ int b2_index_mmr(b2_index* h, int64_t nq, const float* q, int q_where, int k, in
         rc = B2_ERR_CUDA;
     }
     if (rc == B2_OK) rc = search_device(h, nq, q_dev, fetch_k, Df, If, stream);
-    if (rc == B2_OK) rc = gather_rows(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, If, (int64_t)nf, rows, stream);
+    if (rc == B2_OK) rc = gather_rows(h->store.base(), h->ntotal, h->pitch, h->d, h->dtype, If, (int64_t)nf, rows, stream, resid_base(h));
     if (rc == B2_OK) rc = mmr_select(q_dev, h->d, (int)nq, rows, If, Df, fetch_k, k, lambda_mult, oi, os, stream);
     if (rc == B2_OK && out_where == B2_HOST) {
         e = cudaMemcpyAsync(out_ids, oi, nk * 8, cudaMemcpyDeviceToHost, stream);

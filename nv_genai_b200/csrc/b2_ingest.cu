@@ -33,13 +33,19 @@ template <bool VEC, bool REGS, bool BF16>
 __global__ void __launch_bounds__(kIngestThreads) ingest_kernel(const float* src, int64_t n, int d,
                                                                size_t src_pitch_elems, char* dst,
                                                                size_t pitch_bytes, int pitch_elems, bool normalize,
-                                                               float* __restrict__ norms) {
+                                                               float* __restrict__ norms, char* resid = nullptr,
+                                                               uint32_t* __restrict__ resid_err_ord = nullptr) {
     const int lane = threadIdx.x & 31;
     const int64_t warp0 = (int64_t)blockIdx.x * kIngestWarps + (threadIdx.x >> 5);
     const int64_t wstride = (int64_t)gridDim.x * kIngestWarps;
     for (int64_t row = warp0; row < n; row += wstride) {
         const float* s = src + row * src_pitch_elems;
         char* o = dst + row * pitch_bytes;
+        // bf16 rows with a residual plane: the row is stored as hi = bf16(x) plus lo = bf16(x - hi) in a second plane
+        // of the same pitch; what the index holds is then hi + lo (exact in fp32), its norm is the one recorded, and
+        // sum lo^2 feeds the running maximum the error band of the filter-and-refine paths needs
+        char* ores = (BF16 && resid != nullptr) ? resid + row * pitch_bytes : nullptr;
+        float se = 0.f;
         float ss = 0.f;
         float4 keep[REGS ? 8 : 1];
         if (VEC) {
@@ -79,7 +85,19 @@ __global__ void __launch_bounds__(kIngestThreads) ingest_kernel(const float* src
                 v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale;
                 if (BF16) {
                     __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
-                    const float2 fa = __bfloat1622float2(a), fb = __bfloat1622float2(b);
+                    float2 fa = __bfloat1622float2(a), fb = __bfloat1622float2(b);
+                    if (ores != nullptr) {
+                        const __nv_bfloat162 la = __floats2bfloat162_rn(v.x - fa.x, v.y - fa.y),
+                                             lb = __floats2bfloat162_rn(v.z - fb.x, v.w - fb.y);
+                        const float2 ga = __bfloat1622float2(la), gb = __bfloat1622float2(lb);
+                        se = fmaf(ga.x, ga.x, se); se = fmaf(ga.y, ga.y, se);
+                        se = fmaf(gb.x, gb.x, se); se = fmaf(gb.y, gb.y, se);
+                        fa.x += ga.x; fa.y += ga.y; fb.x += gb.x; fb.y += gb.y;
+                        uint2 wl;
+                        wl.x = *reinterpret_cast<const uint32_t*>(&la);
+                        wl.y = *reinterpret_cast<const uint32_t*>(&lb);
+                        reinterpret_cast<uint2*>(ores)[c] = wl;
+                    }
                     ss2 = fmaf(fa.x, fa.x, ss2); ss2 = fmaf(fa.y, fa.y, ss2);
                     ss2 = fmaf(fb.x, fb.x, ss2); ss2 = fmaf(fb.y, fb.y, ss2);
                     uint2 w;
@@ -106,8 +124,17 @@ __global__ void __launch_bounds__(kIngestThreads) ingest_kernel(const float* src
                 float v = (c < d) ? s[c] * scale : 0.f;
                 if (BF16) {
                     const __nv_bfloat16 b = __float2bfloat16_rn(v);
-                    v = __bfloat162float(b);
+                    const float hi = __bfloat162float(b);
                     reinterpret_cast<__nv_bfloat16*>(o)[c] = b;
+                    if (ores != nullptr) {
+                        const __nv_bfloat16 l = __float2bfloat16_rn(v - hi);
+                        const float lo = __bfloat162float(l);
+                        reinterpret_cast<__nv_bfloat16*>(ores)[c] = l;
+                        se = fmaf(lo, lo, se);
+                        v = hi + lo;
+                    } else {
+                        v = hi;
+                    }
                 } else {
                     reinterpret_cast<float*>(o)[c] = v;
                 }
@@ -116,12 +143,17 @@ __global__ void __launch_bounds__(kIngestThreads) ingest_kernel(const float* src
         }
         ss2 = warp_sum(ss2);
         if (norms != nullptr && lane == 0) norms[row] = ss2;
+        if (ores != nullptr && resid_err_ord != nullptr) {
+            se = warp_sum(se);
+            if (lane == 0 && se > 0.f) atomicMax(resid_err_ord, f2ord(se * 1.0001f));
+        }
     }
 }
 
 template <bool BF16>
 static int launch_ingest(const float* src, int64_t n, int d, size_t src_pitch_elems, void* dst, size_t pitch_bytes,
-                         bool normalize, float* norms, cudaStream_t stream) {
+                         bool normalize, float* norms, cudaStream_t stream, void* resid = nullptr,
+                         uint32_t* resid_err_ord = nullptr) {
     if (n <= 0) return B2_OK;
     const int pitch_elems = (int)(pitch_bytes / (BF16 ? 2 : 4));
     const bool vec = (d % 4 == 0) && (src_pitch_elems % 4 == 0) && ((reinterpret_cast<uintptr_t>(src) & 15) == 0) &&
@@ -131,22 +163,24 @@ static int launch_ingest(const float* src, int64_t n, int d, size_t src_pitch_el
     long long blocks = (n + kIngestWarps - 1) / kIngestWarps;
     if (blocks > 148LL * 32) blocks = 148LL * 32;
     char* o = static_cast<char*>(dst);
+    char* rs = static_cast<char*>(resid);
     if (vec && regs)
         ingest_kernel<true, true, BF16><<<(int)blocks, kIngestThreads, 0, stream>>>(src, n, d, src_pitch_elems, o,
-                                                                                  pitch_bytes, pitch_elems, normalize, norms);
+                                                                                  pitch_bytes, pitch_elems, normalize, norms, rs, resid_err_ord);
     else if (vec)
         ingest_kernel<true, false, BF16><<<(int)blocks, kIngestThreads, 0, stream>>>(src, n, d, src_pitch_elems, o,
-                                                                                   pitch_bytes, pitch_elems, normalize, norms);
+                                                                                   pitch_bytes, pitch_elems, normalize, norms, rs, resid_err_ord);
     else
         ingest_kernel<false, false, BF16><<<(int)blocks, kIngestThreads, 0, stream>>>(src, n, d, src_pitch_elems, o,
-                                                                                    pitch_bytes, pitch_elems, normalize, norms);
+                                                                                    pitch_bytes, pitch_elems, normalize, norms, rs, resid_err_ord);
     B2_AFTER_LAUNCH();
     return B2_OK;
 }
 
 int ingest_rows(const float* src, int64_t n, int d, void* dst, size_t pitch_bytes, int dtype, bool normalize,
-                float* norms, cudaStream_t stream) {
-    if (dtype == B2_DTYPE_BF16) return launch_ingest<true>(src, n, d, (size_t)d, dst, pitch_bytes, normalize, norms, stream);
+                float* norms, cudaStream_t stream, void* resid, uint32_t* resid_err_ord) {
+    if (dtype == B2_DTYPE_BF16)
+        return launch_ingest<true>(src, n, d, (size_t)d, dst, pitch_bytes, normalize, norms, stream, resid, resid_err_ord);
     return launch_ingest<false>(src, n, d, (size_t)d, dst, pitch_bytes, normalize, norms, stream);
 }
 
@@ -171,7 +205,7 @@ int normalize_rows_inplace(float* x, int64_t n, int d, cudaStream_t stream) {
 __global__ void __launch_bounds__(256) gather_rows_kernel(const char* __restrict__ rows, int64_t ntotal,
                                                           size_t pitch_bytes, int d, bool bf16,
                                                           const int64_t* __restrict__ ids, int64_t n,
-                                                          float* __restrict__ out) {
+                                                          float* __restrict__ out, const char* __restrict__ resid) {
     const int lane = threadIdx.x & 31;
     const int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (w >= n) return;
@@ -184,7 +218,12 @@ __global__ void __launch_bounds__(256) gather_rows_kernel(const char* __restrict
     const char* r = rows + (size_t)id * pitch_bytes;
     if (bf16) {
         const __nv_bfloat16* rb = reinterpret_cast<const __nv_bfloat16*>(r);
-        for (int c = lane; c < d; c += 32) o[c] = __bfloat162float(rb[c]);
+        if (resid != nullptr) {  // the stored row is hi + lo
+            const __nv_bfloat16* rl = reinterpret_cast<const __nv_bfloat16*>(resid + (size_t)id * pitch_bytes);
+            for (int c = lane; c < d; c += 32) o[c] = __bfloat162float(rb[c]) + __bfloat162float(rl[c]);
+        } else {
+            for (int c = lane; c < d; c += 32) o[c] = __bfloat162float(rb[c]);
+        }
     } else {
         const float* rf = reinterpret_cast<const float*>(r);
         for (int c = lane; c < d; c += 32) o[c] = rf[c];
@@ -192,11 +231,12 @@ __global__ void __launch_bounds__(256) gather_rows_kernel(const char* __restrict
 }
 
 int gather_rows(const void* rows, int64_t ntotal, size_t pitch_bytes, int d, int dtype, const int64_t* ids, int64_t n,
-                float* out, cudaStream_t stream) {
+                float* out, cudaStream_t stream, const void* resid) {
     if (n <= 0) return B2_OK;
     const long long blocks = (n + 7) / 8;
     gather_rows_kernel<<<(unsigned)blocks, 256, 0, stream>>>(static_cast<const char*>(rows), ntotal, pitch_bytes, d,
-                                                            dtype == B2_DTYPE_BF16, ids, n, out);
+                                                            dtype == B2_DTYPE_BF16, ids, n, out,
+                                                            dtype == B2_DTYPE_BF16 ? static_cast<const char*>(resid) : nullptr);
     B2_AFTER_LAUNCH();
     return B2_OK;
 }
@@ -216,7 +256,7 @@ __global__ void __launch_bounds__(256) copy_rows_indexed_kernel(const char* __re
     uint4* b = reinterpret_cast<uint4*>(tmp_rows + (size_t)w * pitch_bytes);
     const int nv = (int)(pitch_bytes >> 4);
     for (int c = lane; c < nv; c += 32) b[c] = a[c];
-    if (lane == 0) tmp_norms[w] = norms[s];
+    if (lane == 0 && norms != nullptr) tmp_norms[w] = norms[s];
 }
 
 // Moves rows so that dst row (first_moved + j) = old row src_of_dst[j], j < n_dst, where
@@ -248,7 +288,7 @@ int compact_rows(void* rows, size_t pitch_bytes, float* norms, const int64_t* sr
         if (e == cudaSuccess)
             e = cudaMemcpyAsync(base + (size_t)(first_moved + c0) * pitch_bytes, tmp, (size_t)m * pitch_bytes,
                                 cudaMemcpyDeviceToDevice, stream);
-        if (e == cudaSuccess)
+        if (e == cudaSuccess && norms != nullptr)
             e = cudaMemcpyAsync(norms + first_moved + c0, tmpn, (size_t)m * sizeof(float), cudaMemcpyDeviceToDevice,
                                 stream);
         if (e != cudaSuccess) {

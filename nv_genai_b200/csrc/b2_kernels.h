@@ -11,7 +11,7 @@ namespace b2 {
 size_t scan_smem_bytes(int nq_tile, int nchunks, bool bf16, int kpad);
 int scan_pass(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* q_dev,
               int nq_valid, int nq_tile, int k, int num_sms, cudaStream_t stream, uint64_t** partial, int* grid,
-              const uint32_t* run_if = nullptr);
+              const uint32_t* run_if = nullptr, const void* resid = nullptr);  // resid: residual plane of bf16 rows
 
 void prof_enable(int on);
 void* prof_begin(cudaStream_t stream);                       // nullptr when profiling is off
@@ -22,6 +22,7 @@ int prof_read(int kind, double* ms, int64_t* n, int reset);
 // Read-only snapshot of an index handle for entry points implemented next to their kernels.
 struct IndexView {
     const void* rows;
+    const void* resid;  // residual plane of bf16 rows (same pitch), or null
     int64_t ntotal;
     size_t pitch;
     int d, dtype, metric, device, num_sms;
@@ -56,7 +57,8 @@ int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metri
 int merge_rescore(const uint64_t* partial, int nq, int nlists, int list_len, int k, int metric, float* D, int64_t* I,
                   size_t out_stride, cudaStream_t stream, const float* qnorm, const float* q_dev, int d, const void* rows,
                   size_t pitch_bytes, int dtype, const float* norms, const float* band, const PeerPush* push = nullptr,
-                  uint32_t* overflow = nullptr, bool l2_direct = false);
+                  uint32_t* overflow = nullptr, bool l2_direct = false, const void* resid = nullptr);
+// resid: residual plane of bf16 rows (same pitch): candidates are re-scored against hi + lo
 // overflow (optional, device, [nq + 1], zeroed by the caller): the lists are sorted best-first and may have dropped
 // candidates beyond list_len; a query whose cut reaches into a full list's last entry gets overflow[q] = 1 (and
 // overflow[nq] = 1) and NO output: the caller redoes it exactly.  Needs nlists * list_len <= 12288.
@@ -95,10 +97,18 @@ struct ApproxRows {
     size_t pitch;             // bytes
     const uint32_t* err_ord;  // device: ordered image of max over rows of |x - bf16(x)|^2
 };
+// Internal status (never crosses the C ABI): the tensor-core search could not finish rigorously and the caller redoes
+// the batch with the exact FFMA scan (rows with a residual plane whose candidate lists overflowed).
+#define B2_INTERNAL_REDO_EXACT 100
+// Residual plane of a bf16 row store: the index holds hi + lo, the tensor cores read hi only.
+struct ResidualRows {
+    const void* rows;         // [n][pitch] bf16, same pitch as the main plane
+    const uint32_t* err_ord;  // device: ordered image of max over rows of |lo|^2
+};
 int gemm_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* norms,
                 const float* q_dev, int64_t nq, int k, int num_sms, float* D, int64_t* I, cudaStream_t stream,
                 const PeerPush* push = nullptr, int query_parts = 0, const uint32_t* max_norm_ord = nullptr,
-                const ApproxRows* approx = nullptr);
+                const ApproxRows* approx = nullptr, const ResidualRows* resid = nullptr);
 // band[q] = 2 x a rigorous bound on |approximate score - exact score| for one-product tensor-core scoring of query q
 // (bf16 or tf32 operands, `steps` accumulation steps, rows bounded by max_norm_ord, optional row rounding error).
 int compute_band(const float* q_dev, int nq, int d, int nq_pad, int steps, bool bf16_operands, bool l2,
@@ -115,13 +125,16 @@ int merge_shards(int metric, int nq, int k, int nparts, const float* D_parts, co
 // b2_ingest.cu -------------------------------------------------------------
 // src: n x d fp32 dense (device) -> dst rows at `pitch_bytes`, fp32 or bf16, padding zeroed;
 // optional L2 normalisation; norms[i] = sum of squares of the STORED row.
+// resid (bf16 rows only, optional): second plane of the same pitch receiving bf16(x - bf16(x)); the row the index
+// holds is then hi + lo, norms[i] its squared norm, and *resid_err_ord the running maximum of sum lo^2 (ordered image).
 int ingest_rows(const float* src, int64_t n, int d, void* dst, size_t pitch_bytes, int dtype, bool normalize,
-                float* norms, cudaStream_t stream);
+                float* norms, cudaStream_t stream, void* resid = nullptr, uint32_t* resid_err_ord = nullptr);
 int normalize_rows_inplace(float* x, int64_t n, int d, cudaStream_t stream);
 // out[j] = row ids[j] as fp32 (n x d dense); negative / out-of-range ids give zero rows
 int gather_rows(const void* rows, int64_t ntotal, size_t pitch_bytes, int d, int dtype, const int64_t* ids, int64_t n,
-                float* out, cudaStream_t stream);
+                float* out, cudaStream_t stream, const void* resid = nullptr);
 // keep[i] != 0 rows are compacted to the front preserving order; dst_index = exclusive prefix of keep
+// (norms may be null: a plane without its own norm array)
 int compact_rows(void* rows, size_t pitch_bytes, float* norms, const int64_t* src_of_dst, int64_t n_dst,
                  int64_t first_moved, cudaStream_t stream);
 
@@ -136,12 +149,16 @@ int mmr_select(const float* q, int d, int nq, const float* cand_rows /*[nq][fetc
 // b2_scan_tc.cu ------------------------------------------------------------
 // Tensor-core scan for 3..16 queries (inner product): the corpus is the M operand, HBM-bound.
 // approx: the filter-and-refine mode is available (fp32 rows; needed for L2).
-bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t nq, bool approx = true);
+// residual: bf16 rows with a residual plane (inner product then rides the approximate mode too, like L2)
+bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t nq, bool approx = true, bool residual = false);
+// the approximate mode's register-resident merge holds (CTAs launched x list length) candidates per query
+bool scan_tc_approx_feasible(int64_t n, int k, int num_sms);
 // max_norm_ord (optional): enables the approximate (filter-and-refine) mode on fp32 rows.  metric L2 (fp32 rows,
 // approximate mode only) takes the rows' squared norms.
 int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, const float* q_dev, int nq, int k,
                    int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push = nullptr,
-                   const uint32_t* max_norm_ord = nullptr, int metric = B2_METRIC_IP, const float* norms = nullptr);
+                   const uint32_t* max_norm_ord = nullptr, int metric = B2_METRIC_IP, const float* norms = nullptr,
+                   const ResidualRows* resid = nullptr);
 
 // b2_synth.cu --------------------------------------------------------------
 int synth_fill(float* out, int64_t row0, int64_t nrows, int d, uint64_t seed, cudaStream_t stream);

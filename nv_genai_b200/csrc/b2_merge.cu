@@ -203,6 +203,7 @@ int merge_partials(const uint64_t* partial, int nq, int nlists, int k, int metri
 struct RescoreCtx {
     const float* q;        // [nq][d] fp32 queries (device)
     const char* rows;      // row store
+    const char* resid;     // bf16 rows with a residual plane (same pitch): the stored row is hi + lo; null = none
     const float* norms;    // |x|^2 per row (L2 keys)
     const float* band;     // [nq]
     size_t pitch_bytes;
@@ -218,8 +219,13 @@ __device__ __forceinline__ float warp_exact_l2(const RescoreCtx& c, const float*
     if (c.bf16) {
         for (int e0 = lane * 8; e0 < c.d; e0 += 256) {
             const uint4 w = *reinterpret_cast<const uint4*>(r + (size_t)e0 * 2);
-            const float x[8] = {bf16lo(w.x), bf16hi(w.x), bf16lo(w.y), bf16hi(w.y),
-                                bf16lo(w.z), bf16hi(w.z), bf16lo(w.w), bf16hi(w.w)};
+            float x[8] = {bf16lo(w.x), bf16hi(w.x), bf16lo(w.y), bf16hi(w.y),
+                          bf16lo(w.z), bf16hi(w.z), bf16lo(w.w), bf16hi(w.w)};
+            if (c.resid != nullptr) {
+                const uint4 y = *reinterpret_cast<const uint4*>(c.resid + (size_t)row * c.pitch_bytes + (size_t)e0 * 2);
+                x[0] += bf16lo(y.x); x[1] += bf16hi(y.x); x[2] += bf16lo(y.y); x[3] += bf16hi(y.y);
+                x[4] += bf16lo(y.z); x[5] += bf16hi(y.z); x[6] += bf16lo(y.w); x[7] += bf16hi(y.w);
+            }
 #pragma unroll
             for (int e = 0; e < 8; ++e)
                 if (e0 + e < c.d) {
@@ -250,8 +256,13 @@ __device__ __forceinline__ float warp_exact_dot(const RescoreCtx& c, const float
     if (c.bf16) {
         for (int e0 = lane * 8; e0 < c.d; e0 += 256) {
             const uint4 w = *reinterpret_cast<const uint4*>(r + (size_t)e0 * 2);  // 8 bf16; padding columns are zero
-            const float x[8] = {bf16lo(w.x), bf16hi(w.x), bf16lo(w.y), bf16hi(w.y),
-                                bf16lo(w.z), bf16hi(w.z), bf16lo(w.w), bf16hi(w.w)};
+            float x[8] = {bf16lo(w.x), bf16hi(w.x), bf16lo(w.y), bf16hi(w.y),
+                          bf16lo(w.z), bf16hi(w.z), bf16lo(w.w), bf16hi(w.w)};
+            if (c.resid != nullptr) {
+                const uint4 y = *reinterpret_cast<const uint4*>(c.resid + (size_t)row * c.pitch_bytes + (size_t)e0 * 2);
+                x[0] += bf16lo(y.x); x[1] += bf16hi(y.x); x[2] += bf16lo(y.y); x[3] += bf16hi(y.y);
+                x[4] += bf16lo(y.z); x[5] += bf16hi(y.z); x[6] += bf16lo(y.w); x[7] += bf16hi(y.w);
+            }
 #pragma unroll
             for (int e = 0; e < 8; ++e)
                 if (e0 + e < c.d) acc = fmaf(x[e], __ldg(qrow + e0 + e), acc);
@@ -426,7 +437,7 @@ __global__ void __launch_bounds__(kMergeThreads) merge_rescore_select_kernel(con
 int merge_rescore(const uint64_t* partial, int nq, int nlists, int list_len, int k, int metric, float* D, int64_t* I,
                   size_t out_stride, cudaStream_t stream, const float* qnorm, const float* q_dev, int d, const void* rows,
                   size_t pitch_bytes, int dtype, const float* norms, const float* band, const PeerPush* push_in,
-                  uint32_t* overflow, bool l2_direct) {
+                  uint32_t* overflow, bool l2_direct, const void* resid) {
     const int kpad = next_pow2(k < 32 ? 32 : k);
     const int total = nlists * list_len;
     PeerPush push;
@@ -444,6 +455,7 @@ int merge_rescore(const uint64_t* partial, int nq, int nlists, int list_len, int
     RescoreCtx ctx;
     ctx.q = q_dev;
     ctx.rows = static_cast<const char*>(rows);
+    ctx.resid = dtype == B2_DTYPE_BF16 ? static_cast<const char*>(resid) : nullptr;
     ctx.norms = norms;
     ctx.band = band;
     ctx.pitch_bytes = pitch_bytes;

@@ -94,6 +94,7 @@ struct ScanParams {
     int k, kpad;
     uint64_t* partial;     // [NQ][gridDim.x][k] sorted best-first
     const uint32_t* run_if;  // not null: the launch does nothing unless *run_if != 0 (fix-up pass of the tensor-core scan)
+    long long resid_delta;   // bf16 rows with a residual plane: byte offset from a row to its residual row (0 = none)
 };
 
 // Transposing butterfly: V per-lane partial sums -> max(V/32,1) complete sums per lane.
@@ -233,6 +234,12 @@ __global__ void __launch_bounds__(kScanThreads) scan_topk_kernel(const ScanParam
                 uint4 x[R];
 #pragma unroll
                 for (int r = 0; r < R; ++r) x[r] = ld_stream_u4(rp[r] + (size_t)j * 512);
+                // residual plane (warp-uniform): the stored row is hi + lo, exact in fp32
+                const bool two = p.resid_delta != 0;
+                uint4 y[R];
+#pragma unroll
+                for (int r = 0; r < R; ++r)
+                    y[r] = two ? ld_stream_u4(rp[r] + p.resid_delta + (size_t)j * 512) : make_uint4(0u, 0u, 0u, 0u);
 #pragma unroll
                 for (int qi = 0; qi < NQ; ++qi) {
                     const float4 qa = q4[((qi * nchunks + j) * 2 + 0) * 32 + lane];
@@ -240,8 +247,12 @@ __global__ void __launch_bounds__(kScanThreads) scan_topk_kernel(const ScanParam
 #pragma unroll
                     for (int r = 0; r < R; ++r) {
                         float a = acc[qi * R + r];
-                        const float e0 = bf16lo(x[r].x), e1 = bf16hi(x[r].x), e2 = bf16lo(x[r].y), e3 = bf16hi(x[r].y);
-                        const float e4 = bf16lo(x[r].z), e5 = bf16hi(x[r].z), e6 = bf16lo(x[r].w), e7 = bf16hi(x[r].w);
+                        float e0 = bf16lo(x[r].x), e1 = bf16hi(x[r].x), e2 = bf16lo(x[r].y), e3 = bf16hi(x[r].y);
+                        float e4 = bf16lo(x[r].z), e5 = bf16hi(x[r].z), e6 = bf16lo(x[r].w), e7 = bf16hi(x[r].w);
+                        if (two) {
+                            e0 += bf16lo(y[r].x); e1 += bf16hi(y[r].x); e2 += bf16lo(y[r].y); e3 += bf16hi(y[r].y);
+                            e4 += bf16lo(y[r].z); e5 += bf16hi(y[r].z); e6 += bf16lo(y[r].w); e7 += bf16hi(y[r].w);
+                        }
                         if (METRIC == B2_METRIC_IP) {
                             a = fmaf(e0, qa.x, a); a = fmaf(e1, qa.y, a); a = fmaf(e2, qa.z, a); a = fmaf(e3, qa.w, a);
                             a = fmaf(e4, qb.x, a); a = fmaf(e5, qb.y, a); a = fmaf(e6, qb.z, a); a = fmaf(e7, qb.w, a);
@@ -383,9 +394,11 @@ static int dispatch_nq(int nq_tile, const ScanParams& p, int num_sms, cudaStream
 // partial lists in *partial (stream-ordered allocation; the caller frees it with cudaFreeAsync).
 int scan_pass(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, int metric, const float* q_dev,
               int nq_valid, int nq_tile, int k, int num_sms, cudaStream_t stream, uint64_t** partial, int* grid,
-              const uint32_t* run_if) {
+              const uint32_t* run_if, const void* resid) {
     ScanParams p;
     p.run_if = run_if;
+    p.resid_delta = (resid != nullptr && dtype == B2_DTYPE_BF16)
+                        ? (long long)(static_cast<const char*>(resid) - static_cast<const char*>(rows)) : 0;
     p.rows = static_cast<const char*>(rows);
     p.n = (uint32_t)n;
     p.pitch_bytes = (uint32_t)pitch_bytes;
@@ -520,6 +533,8 @@ extern "C" int b2_index_search_static(b2_index* h, int64_t nq, const float* q_de
         p.kpad = next_pow2(k < 32 ? 32 : k);
         p.partial = nullptr;
         p.run_if = nullptr;
+        p.resid_delta = (v.resid != nullptr && v.dtype == B2_DTYPE_BF16)
+                            ? (long long)(static_cast<const char*>(v.resid) - static_cast<const char*>(v.rows)) : 0;
         const bool bf16 = v.dtype == B2_DTYPE_BF16;
         const int tile = next_pow2((int)nq);
         uint64_t* scratch = nullptr;

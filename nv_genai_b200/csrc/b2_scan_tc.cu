@@ -390,7 +390,8 @@ int launch_scan_tc(const CUtensorMap& tmRows, const CUtensorMap& tmQ, const Scan
 template <bool BF16>
 __global__ void scan_tc_prep_kernel(const float* __restrict__ q, int nq, int d, int nqt, int kp, void* __restrict__ Q,
                                     float* __restrict__ Qx, int steps, int l2, const uint32_t* __restrict__ max_norm_ord,
-                                    float* __restrict__ band, uint32_t* __restrict__ flags) {
+                                    float* __restrict__ band, uint32_t* __restrict__ flags,
+                                    const uint32_t* __restrict__ row_err_ord = nullptr) {
     const int lane = threadIdx.x & 31;
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (blockIdx.x == 0)
@@ -422,13 +423,21 @@ __global__ void scan_tc_prep_kernel(const float* __restrict__ q, int nq, int d, 
         ss += __shfl_xor_sync(kFull, ss, s);
         se += __shfl_xor_sync(kFull, se, s);
     }
-    if (lane == 0) band[row] = band_from_sums(ss, se, !BF16, steps, l2 != 0, d, ord2f(*max_norm_ord), 0.f);
+    // row_err: the rows the scores are finally computed against differ from what the tensor core reads (residual plane)
+    if (lane == 0)
+        band[row] = band_from_sums(ss, se, !BF16, steps, l2 != 0, d, ord2f(*max_norm_ord),
+                                   row_err_ord != nullptr ? ord2f(*row_err_ord) : 0.f);
 }
 
 }  // namespace
 
-bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t nq, bool approx) {
+bool scan_tc_approx_feasible(int64_t n, int k, int num_sms) {
+    return (long long)std::min<long long>(num_sms, (n + kTileRows - 1) / kTileRows) * next_pow2(k < 32 ? 32 : k) <= 12288;
+}
+
+bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t nq, bool approx, bool residual) {
     if (getenv("B2_NO_TENSOR") != nullptr || getenv("B2_NO_SCAN_TC") != nullptr) return false;
+    if (residual && (k > 64 || !approx || getenv("B2_SCAN_TC_EXACT") != nullptr)) return false;
     const int elem = dtype == B2_DTYPE_BF16 ? 2 : 4;
     // L2 rides the approximate mode only (k <= 64; bf16 rows too: one bf16 product): keys 2 q.x - |x|^2 for the filter, the direct form
     // sum (x - q)^2 -- faiss's arithmetic below 20 queries -- for the candidates that are re-scored
@@ -476,7 +485,8 @@ static void pick_pipeline(int kslices, bool sps_allowed, int nqt, int kpad, int 
 // the error band of the k-th best).
 static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes, int d, const float* q_dev, int nq, int k,
                                  int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push,
-                                 const uint32_t* max_norm_ord, int metric, const float* norms, int dtype) {
+                                 const uint32_t* max_norm_ord, int metric, const float* norms, int dtype,
+                                 const ResidualRows* resid) {
     const bool l2 = metric == B2_METRIC_L2;
     const bool bf16 = dtype == B2_DTYPE_BF16;  // bf16 rows come here for L2 only: one bf16 product, the stored rows are exact
     const int elem = bf16 ? 2 : 4;
@@ -533,7 +543,8 @@ static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes
         const int steps = bf16 ? kp / 16 : kp / 8;
         if (bf16)
             scan_tc_prep_kernel<true><<<(nqt + 7) / 8, 256, 0, stream>>>(q_dev, nq, d, nqt, kp, Q, nullptr, steps, l2 ? 1 : 0,
-                                                                        max_norm_ord, band, flags);
+                                                                        max_norm_ord, band, flags,
+                                                                        resid != nullptr ? resid->err_ord : nullptr);
         else
             scan_tc_prep_kernel<false><<<(nqt + 7) / 8, 256, 0, stream>>>(q_dev, nq, d, nqt, kp, Q, l2 ? nullptr : static_cast<float*>(Qx),
                                                                          steps, l2 ? 1 : 0, max_norm_ord, band, flags);
@@ -553,10 +564,10 @@ static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes
     }
     if (rc == B2_OK)
         rc = merge_rescore(p.partial, nq, grid, p.klist, k, metric, D, I, (size_t)k, stream, nullptr, q_dev, d, rows,
-                           pitch_bytes, dtype, norms, band, push, flags, l2);
+                           pitch_bytes, dtype, norms, band, push, flags, l2, resid != nullptr ? resid->rows : nullptr);
     // ---- exact fix-up for the flagged queries (each kernel returns immediately when there is none)
-    if (rc == B2_OK && l2) {
-        // L2: the FFMA scan (direct form), a pass per query tile: 16 queries, or fewer when rows are so long that 16
+    if (rc == B2_OK && (l2 || bf16)) {
+        // L2, and bf16 rows (with a residual plane: both planes): the FFMA scan, a pass per query tile: 16 queries, or fewer when rows are so long that 16
         // query rows do not fit its shared memory (d = 4096: 8)
         int tmax = 16;
         while (tmax > 1 && scan_smem_bytes(tmax, (int)(pitch_bytes / 512), bf16, next_pow2(k < 32 ? 32 : k)) > 200 * 1024) tmax >>= 1;
@@ -564,15 +575,16 @@ static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes
             const int valid = std::min(tmax, nq - off);
             uint64_t* part = nullptr;
             int g2 = 0;
-            rc = scan_pass(rows, n, pitch_bytes, d, dtype, B2_METRIC_L2, q_dev + (size_t)off * d, valid,
-                           next_pow2(valid), k, num_sms, stream, &part, &g2, flags + nq);
+            rc = scan_pass(rows, n, pitch_bytes, d, dtype, metric, q_dev + (size_t)off * d, valid,
+                           next_pow2(valid), k, num_sms, stream, &part, &g2, flags + nq,
+                           resid != nullptr ? resid->rows : nullptr);
             if (rc != B2_OK) break;
             PeerPush pp;
             if (push != nullptr) {
                 pp = *push;
                 pp.q_offset += off;
             }
-            rc = merge_partials(part, valid, g2, k, B2_METRIC_L2, 0, D ? D + (size_t)off * k : nullptr,
+            rc = merge_partials(part, valid, g2, k, metric, 0, D ? D + (size_t)off * k : nullptr,
                                 I ? I + (size_t)off * k : nullptr, (size_t)k, stream, nullptr, push != nullptr ? &pp : nullptr,
                                 flags + off);
             cudaFreeAsync(part, stream);
@@ -598,14 +610,19 @@ static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes
 
 int scan_tc_search(const void* rows, int64_t n, size_t pitch_bytes, int d, int dtype, const float* q_dev, int nq, int k,
                    int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push,
-                   const uint32_t* max_norm_ord, int metric, const float* norms) {
+                   const uint32_t* max_norm_ord, int metric, const float* norms, const ResidualRows* resid) {
     const bool bf16 = dtype == B2_DTYPE_BF16;
+    if (!bf16) resid = nullptr;
     const int elem = bf16 ? 2 : 4;
     static const bool no_approx = getenv("B2_SCAN_TC_EXACT") != nullptr;
-    if ((!bf16 || metric == B2_METRIC_L2) && max_norm_ord != nullptr && !no_approx && k <= 64 &&
-        (long long)std::min<long long>(num_sms, (n + kTileRows - 1) / kTileRows) * next_pow2(k < 32 ? 32 : k) <= 12288)
+    if ((!bf16 || metric == B2_METRIC_L2 || resid != nullptr) && max_norm_ord != nullptr && !no_approx && k <= 64 &&
+        scan_tc_approx_feasible(n, k, num_sms))
         return scan_tc_search_approx(rows, n, pitch_bytes, d, q_dev, nq, k, num_sms, D, I, stream, push, max_norm_ord,
-                                     metric, norms, dtype);
+                                     metric, norms, dtype, resid);
+    if (resid != nullptr) {
+        set_error("tensor-core scan: rows with a residual plane need the approximate mode (k <= 64)");
+        return B2_ERR_UNSUPPORTED;
+    }
     if (metric != B2_METRIC_IP) {
         set_error("tensor-core scan: L2 needs the approximate mode (fp32 rows, k <= 64)");
         return B2_ERR_UNSUPPORTED;

@@ -25,7 +25,10 @@ METRIC_INNER_PRODUCT = N.METRIC_INNER_PRODUCT
 METRIC_L2 = N.METRIC_L2
 
 _DTYPES = {"float32": N.DTYPE_F32, "fp32": N.DTYPE_F32, "f32": N.DTYPE_F32, "bfloat16": N.DTYPE_BF16,
-           "bf16": N.DTYPE_BF16}
+           "bf16": N.DTYPE_BF16, "bfloat16+residual": N.DTYPE_BF16, "bf16+residual": N.DTYPE_BF16}
+# "bfloat16+residual": bf16 rows plus a second bf16 plane holding x - bf16(x) (4 bytes per element in HBM).  Searches
+# stream the main plane only, like a plain bf16 store, and every returned score is re-computed against both planes, so
+# recall against the fp32 embeddings is that of ~16 mantissa bits instead of 8 (b2_index_set_option "bf16_residual").
 
 
 def _torch():
@@ -103,9 +106,12 @@ class IndexFlat:
         if dtype not in _DTYPES:
             raise ValueError(f"dtype must be one of {sorted(_DTYPES)}")
         self._h = ctypes.c_void_p()
-        self._dtype_name = "bfloat16" if _DTYPES[dtype] == N.DTYPE_BF16 else "float32"
+        residual = dtype.endswith("+residual")
+        self._dtype_name = ("bfloat16+residual" if residual else "bfloat16") if _DTYPES[dtype] == N.DTYPE_BF16 else "float32"
         self.device = _resolve_device(device)
         N.check(N.lib.b2_index_create(int(d), int(metric), _DTYPES[dtype], self.device, ctypes.byref(self._h)))
+        if residual:
+            N.check(N.lib.b2_index_set_option(self._h, b"bf16_residual", 1))
         self.is_trained = True
 
     # ---- attributes faiss exposes
