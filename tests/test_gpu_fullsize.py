@@ -218,3 +218,44 @@ def test_prefix_property_and_decomposition(big):
     Dm, Im = merge_shard_lists(flat.METRIC_IP, torch.stack(parts_D), torch.stack(parts_I))
     Dw, Iw = whole.search(q, 10)
     assert torch.equal(Im, Iw) and torch.equal(Dm, Dw)
+
+
+# ------------------------------------------------------------------ clustered corpus (distribution C)
+def test_clustered_corpus_loads_the_band_and_the_candidate_lists():
+    """2M rows drawn around 4096 unit centroids (sigma 0.05 per component, renormalised), queries from the same
+    centroids: every query has ~490 rows of its own cluster within a few per cent of each other's score, which is what
+    fills the error band and the k + slack candidate lists of the filter-and-refine paths (and, if they overflow, takes
+    the exact fix-up launch).  Batch 16 (tensor-core scan) and batch 4096 (GEMM; 32 queries through the oracle)."""
+    import torch
+
+    from nv_genai_b200 import IndexFlatIP
+
+    n, ncent = 2_000_000, 4096
+    cent = flat.synth(0, ncent, D, 0xC0FFEE)
+    flat.normalize_L2(cent)
+    x = np.empty((n, D), dtype=np.float32)
+    for r0 in range(0, n, 500_000):
+        blk = flat.synth(r0, 500_000, D, 0xC0FFEF)
+        blk *= np.float32(0.05)
+        blk += cent[(np.arange(r0, r0 + 500_000) % ncent)]
+        x[r0:r0 + 500_000] = blk
+    flat.normalize_L2(x)
+    q_all = flat.synth(0, NQ_BIG, D, 0xC0FFF0)
+    q_all *= np.float32(0.05)
+    q_all += cent[(np.arange(NQ_BIG) * 7) % ncent]
+    flat.normalize_L2(q_all)
+    q32 = np.ascontiguousarray(q_all[::SAMPLE_STEP])
+    Dr16, Ir16, _ = flat.search_seq(x, q_all[:16], 10, flat.METRIC_IP)
+    Dr32, Ir32, _ = flat.search_seq(x, q32, 100, flat.METRIC_IP)
+    xb = flat.round_bf16(x)
+    Db32, Ib32, _ = flat.search_seq(xb, q32, 100, flat.METRIC_IP)
+    for dtype, rows, ref32 in (("float32", x, (Dr32, Ir32)), ("bfloat16", xb, (Db32, Ib32))):
+        idx = IndexFlatIP(D, dtype=dtype)
+        idx.add(rows)
+        if dtype == "float32":
+            D_, I_ = idx.search(q_all[:16], 10)
+            assert_parity(D_, I_, Dr16, Ir16, x, q_all[:16], metric_ip=True)
+        Dt, It = idx.search(torch.from_numpy(q_all).cuda(), 100)
+        assert_parity(Dt[::SAMPLE_STEP].cpu().numpy(), It[::SAMPLE_STEP].cpu().numpy(), ref32[0], ref32[1], rows, q32,
+                      metric_ip=True)
+        del idx
