@@ -1106,7 +1106,6 @@ int b2_index_set_option(b2_index* h, const char* name, int64_t value) {
             set_error("b2_index_set_option: bf16_residual must be 0 or 1");
             return B2_ERR_INVALID;
         }
-        std::unique_lock<std::shared_mutex> lk(h->mu);
         if ((int)value == h->residual_enabled) return B2_OK;
         if (h->dtype != B2_DTYPE_BF16 || h->ntotal != 0) {
             set_error("b2_index_set_option: bf16_residual can only be changed on an EMPTY bf16 index (dtype %d, %lld rows)",

@@ -51,7 +51,7 @@ def test_fp32_store_matches_blas_oracle(metric, nq, k):
     idx = _mk(metric, d)
     idx.add(x)
     (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, k))
-    assert launches in (3, 6, 7), launches  # one pass for the whole batch, not ceil(nq/16) scan passes
+    assert launches in (3, 5, 6), launches  # one pass for the whole batch, not ceil(nq/16) scan passes
     Dr, Ir = flat.search_blas(x, q, k, metric)
     assert_parity(D, I, Dr, Ir, x, q, metric_ip=(metric == flat.METRIC_IP))
     D64, I64 = flat.search_f64(x, q, k, metric)
@@ -81,7 +81,7 @@ def test_bf16_store_matches_oracle_on_rounded_rows(metric):
     idx = _mk(metric, d, "bfloat16")
     idx.add(x)
     (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, k))
-    assert launches in (3, 6, 7)
+    assert launches in (3, 5, 6)
     xr = flat.round_bf16(x)
     Dr, Ir = flat.search_blas(xr, q, k, metric)
     assert_parity(D, I, Dr, Ir, xr, q, metric_ip=(metric == flat.METRIC_IP))
@@ -188,8 +188,8 @@ def test_small_batch_tensor_scan_matches_sequential_oracle(dtype, nq, k):
     idx.add(x)
     (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, k))
     # bf16 rows, or k > 64: prep + scan_tc + merge (the FFMA scan is 2).  fp32 rows, k <= 64: filter and refine =
-    # prep + band + approximate scan_tc + merge/re-score, then the fix-up trio that returns at once
-    assert launches == (7 if dtype == "float32" and k <= 64 else 3), launches
+    # one preparation kernel + approximate scan_tc + merge/re-score, then the fix-up pair that returns at once
+    assert launches == (5 if dtype == "float32" and k <= 64 else 3), launches
     xr = flat.round_bf16(x) if dtype == "bfloat16" else x
     Dr, Ir, _ = flat.search_seq(xr, q, k, flat.METRIC_IP)
     assert_parity(D, I, Dr, Ir, xr, q, metric_ip=True)
@@ -205,7 +205,7 @@ def test_medium_batch_rides_one_tensor_scan_pass_when_k_is_small(dtype, nq, k):
     idx = _mk(flat.METRIC_IP, d, dtype)
     idx.add(x)
     (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, k))
-    assert launches in (3, 6, 7), launches  # one pass over the rows either way
+    assert launches in (3, 5, 6), launches  # one pass over the rows either way
     xr = flat.round_bf16(x) if dtype == "bfloat16" else x
     Dr, Ir = flat.search_f64(xr, q, k, flat.METRIC_IP)
     assert_parity(D, I, Dr.astype(np.float32), Ir, xr, q, metric_ip=True)
@@ -237,7 +237,7 @@ def test_small_batch_l2_keeps_the_direct_form():
     idx = _mk(flat.METRIC_L2, d)
     idx.add(x)
     (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, 4))
-    assert launches == 6, launches  # prep + band + approximate scan + merge/re-score, FFMA fix-up pair (returns at once)
+    assert launches == 5, launches  # preparation + approximate scan + merge/re-score, FFMA fix-up pair (returns at once)
     assert I[2, 0] == 77 and D[2, 0] == 0.0
     Dr, Ir, _ = flat.search_seq(x, q, 4, flat.METRIC_L2)
     assert_parity(D, I, Dr, Ir, x, q, metric_ip=False)
@@ -247,7 +247,7 @@ def test_small_batch_l2_keeps_the_direct_form():
     xb = _mk(flat.METRIC_L2, d, "bfloat16")  # bf16 rows: one bf16 product as the filter, same re-scoring
     xb.add(x)
     (D, I), launches = _launched_tensor_kernel(lambda: xb.search(q, 4))
-    assert launches == 6 and I[2, 0] == 77
+    assert launches == 5 and I[2, 0] == 77
     xr = flat.round_bf16(x)
     Dr, Ir, _ = flat.search_seq(xr, q, 4, flat.METRIC_L2)
     assert_parity(D, I, Dr, Ir, xr, q, metric_ip=False)
