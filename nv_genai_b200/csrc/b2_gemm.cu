@@ -1518,13 +1518,14 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
         cudaEventCreate(&dbg_ev0);
         cudaEventRecord(dbg_ev0, stream);
     }
-    auto launch_approx = [&](const GemmParams& gp, int g) {
+    auto launch_approx_smem = [&](const GemmParams& gp, int g, size_t sm) {
         if (abf16)
-            return swb == 128 ? launch_gemm_cg<0, 1, 128>(tmA, tmB, gp, g, smem, stream, cg)
-                              : launch_gemm_cg<0, 1, 64>(tmA, tmB, gp, g, smem, stream, cg);
-        return swb == 128 ? launch_gemm_cg<2, 1, 128>(tmA, tmB, gp, g, smem, stream, cg)
-                          : launch_gemm_cg<2, 1, 64>(tmA, tmB, gp, g, smem, stream, cg);
+            return swb == 128 ? launch_gemm_cg<0, 1, 128>(tmA, tmB, gp, g, sm, stream, cg)
+                              : launch_gemm_cg<0, 1, 64>(tmA, tmB, gp, g, sm, stream, cg);
+        return swb == 128 ? launch_gemm_cg<2, 1, 128>(tmA, tmB, gp, g, sm, stream, cg)
+                          : launch_gemm_cg<2, 1, 64>(tmA, tmB, gp, g, sm, stream, cg);
     };
+    auto launch_approx = [&](const GemmParams& gp, int g) { return launch_approx_smem(gp, g, smem); };
     if (rc == B2_OK && two_pass) {
         GemmParams ps = p;
         ps.n_tiles = n_sample;
@@ -1534,12 +1535,31 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
         ps.tile_mul = sstride;
         ps.tile_skip = 0;
         ps.list_base = keep_sample_lists ? nseg_m : 0;
+        // every item of the pre-pass starts cold and is short, so it is bound by reservoir selections, not by the
+        // operand pipeline: the longest reservoir that leaves three pipeline stages (a selection per rcap - k admissions)
+        int stages_s = stages;
+        int rcap_s = p.rcap;
+        {
+            const int want = std::min(kMaxRcap, std::max(32, 2 * k)) / 8 * 8;
+            for (int st = stages; st >= 3; --st) {
+                int rc_try = want;
+                while (rc_try > p.rcap && gemm_smem_slots(false, 1, swb, st, rc_try + 1, cg, 0) > 227 * 1024) rc_try -= 8;
+                if (rc_try > rcap_s) {
+                    rcap_s = rc_try;
+                    stages_s = st;
+                }
+                if (rc_try >= want) break;
+            }
+        }
+        ps.rcap = rcap_s;
+        ps.num_stages = stages_s;
         if (!keep_sample_lists) {
             ps.partial = spartial;
             ps.n_lists = nseg_s;
         }
         ps.stats = nullptr;
-        rc = launch_approx(ps, (int)std::min<long long>(grid_max, ps.n_items) * cg);
+        rc = launch_approx_smem(ps, (int)std::min<long long>(grid_max, ps.n_items) * cg,
+                                gemm_smem_slots(false, 1, swb, stages_s, rcap_s + 1, cg, 0));
         if (rc == B2_OK) {
             const size_t us = (size_t)kUnionWarps * nseg_s * p.list_len * 4;
             static std::mutex umu;
@@ -1567,6 +1587,11 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
                 }
             }
         }
+    }
+    cudaEvent_t dbg_evp = nullptr;
+    if (debug_t && two_pass) {
+        cudaEventCreate(&dbg_evp);
+        cudaEventRecord(dbg_evp, stream);
     }
     if (rc == B2_OK) rc = launch_approx(p, grid);
     static const bool debug = std::getenv("B2_GEMM_DEBUG") != nullptr;
@@ -1645,8 +1670,13 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
         cudaEventElapsedTime(&t_approx, dbg_ev0, dbg_ev[1]);
         cudaEventElapsedTime(&t_fix, dbg_ev[1], dbg_ev[2]);
         cudaEventElapsedTime(&t_merge, dbg_ev[2], dbg_ev[3]);
-        std::fprintf(stderr, "[b2 gemm refine] approx %.2f ms (stages %d, swizzle %d), fix-up %.2f ms (incl. the flag read-back), merge %.2f ms\n",
-                     t_approx, stages, swb, t_fix, t_merge);
+        float t_pre = 0.f;
+        if (dbg_evp != nullptr) {
+            cudaEventElapsedTime(&t_pre, dbg_ev0, dbg_evp);
+            cudaEventDestroy(dbg_evp);
+        }
+        std::fprintf(stderr, "[b2 gemm refine] approx %.2f ms (of which threshold pre-pass + union %.2f ms; stages %d, swizzle %d), fix-up %.2f ms (incl. the flag read-back), merge %.2f ms\n",
+                     t_approx, t_pre, stages, swb, t_fix, t_merge);
         for (auto& e : dbg_ev) cudaEventDestroy(e);
         cudaEventDestroy(dbg_ev0);
     }

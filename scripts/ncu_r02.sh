@@ -9,7 +9,7 @@ python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-check > gpurun_out/n
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r02_launches_default_bench.csv \
     python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-check > gpurun_out/ncu_bench.log 2>&1
 python scripts/time_gemm.py --rows 4000000 --dtype bfloat16 --k 100 --reps 1 > gpurun_out/ncu_gemm_plain.json 2>/dev/null || exit 1
-ncu --set full --clock-control none --import-source on -k regex:gemm_topk_kernel -s 2 -c 2 -o gpurun_out/r02_gemm_k100 -f \
+ncu --set full --clock-control none --import-source on -k regex:gemm_topk_kernel -s 3 -c 2 -o gpurun_out/r02_gemm_k100 -f \
     python scripts/time_gemm.py --rows 4000000 --dtype bfloat16 --k 100 --reps 1 > gpurun_out/ncu_gemm.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:scan_tc_kernel -s 2 -c 1 -o gpurun_out/r02_scantc_batch1 -f \
     python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-check > gpurun_out/ncu_scan.log 2>&1

@@ -51,7 +51,7 @@ def test_fp32_store_matches_blas_oracle(metric, nq, k):
     idx = _mk(metric, d)
     idx.add(x)
     (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, k))
-    assert launches in (3, 5, 6), launches  # one pass for the whole batch, not ceil(nq/16) scan passes
+    assert launches in (3, 5, 6, 7), launches  # one pass for the whole batch, not ceil(nq/16) scan passes
     Dr, Ir = flat.search_blas(x, q, k, metric)
     assert_parity(D, I, Dr, Ir, x, q, metric_ip=(metric == flat.METRIC_IP))
     D64, I64 = flat.search_f64(x, q, k, metric)
@@ -81,7 +81,7 @@ def test_bf16_store_matches_oracle_on_rounded_rows(metric):
     idx = _mk(metric, d, "bfloat16")
     idx.add(x)
     (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, k))
-    assert launches in (3, 5, 6)
+    assert launches in (3, 5, 6, 7)
     xr = flat.round_bf16(x)
     Dr, Ir = flat.search_blas(xr, q, k, metric)
     assert_parity(D, I, Dr, Ir, xr, q, metric_ip=(metric == flat.METRIC_IP))
@@ -205,7 +205,7 @@ def test_medium_batch_rides_one_tensor_scan_pass_when_k_is_small(dtype, nq, k):
     idx = _mk(flat.METRIC_IP, d, dtype)
     idx.add(x)
     (D, I), launches = _launched_tensor_kernel(lambda: idx.search(q, k))
-    assert launches in (3, 5, 6), launches  # one pass over the rows either way
+    assert launches in (3, 5, 6, 7), launches  # one pass over the rows either way
     xr = flat.round_bf16(x) if dtype == "bfloat16" else x
     Dr, Ir = flat.search_f64(xr, q, k, flat.METRIC_IP)
     assert_parity(D, I, Dr.astype(np.float32), Ir, xr, q, metric_ip=True)
