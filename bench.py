@@ -194,7 +194,7 @@ def scan_kernel_name(batch, k, rows, dim, dtype):
     """Which scan kernel b2_index_search picks for an inner-product batch (b2_scan_tc.cu: scan_tc_supported)."""
     bf16 = dtype == "bfloat16"
     min_nq = 3 if bf16 else 5
-    if rows * dim * (2 if bf16 else 4) >= 8e9 and (bf16 or k <= 64):
+    if rows * dim * (2 if bf16 else 4) >= float(os.environ.get("B2_SCAN_TC_MIN_BYTES", "8e9")) and (bf16 or k <= 64):
         min_nq = 1
     if "B2_SCAN_TC_MIN_NQ" in os.environ:
         min_nq = int(os.environ["B2_SCAN_TC_MIN_NQ"])
