@@ -985,39 +985,39 @@ int b2_index_remove_ids(b2_index* h, int64_t n, const int64_t* ids, int64_t* n_r
     if (h->ntotal == 0) return B2_OK;
     DeviceGuard g(h->device);
     const int64_t nt = h->ntotal;
-    std::vector<uint8_t> drop((size_t)nt, 0);
-    int64_t removed = 0, first = nt;
-    for (int64_t i = 0; i < n; ++i) {
-        const int64_t id = ids[i];
-        if (id >= 0 && id < nt && !drop[(size_t)id]) {
-            drop[(size_t)id] = 1;
-            ++removed;
-            first = std::min(first, id);
-        }
-    }
-    if (removed == 0) return B2_OK;
-    std::vector<int64_t> src;
-    src.reserve((size_t)(nt - first - removed));
-    for (int64_t i = first; i < nt; ++i)
-        if (!drop[(size_t)i]) src.push_back(i);
+    // the keep list is built on the device (b2_ingest.cu: build_keep_list): only the ids cross PCIe
     cudaStream_t stream = nullptr;
+    int64_t removed = 0, first = nt;
+    int64_t* ids_dev = nullptr;
+    int64_t* src_dev = nullptr;
+    void* scratch = nullptr;
+    const size_t sbytes = keep_list_scratch_bytes(nt);
     int rc = B2_OK;
-    if (!src.empty()) {
-        int64_t* src_dev = nullptr;
-        B2_CUDA_TRY(cudaMallocAsync(&src_dev, src.size() * 8, stream));
-        cudaError_t e = cudaMemcpyAsync(src_dev, src.data(), src.size() * 8, cudaMemcpyHostToDevice, stream);
-        if (e != cudaSuccess) {
+    auto cu = [&](cudaError_t e) {
+        if (e != cudaSuccess && rc == B2_OK) {
             set_error("remove_ids: %s", cudaGetErrorString(e));
-            rc = B2_ERR_CUDA;
-        } else {
-            rc = compact_rows(h->store.base(), h->pitch, h->norms, src_dev, (int64_t)src.size(), first, stream);
-            if (rc == B2_OK && h->residual_enabled)
-                rc = compact_rows(h->resid.base(), h->pitch, nullptr, src_dev, (int64_t)src.size(), first, stream);
+            rc = e == cudaErrorMemoryAllocation ? B2_ERR_OOM : B2_ERR_CUDA;
         }
-        cudaFreeAsync(src_dev, stream);
+    };
+    cu(cudaMallocAsync(&ids_dev, (size_t)n * 8, stream));
+    if (rc == B2_OK) cu(cudaMallocAsync(&src_dev, (size_t)nt * 8, stream));
+    if (rc == B2_OK) cu(cudaMallocAsync(&scratch, sbytes, stream));
+    if (rc == B2_OK) cu(cudaMemcpyAsync(ids_dev, ids, (size_t)n * 8, cudaMemcpyHostToDevice, stream));
+    if (rc == B2_OK) rc = build_keep_list(ids_dev, n, nt, src_dev, scratch, sbytes, &removed, &first, stream);
+    if (rc == B2_OK && removed > 0) {
+        const int64_t n_dst = nt - first - removed;  // rows behind the first dropped one that stay
+        if (n_dst > 0) {
+            rc = compact_rows(h->store.base(), h->pitch, h->norms, src_dev, n_dst, first, stream);
+            if (rc == B2_OK && h->residual_enabled)
+                rc = compact_rows(h->resid.base(), h->pitch, nullptr, src_dev, n_dst, first, stream);
+        }
     }
+    if (ids_dev) cudaFreeAsync(ids_dev, stream);
+    if (src_dev) cudaFreeAsync(src_dev, stream);
+    if (scratch) cudaFreeAsync(scratch, stream);
     B2_CUDA_TRY(cudaStreamSynchronize(stream));
     if (rc != B2_OK) return rc;
+    if (removed == 0) return B2_OK;
     h->ntotal = nt - removed;
     h->shadow_rows = std::min(h->shadow_rows, first);  // rows from the first removed one on moved: reconvert lazily
     h->shadow_refused_rows = 0;

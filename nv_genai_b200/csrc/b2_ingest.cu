@@ -301,6 +301,150 @@ int compact_rows(void* rows, size_t pitch_bytes, float* norms, const int64_t* sr
     return rc;
 }
 
+// ------------------------------------------------------------------ keep list of remove_ids, built on the device
+// IndexFlatCodes::remove_ids walks all rows on the host; here the ids (a few KB) are the only thing that crosses PCIe:
+// a bitmap of the rows to drop, a prefix sum over the kept rows of each 32-row word (block scan + scan of the block
+// totals), and the list "destination first + j takes row src[j]" that compact_rows consumes.
+// stats[0] = rows dropped (distinct, in range), stats[1] = first dropped row (ntotal if none).
+__global__ void mark_drop_kernel(const int64_t* __restrict__ ids, int64_t n, int64_t ntotal, uint32_t* __restrict__ drop,
+                                 unsigned long long* __restrict__ stats) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t id = ids[i];
+        if (id < 0 || id >= ntotal) continue;
+        const uint32_t bit = 1u << (id & 31);
+        if ((atomicOr(drop + (id >> 5), bit) & bit) == 0u) {  // first time this row is named
+            atomicAdd(stats, 1ull);
+            atomicMin(stats + 1, (unsigned long long)id);
+        }
+    }
+}
+
+constexpr int kKeepThreads = 1024;  // one thread per 32-row word: a block covers 32768 rows
+
+__device__ __forceinline__ uint32_t keep_word(const uint32_t* drop, int64_t w, int64_t nwords, int64_t ntotal) {
+    if (w >= nwords) return 0u;
+    uint32_t keep = ~drop[w];
+    const int64_t left = ntotal - w * 32;
+    if (left < 32) keep &= (1u << left) - 1u;
+    return keep;
+}
+
+// pass 1: kept rows per block
+__global__ void __launch_bounds__(kKeepThreads) keep_count_kernel(const uint32_t* __restrict__ drop, int64_t nwords,
+                                                                 int64_t ntotal, uint32_t* __restrict__ block_tot) {
+    __shared__ uint32_t wsum[kKeepThreads / 32];
+    const int64_t w = (int64_t)blockIdx.x * kKeepThreads + threadIdx.x;
+    uint32_t c = __popc(keep_word(drop, w, nwords, ntotal));
+    c = __reduce_add_sync(kFull, c);
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        uint32_t v = wsum[threadIdx.x];
+        v = __reduce_add_sync(kFull, v);
+        if (threadIdx.x == 0) block_tot[blockIdx.x] = v;
+    }
+}
+
+// pass 2: exclusive scan of the block totals, 64-bit (one block; a few hundred entries at 10M rows)
+__global__ void __launch_bounds__(1024) keep_scan_blocks_kernel(const uint32_t* __restrict__ block_tot, int64_t nblocks,
+                                                               unsigned long long* __restrict__ block_off) {
+    __shared__ unsigned long long carry_s;
+    __shared__ unsigned long long wtot[32];
+    if (threadIdx.x == 0) carry_s = 0ull;
+    __syncthreads();
+    for (int64_t base = 0; base < nblocks; base += 1024) {
+        const int64_t i = base + threadIdx.x;
+        const unsigned long long v = i < nblocks ? block_tot[i] : 0ull;
+        unsigned long long incl = v;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) {
+            const unsigned long long t = __shfl_up_sync(kFull, incl, s);
+            if ((threadIdx.x & 31) >= s) incl += t;
+        }
+        if ((threadIdx.x & 31) == 31) wtot[threadIdx.x >> 5] = incl;
+        __syncthreads();
+        unsigned long long woff = 0ull;
+        for (int ww = 0; ww < (int)(threadIdx.x >> 5); ++ww) woff += wtot[ww];
+        const unsigned long long carry = carry_s;
+        if (i < nblocks) block_off[i] = carry + woff + incl - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry_s = carry + woff + incl;
+        __syncthreads();
+    }
+}
+
+// pass 3: src[kept rows before r - first] = r for every kept row r >= first
+__global__ void __launch_bounds__(kKeepThreads) keep_emit_kernel(const uint32_t* __restrict__ drop, int64_t nwords,
+                                                                int64_t ntotal,
+                                                                const unsigned long long* __restrict__ block_off,
+                                                                const unsigned long long* __restrict__ stats,
+                                                                int64_t* __restrict__ src) {
+    __shared__ uint32_t wsum[kKeepThreads / 32];
+    const int64_t first = (int64_t)stats[1];
+    const int64_t w = (int64_t)blockIdx.x * kKeepThreads + threadIdx.x;
+    if ((int64_t)(blockIdx.x + 1) * kKeepThreads * 32 <= first) return;  // the whole block lies before the first dropped row
+    uint32_t keep = keep_word(drop, w, nwords, ntotal);
+    const uint32_t c = __popc(keep);
+    uint32_t incl = c;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) {
+        const uint32_t t = __shfl_up_sync(kFull, incl, s);
+        if ((threadIdx.x & 31) >= s) incl += t;
+    }
+    if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = incl;
+    __syncthreads();
+    uint32_t woff = 0;
+    for (int ww = 0; ww < (int)(threadIdx.x >> 5); ++ww) woff += wsum[ww];
+    int64_t pos = (int64_t)block_off[blockIdx.x] + woff + incl - c;  // kept rows before this word
+    while (keep) {
+        const int b = __ffs(keep) - 1;
+        keep &= keep - 1u;
+        const int64_t r = w * 32 + b;
+        if (r >= first) src[pos - first] = r;
+        ++pos;
+    }
+}
+
+// ids_dev: n ids on the device.  Outputs (device): src list (capacity ntotal entries), stats[2]; host: *removed, *first.
+int build_keep_list(const int64_t* ids_dev, int64_t n, int64_t ntotal, int64_t* src_dev, void* scratch, size_t scratch_bytes,
+                    int64_t* removed, int64_t* first, cudaStream_t stream) {
+    const int64_t nwords = (ntotal + 31) / 32;
+    const int64_t nblocks = (nwords + kKeepThreads - 1) / kKeepThreads;
+    const size_t need = keep_list_scratch_bytes(ntotal);
+    if (scratch_bytes < need) {
+        set_error("build_keep_list: scratch too small");
+        return B2_ERR_INVALID;
+    }
+    char* base = static_cast<char*>(scratch);
+    unsigned long long* stats = reinterpret_cast<unsigned long long*>(base);
+    unsigned long long* block_off = stats + 2;
+    uint32_t* block_tot = reinterpret_cast<uint32_t*>(block_off + nblocks);
+    uint32_t* drop = block_tot + ((nblocks + 1) & ~(int64_t)1);
+    B2_CUDA_TRY(cudaMemsetAsync(drop, 0, (size_t)nwords * 4, stream));
+    const unsigned long long init[2] = {0ull, (unsigned long long)ntotal};
+    B2_CUDA_TRY(cudaMemcpyAsync(stats, init, sizeof(init), cudaMemcpyHostToDevice, stream));
+    mark_drop_kernel<<<(unsigned)std::min<int64_t>((n + 255) / 256, 1184), 256, 0, stream>>>(ids_dev, n, ntotal, drop, stats);
+    B2_AFTER_LAUNCH();
+    keep_count_kernel<<<(unsigned)nblocks, kKeepThreads, 0, stream>>>(drop, nwords, ntotal, block_tot);
+    B2_AFTER_LAUNCH();
+    keep_scan_blocks_kernel<<<1, 1024, 0, stream>>>(block_tot, nblocks, block_off);
+    B2_AFTER_LAUNCH();
+    keep_emit_kernel<<<(unsigned)nblocks, kKeepThreads, 0, stream>>>(drop, nwords, ntotal, block_off, stats, src_dev);
+    B2_AFTER_LAUNCH();
+    unsigned long long st[2] = {0ull, 0ull};
+    B2_CUDA_TRY(cudaMemcpyAsync(st, stats, sizeof(st), cudaMemcpyDeviceToHost, stream));
+    B2_CUDA_TRY(cudaStreamSynchronize(stream));
+    *removed = (int64_t)st[0];
+    *first = (int64_t)st[1];
+    return B2_OK;
+}
+
+size_t keep_list_scratch_bytes(int64_t ntotal) {
+    const int64_t nwords = (ntotal + 31) / 32;
+    const int64_t nblocks = (nwords + kKeepThreads - 1) / kKeepThreads;
+    return 16 + (size_t)nblocks * 8 + (size_t)((nblocks + 1) & ~(int64_t)1) * 4 + (size_t)nwords * 4 + 64;
+}
+
 // ------------------------------------------------------------------ running maximum of the squared row norms
 // (ordered-uint image, atomicMax): the refine mode of the tensor-core search bounds its scoring error with it.
 __global__ void max_norm_kernel(const float* __restrict__ norms, int64_t n, uint32_t* __restrict__ out) {

@@ -138,6 +138,13 @@ int gather_rows(const void* rows, int64_t ntotal, size_t pitch_bytes, int d, int
 int compact_rows(void* rows, size_t pitch_bytes, float* norms, const int64_t* src_of_dst, int64_t n_dst,
                  int64_t first_moved, cudaStream_t stream);
 
+// remove_ids on the device: from n ids (device) the list src[j] = row that moves to (first + j), the number of
+// distinct rows dropped and the first of them (ntotal if none).  src_dev holds up to ntotal entries; scratch of
+// keep_list_scratch_bytes(ntotal) bytes.  Synchronises `stream` (the two counts come back to the host).
+size_t keep_list_scratch_bytes(int64_t ntotal);
+int build_keep_list(const int64_t* ids_dev, int64_t n, int64_t ntotal, int64_t* src_dev, void* scratch, size_t scratch_bytes,
+                    int64_t* removed, int64_t* first, cudaStream_t stream);
+
 // max_norm_ord = max(max_norm_ord, ordered image of max(norms[0..n)))
 int update_max_norm(const float* norms, int64_t n, uint32_t* max_norm_ord, cudaStream_t stream);
 

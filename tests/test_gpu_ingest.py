@@ -155,3 +155,30 @@ def test_bulk_host_add_through_the_pinned_ring_and_from_pinned_memory():
     # a second bulk add reuses the ring
     a.add(x[:40_000], normalize=False)
     assert a.ntotal == n + 40_000 and np.array_equal(a.reconstruct_n(n, 40_000), x[:40_000])
+
+
+def test_remove_ids_keep_list_built_on_the_device_matches_numpy_compaction():
+    """remove_ids marks, scans and compacts on the device (only the ids are uploaded): random ids with duplicates,
+    negative and out-of-range entries, runs that cross the 32-row words and the 32768-row blocks of the scan."""
+    from nv_genai_b200 import IndexFlatL2
+
+    n, d = 200_003, 64
+    x = flat.synth(0, n, d, 55)
+    rng = np.random.default_rng(5)
+    for ids in (
+        np.array([n - 1]),                                  # only the last row
+        np.array([0]),                                      # only the first: everything moves
+        np.concatenate([rng.integers(0, n, 7000), [-5, n, n + 10, 31, 32, 33, 32767, 32768, 65535, 65536]]),
+        np.arange(40_000, 120_000),                         # a run over several scan blocks
+    ):
+        idx = IndexFlatL2(d)
+        idx.add(x)
+        keep = np.ones(n, bool)
+        valid = ids[(ids >= 0) & (ids < n)]
+        keep[valid] = False
+        assert idx.remove_ids(ids) == int((~keep).sum())
+        assert idx.ntotal == int(keep.sum())
+        assert np.array_equal(idx.reconstruct_n(0, idx.ntotal), x[keep])
+        D, I = idx.search(x[keep][:3], 1)
+        assert I[:, 0].tolist() == [0, 1, 2] and np.all(D[:, 0] == 0.0)
+    assert idx.remove_ids(np.array([10**9, -1])) == 0 and idx.ntotal == int(keep.sum())
