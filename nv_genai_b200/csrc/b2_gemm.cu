@@ -45,16 +45,20 @@
 //     corrections, added in fp32 registers by the epilogue.  That uses all 512 TMEM columns, so the
 //     fp32 path is single-buffered (tile time ~33k cycles vs ~2k for the read-out).
 //   Epilogue: tcgen05.ld (software-pipelined over 32-column chunks), one thread = one query = one TMEM lane.  A max
-//   tree rejects the chunks without a candidate for any of the warp's 32 queries; survivors replace the minimum of
-//   the query's UNSORTED list of its k best keys in shared memory (warp-cooperative, redux-tracked minimum = the
-//   running k-th best = the threshold; up to four queries per step while several have survivors) and are appended
-//   to the query's candidate log in global memory.
+//   tree rejects the chunks without a candidate for any of the warp's 32 queries; survivors are appended by the
+//   query's own lane to its key RESERVOIR in shared memory (rcap > k slots, faiss's ReservoirResultHandler scheme) and
+//   to the query's candidate log in global memory; a full reservoir is reduced to its k best by the warp (bisection on
+//   the key bits) and the k-th best becomes the query's threshold.
 //   Work item = (query tile, corpus segment); items are dealt round-robin to the CTAs with the
 //   query tile varying fastest, so the CTAs that run at the same time read the same corpus
 //   segment and the corpus is streamed from HBM about once.  A finished item publishes its
 //   k-th best key per query (atomicMax); later items of the same query tile start from that
 //   bound, and running items trade bounds every 32 tiles.  Every item emits k (refine: k + slack) candidates per
 //   query; merge_partials_kernel / merge_rescore finish.
+//   For k >= 32 on a long corpus the refine search is TWO launches: a threshold pre-pass over every 32nd corpus tile,
+//   tau_union_kernel (the k-th best key of the union of the pre-pass lists: a lower bound of the final k-th, since it is
+//   the k-th best of a subset of the rows), then the main pass over the other tiles, whose items all start from that
+//   bound instead of -inf (see gemm_search_refine).
 //
 // Tie rule: equal keys keep the lower row id (a key has to be strictly better than the running
 // k-th to enter, rows arrive in id order, and bounds imported from other segments admit ties).
