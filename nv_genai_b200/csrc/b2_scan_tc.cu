@@ -279,6 +279,8 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
     } else {
         // ================= epilogue: warps 0..3, thread = corpus row = TMEM lane
         uint32_t tc = 0;
+        // lists of 32 slots that keep at most 24: run them as reservoirs (see below); longer lists keep the insertion path
+        const bool reservoir = p.kpad == 32 && p.klist <= 24;
         for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++tc) {
             const uint32_t buf = tc & 1u, par = (tc >> 1) & 1u;
             mbar_wait(smem_u32(tfull_bar + buf), par);
@@ -318,6 +320,56 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
                         const float key = (APX && p.norms != nullptr) ? fmaf(2.f, big[jj], -nrm) : (big[jj] + small[jj]) + 0.0f;
                         const uint64_t cand = pack_cand(key, row);
                         const int li = j * kEpiWarps + warp;
+                        if (reservoir) {
+                            // 32-slot reservoir per (warp, query): passing lanes append side by side in one step (slot =
+                            // count + rank among the passing lanes); only a full reservoir is reduced to its klist best
+                            // - every lane holds one entry and ranks it against the other 31 by shuffles - and the
+                            // klist-th best becomes the threshold.  An admission costs a store instead of the
+                            // replace-the-worst-and-rescan chain of warp_list_insert, which is what the thresholds'
+                            // settling phase of every CTA (~k (1 + ln(rows per CTA / k)) admissions per query, all
+                            // 148 CTAs at once) used to cost: ~300 us per launch at 16 queries, whatever the row count.
+                            uint64_t* L = lists + (size_t)li * p.kpad;
+                            uint64_t thr = worst_s[li];
+                            int cnt = worstpos_s[li];  // entries in the reservoir
+                            bool pass = row < p.n && key > -FLT_MAX && cand > thr;
+                            unsigned m = __ballot_sync(kFull, pass);
+                            if (m) {
+                                const unsigned lt = (1u << lane) - 1u;
+                                while (m) {
+                                    const int room = 32 - cnt;
+                                    if (room == 0) {
+                                        const uint64_t e = L[lane];
+                                        int rank = 0;
+#pragma unroll 8
+                                        for (int s2 = 0; s2 < 32; ++s2) rank += (shfl_u64(e, s2) > e) ? 1 : 0;  // entries are distinct
+                                        __syncwarp();
+                                        if (rank < p.klist) L[rank] = e;  // sorted best-first as a by-product
+                                        if (lane >= p.klist) L[lane] = B2_SENTINEL;  // the slots behind them are free again
+                                        const int src = __ffs(__ballot_sync(kFull, rank == p.klist - 1)) - 1;
+                                        thr = shfl_u64(e, src);
+                                        cnt = p.klist;
+                                        __syncwarp();
+                                        pass = pass && cand > thr;
+                                        m = __ballot_sync(kFull, pass);
+                                        continue;
+                                    }
+                                    const int r = __popc(m & lt);
+                                    if (pass && r < room) {
+                                        L[cnt + r] = cand;
+                                        pass = false;
+                                    }
+                                    cnt += min(__popc(m), room);
+                                    m = __ballot_sync(kFull, pass);
+                                }
+                                __syncwarp();
+                                if (lane == 0) {
+                                    worst_s[li] = thr;
+                                    worstpos_s[li] = cnt;
+                                }
+                                __syncwarp();
+                            }
+                            continue;
+                        }
                         const bool pass = row < p.n && key > -FLT_MAX && cand > worst_s[li];
                         unsigned m = __ballot_sync(kFull, pass);
                         while (m) {
