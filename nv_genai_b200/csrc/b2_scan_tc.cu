@@ -279,8 +279,8 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap tmRows, const __grid_constant
     } else {
         // ================= epilogue: warps 0..3, thread = corpus row = TMEM lane
         uint32_t tc = 0;
-        // lists of 32 slots that keep at most 24: run them as reservoirs (see below); longer lists keep the insertion path
-        const bool reservoir = p.kpad == 32 && p.klist <= 24;
+        // lists of 32 slots that keep at most 28: run them as reservoirs (see below); longer lists keep the insertion path
+        const bool reservoir = p.kpad == 32 && p.klist <= 28;
         for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++tc) {
             const uint32_t buf = tc & 1u, par = (tc >> 1) & 1u;
             mbar_wait(smem_u32(tfull_bar + buf), par);

@@ -91,3 +91,44 @@ def test_bench_and_oracle_use_the_same_synthetic_streams():
     spec.loader.exec_module(b)
     assert b.CORPUS_SEED == flat.CORPUS_SEED and b.QUERY_SEED == flat.QUERY_SEED
     assert set(b.CONFIGS) >= {"cfg1", "cfg2", "cfg2b16", "cfg3", "cfg3bf16", "cfg4", "cfg5"}
+
+
+def test_shard_group_and_query_push_reject_bad_arguments_without_a_gpu():
+    from nv_genai_b200 import _native as N
+
+    g = ctypes.c_void_p()
+    devs = (ctypes.c_int * 2)(0, 0)
+    assert N.lib.b2_shard_group_create(0, devs, 8, N.METRIC_L2, N.DTYPE_F32, 100, ctypes.byref(g)) == N.B2_ERR_INVALID
+    assert N.lib.b2_shard_group_create(2, devs, 8, N.METRIC_L2, N.DTYPE_F32, 0, ctypes.byref(g)) == N.B2_ERR_INVALID
+    assert N.lib.b2_shard_group_create(17, devs, 8, N.METRIC_L2, N.DTYPE_F32, 100, ctypes.byref(g)) == N.B2_ERR_INVALID
+    assert N.lib.b2_shard_search(None, 1, None, 0, 1, None, None, 0, None) == N.B2_ERR_INVALID
+    assert N.lib.b2_shard_group_ntotal(None) == -1 and N.lib.b2_shard_group_nshards(None) == -1
+    assert N.lib.b2_shard_group_add(None, 1, None, 0, 0) == N.B2_ERR_INVALID
+    N.lib.b2_shard_group_destroy(None)  # a null handle is a no-op
+    assert N.lib.b2_query_push(None, 16, 1, None, None, 1, 0, None) == N.B2_ERR_INVALID
+    assert N.lib.b2_flag_wait(None, 1, 0, None) == N.B2_ERR_INVALID
+    assert b"b2_flag_wait" in N.lib.b2_last_error()
+
+
+def test_bench_check_helpers():
+    """The comparison bench.py applies to what it timed: the parity rule in short form."""
+    import importlib.util
+
+    import numpy as np
+
+    spec = importlib.util.spec_from_file_location("_bench2", os.path.join(ROOT, "bench.py"))
+    b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(b)
+    Dr = np.array([[0.9, 0.8, 0.7, 0.6]], np.float32)
+    Ir = np.array([[5, 9, 2, 7]], np.int64)
+    assert b.compare_topk(Dr, Ir, Dr, Ir) == "ok"
+    assert b.compare_topk(Dr * (1 + 5e-6), Ir, Dr, Ir) == "ok"
+    assert b.compare_topk(Dr * 1.001, Ir, Dr, Ir) != "ok"
+    swapped = np.array([[9, 5, 2, 7]], np.int64)
+    assert b.compare_topk(Dr, swapped, Dr, Ir) != "ok"  # 0.9 and 0.8 do not tie
+    tie = np.array([[0.9, 0.9, 0.7, 0.6]], np.float32)
+    assert b.compare_topk(tie, swapped, tie, Ir) == "ok"
+    assert b.compare_topk(Dr[:, :3], Ir[:, :3], Dr, Ir).startswith("shape")
+    ids = b.planted_ids(10_000_000, 8)
+    assert len(ids) == 8 and ids[0] == 0 and 9_999_999 in ids and 1_249_999 in ids and 1_250_000 in ids
+    assert b.planted_ids(10, 1) == [0, 1, 4, 5, 9, 3, 6, 2]
