@@ -389,3 +389,31 @@ def test_more_near_ties_than_the_candidate_lists_hold_take_the_exact_fix_up(dtyp
     # k = 60: still more copies than k, list = 64 (scan) / k + slack (GEMM)
     D, I = idx.search(q, 60)
     assert np.array_equal(I[0], copies[:60])
+
+
+@pytest.mark.parametrize("dtype", ["float32", "bfloat16", "bfloat16+residual"])
+def test_overflowing_lists_in_the_two_launch_search_take_the_fix_up(dtype):
+    """k >= 32 on >= 2048 corpus tiles: threshold pre-pass over every 32nd tile, union, main pass.  Hundreds of exact
+    copies of one query in neighbouring rows overflow a main-pass list; 256 copies of another query filling a SAMPLE
+    tile overflow a pre-pass list.  The flagged query group is redone (all-exact tensor kernel over all tiles and
+    all list slots; on a residual-plane store the whole batch by the two-plane FFMA scan) and every query must still
+    match the float64 oracle, the copies coming back lowest id first."""
+    n, d, nq, k = 600_000, 256, 40, 50
+    x, q = _data(n, d, nq, True, seed=93)
+    main_copies = np.arange(100_000, 100_400)          # tiles 390..392: not sample tiles
+    sample_copies = np.arange(416 * 256, 417 * 256)    # tile 416 = 13 * 32: a tile of the pre-pass
+    x[main_copies] = q[0]
+    x[sample_copies] = q[1]
+    idx = _mk(flat.METRIC_IP, d, dtype)
+    idx.add(x)
+    D, I = idx.search(q, k)
+    assert np.array_equal(I[0], main_copies[:k]), I[0][:8]
+    assert np.array_equal(I[1], sample_copies[:k]), I[1][:8]
+    if dtype == "float32":
+        xr = x
+    else:
+        xr = flat.round_bf16(x)
+        if dtype.endswith("+residual"):
+            xr = xr + flat.round_bf16(x - xr)
+    Dr, Ir = flat.search_f64(xr, q, k, flat.METRIC_IP)
+    assert_parity(D, I, Dr.astype(np.float32), Ir, xr, q, metric_ip=True)
