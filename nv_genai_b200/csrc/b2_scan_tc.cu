@@ -30,9 +30,11 @@
 //   (one per 32-byte K step of a slice), added in fp32 registers.
 // MMA time per slice is 64-96 cycles against ~650 cycles of HBM time per 16 KB slice and SM, so the
 // kernel is HBM-bound like the FFMA scan at batch 1; the tensor pipe is ~15 % busy by design.
-// Selection is the FFMA scan's: one thread = one row, per-(warp, query) top-k lists in shared
-// memory guarded by their worst entry, CTA merge at the end, same partial-list format, same merge
-// kernel, same tie rule (equal scores -> lowest id).
+// Selection: one thread = one row, per-(warp, query) lists in shared memory guarded by a threshold, CTA
+// merge at the end, the FFMA scan's partial-list format, merge kernel and tie rule (equal scores -> lowest
+// id).  Lists of 32 slots that keep at most 28 entries (k <= ~20) run as reservoirs: the lanes whose row
+// passes append side by side in one step and only a full reservoir is ranked (all pairs, by shuffles);
+// longer lists replace their worst entry per admission (warp_list_insert), as the FFMA scan does.
 //
 // Algorithmic HBM bytes per launch = n * pitch_bytes (each row read exactly once).
 #include "b2_kernels.h"
@@ -531,10 +533,12 @@ static void pick_pipeline(int kslices, bool sps_allowed, int nqt, int kpad, int 
     }
 }
 
-// fp32 rows, k <= 64: filter and refine (see scan_tc_kernel, APX).  Launches: prep (1 part) + band + approximate scan +
-// merge_rescore, then the exact fix-up -- prep (2 parts) + exact scan + merge -- whose kernels return at once unless
-// merge_rescore raised a query's overflow flag (never seen on real data: a CTA would have to hold kpad candidates within
-// the error band of the k-th best).
+// k <= 64: filter and refine (see scan_tc_kernel, APX) - fp32 rows for both metrics, bf16 rows for L2 and, with a
+// residual plane, for inner product too.  Launches: scan_tc_prep_kernel (operands, band, cleared flags) + approximate
+// scan + merge_rescore, then the exact fix-up pair -- exact tensor-core scan (fp32 rows, inner product) or FFMA scan
+// passes (L2; bf16 rows, both planes) + merge -- whose kernels return at once unless merge_rescore raised a query's
+// overflow flag (a CTA would have to hold a full list of candidates within the error band of the k-th best: runs of
+// near-duplicate rows do that, random data never).
 static int scan_tc_search_approx(const void* rows, int64_t n, size_t pitch_bytes, int d, const float* q_dev, int nq, int k,
                                  int num_sms, float* D, int64_t* I, cudaStream_t stream, const PeerPush* push,
                                  const uint32_t* max_norm_ord, int metric, const float* norms, int dtype,
