@@ -1445,10 +1445,10 @@ static int gemm_search_refine(const void* rows, int64_t n, size_t pitch_bytes, i
     int tps_s = 0, nseg_s = 0, tps_m = 0, nseg_m = 0;
     if (two_pass) plan(n_sample, &tps_s, &nseg_s);
     plan(total_tiles - n_sample, &tps_m, &nseg_m);
-    // merge_rescore's fast kernel holds all candidates of a query in registers (<= 12288): when the pre-pass lists do
+    // merge_rescore's fast kernel holds all candidates of a query in registers (<= kMergeSelectMax): when the pre-pass lists do
     // not fit beside the main ones, the main launch covers the sample tiles again (3 % more products) and the pre-pass
     // lists only feed the threshold union
-    const bool keep_sample_lists = two_pass && (size_t)(nseg_m + nseg_s) * p.list_len <= 12288;
+    const bool keep_sample_lists = two_pass && (size_t)(nseg_m + nseg_s) * p.list_len <= (size_t)kMergeSelectMax;
     if (two_pass && !keep_sample_lists) plan(total_tiles, &tps_m, &nseg_m);
     p.n_lists = keep_sample_lists ? nseg_m + nseg_s : nseg_m;  // what merge_rescore reads
     // the main launch (when there is no pre-pass: the only one)

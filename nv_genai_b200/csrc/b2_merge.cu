@@ -338,9 +338,9 @@ __global__ void __launch_bounds__(kMergeThreads) merge_rescore_kernel(const uint
 // found by bisection on the 32 key bits (one block-wide count per bit), the few candidates above the cut are compacted
 // into shared memory, re-scored one per warp (balanced over the 16 warps), and only those are sorted.  Measured at
 // 10M x 1024, 4096 queries, k = 100 (23 x 264 candidates per query): 6.9 ms -> see DESIGN.md for the chunked-sort kernel above.
-constexpr int kSelMaxPerThread = 24;
+constexpr int kSelMaxPerThread = kMergeSelectMax / kMergeThreads;  // 28
 
-__global__ void __launch_bounds__(kMergeThreads) merge_rescore_select_kernel(const uint64_t* __restrict__ partial, int total,
+__global__ void __launch_bounds__(kMergeThreads, 1) merge_rescore_select_kernel(const uint64_t* __restrict__ partial, int total,
                                                                             int k, int kpad, int sort_n, int metric,
                                                                             float* D, int64_t* I, size_t out_stride,
                                                                             const float* __restrict__ qnorm,

@@ -486,7 +486,7 @@ __global__ void scan_tc_prep_kernel(const float* __restrict__ q, int nq, int d, 
 }  // namespace
 
 bool scan_tc_approx_feasible(int64_t n, int k, int num_sms) {
-    return (long long)std::min<long long>(num_sms, (n + kTileRows - 1) / kTileRows) * next_pow2(k < 32 ? 32 : k) <= 12288;
+    return (long long)std::min<long long>(num_sms, (n + kTileRows - 1) / kTileRows) * next_pow2(k < 32 ? 32 : k) <= kMergeSelectMax;
 }
 
 bool scan_tc_supported(int64_t n, int d, int dtype, int metric, int k, int64_t nq, bool approx, bool residual) {
