@@ -62,7 +62,7 @@ int merge_rescore(const uint64_t* partial, int nq, int nlists, int list_len, int
 // overflow (optional, device, [nq + 1], zeroed by the caller): the lists are sorted best-first and may have dropped
 // candidates beyond list_len; a query whose cut reaches into a full list's last entry gets overflow[q] = 1 (and
 // overflow[nq] = 1) and NO output: the caller redoes it exactly.  Needs nlists * list_len <= kMergeSelectMax.
-constexpr int kMergeSelectMax = 28 * 512;  // candidates per query the register-resident merge holds (28 per thread)
+constexpr int kMergeSelectMax = 24 * 512;  // candidates per query the register-resident merge holds (24 per thread)
 // merge of exchanged blocks that first waits (per query) for every part's flag to reach `epoch`
 int merge_shards_wait(int metric, int nq, int k, int nparts, const char* blocks, size_t part_stride_bytes,
                       const uint32_t* flags, size_t flag_stride_elems, uint32_t epoch, const int64_t* id_bases, float* D,

@@ -338,9 +338,14 @@ __global__ void __launch_bounds__(kMergeThreads) merge_rescore_kernel(const uint
 // found by bisection on the 32 key bits (one block-wide count per bit), the few candidates above the cut are compacted
 // into shared memory, re-scored one per warp (balanced over the 16 warps), and only those are sorted.  Measured at
 // 10M x 1024, 4096 queries, k = 100 (23 x 264 candidates per query): 6.9 ms -> see DESIGN.md for the chunked-sort kernel above.
-constexpr int kSelMaxPerThread = kMergeSelectMax / kMergeThreads;  // 28
+constexpr int kSelMaxPerThread = kMergeSelectMax / kMergeThreads;  // 24
 
-__global__ void __launch_bounds__(kMergeThreads, 1) merge_rescore_select_kernel(const uint64_t* __restrict__ partial, int total,
+// MINB = CTAs per SM the compiler plans for.  1: the candidates stay in registers (102 registers, no spills) - the
+// latency of a search of a few queries, where a CTA per query cannot fill the GPU anyway (36 -> 30 us at one query).
+// 2: 64 registers with the candidate array partly in local memory, but two CTAs per SM - faster when thousands of
+// queries are merged (2.3 vs 1.7 ms at 4096 queries, k = 100).
+template <int MINB>
+__global__ void __launch_bounds__(kMergeThreads, MINB) merge_rescore_select_kernel(const uint64_t* __restrict__ partial, int total,
                                                                             int k, int kpad, int sort_n, int metric,
                                                                             float* D, int64_t* I, size_t out_stride,
                                                                             const float* __restrict__ qnorm,
@@ -470,8 +475,12 @@ int merge_rescore(const uint64_t* partial, int nq, int nlists, int list_len, int
     if (total <= kSelMaxPerThread * kMergeThreads && !no_select) {
         // a round holds up to sort_n - kpad re-scored candidates; 1024 is plenty (k + in-band entries, typically < 300)
         const int sel_sort_n = std::max(2 * kpad, 1024);
-        merge_rescore_select_kernel<<<nq, kMergeThreads, (size_t)sel_sort_n * sizeof(uint64_t), stream>>>(
-            partial, total, k, kpad, sel_sort_n, metric, D, I, out_stride, qnorm, ctx, push, overflow, list_len);
+        if (nq <= 148)
+            merge_rescore_select_kernel<1><<<nq, kMergeThreads, (size_t)sel_sort_n * sizeof(uint64_t), stream>>>(
+                partial, total, k, kpad, sel_sort_n, metric, D, I, out_stride, qnorm, ctx, push, overflow, list_len);
+        else
+            merge_rescore_select_kernel<2><<<nq, kMergeThreads, (size_t)sel_sort_n * sizeof(uint64_t), stream>>>(
+                partial, total, k, kpad, sel_sort_n, metric, D, I, out_stride, qnorm, ctx, push, overflow, list_len);
         B2_AFTER_LAUNCH();
         return B2_OK;
     }
