@@ -250,6 +250,13 @@ int b2_shard_group_add(b2_shard_group* g, int64_t n, const float* x, int x_where
     return B2_OK;
 }
 
+int b2_shard_group_set_option(b2_shard_group* g, const char* name, int64_t value) {
+    B2_TRY(shard_check(g));
+    std::lock_guard<std::mutex> lk(g->mu);
+    for (int i = 0; i < g->n; ++i) B2_TRY(b2_index_set_option(g->shard[i], name, value));
+    return B2_OK;
+}
+
 int b2_shard_group_reset(b2_shard_group* g) {
     B2_TRY(shard_check(g));
     std::lock_guard<std::mutex> lk(g->mu);

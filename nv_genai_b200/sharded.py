@@ -277,7 +277,12 @@ class ShardGroup:
         arr = (ctypes.c_int * len(self.devices))(*self.devices)
         N.check(N.lib.b2_shard_group_create(len(self.devices), arr, self._d, self.metric_type, _DTYPES[dtype],
                                             int(rows_per_shard), ctypes.byref(self._h)))
+        if dtype.endswith("+residual"):
+            N.check(N.lib.b2_shard_group_set_option(self._h, b"bf16_residual", 1))
         self.is_trained = True
+
+    def set_option(self, name: str, value: int) -> None:
+        self._N.check(self._N.lib.b2_shard_group_set_option(self._h, name.encode(), int(value)))
 
     d = property(lambda self: self._d)
     ntotal = property(lambda self: int(self._N.lib.b2_shard_group_ntotal(self._h)))

@@ -19,7 +19,7 @@ def _devices(n):
 
 
 @pytest.mark.parametrize("metric", [flat.METRIC_IP, flat.METRIC_L2])
-@pytest.mark.parametrize("dtype", ["float32", "bfloat16"])
+@pytest.mark.parametrize("dtype", ["float32", "bfloat16", "bfloat16+residual"])
 def test_shard_group_equals_single_index_and_oracle(metric, dtype):
     from nv_genai_b200 import IndexFlat, ShardGroup
 
@@ -38,7 +38,11 @@ def test_shard_group_equals_single_index_and_oracle(metric, dtype):
     assert grp.ntotal == n and [grp.shard_ntotal(i) for i in range(4)] == [12_500] * 4
     one = IndexFlat(d, metric, dtype)
     one.add(x)
-    xs = flat.round_bf16(x) if dtype == "bfloat16" else x
+    xs = x
+    if dtype.startswith("bfloat16"):
+        xs = flat.round_bf16(x)
+        if dtype.endswith("+residual"):
+            xs = xs + flat.round_bf16(x - xs)
     for nq, k in ((1, 4), (16, 10), (40, 100)):
         D, I = grp.search(q[:nq], k)
         D1, I1 = one.search(q[:nq], k)
