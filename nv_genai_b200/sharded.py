@@ -257,7 +257,12 @@ class ShardedFlatIndex:
         nb_i = nq * k * 8
         I_parts = gathered[:, :nb_i].contiguous().view(t.int64).reshape(self.world, nq, k)
         D_parts = gathered[:, nb_i:].contiguous().view(t.float32).reshape(self.world, nq, k)
-        return self._merge(self.metric, D_parts, I_parts)
+        D, I = self._merge(self.metric, D_parts, I_parts)
+        if out is not None:  # packed [I | D], as on the CUDA path
+            nres = nq * k
+            out[: nres * 8].view(t.int64).view(nq, k).copy_(I)
+            out[nres * 8:].view(t.float32).view(nq, k).copy_(D)
+        return D, I
 
 
 class ShardGroup:

@@ -74,6 +74,11 @@ def _worker(rank, world, port, n, d, nq, k, metric, out):
         sh2.add_local(x[lo:hi])
         D2, I2 = sh2.search(torch.from_numpy(q), k)
         assert np.array_equal(I2.numpy(), Ir)
+        # packed output block [I | D]: what a caller copies back with one transfer
+        packed = torch.empty(nq * k * 12, dtype=torch.uint8)
+        sh2.search(torch.from_numpy(q), k, out=packed)
+        assert np.array_equal(packed[: nq * k * 8].view(torch.int64).view(nq, k).numpy(), Ir)
+        assert np.array_equal(packed[nq * k * 8:].view(torch.float32).view(nq, k).numpy(), Dr)
         # k larger than a shard
         small = ShardedFlatIndex(d, metric, local_index=OracleIndex(d, metric), merge_fn=numpy_merge)
         small.add_global(x[:5])
