@@ -184,3 +184,31 @@ def test_property_permutation_and_k_monotone(n, d, k, seed, ip):
     # top-(k+1) extends top-k
     D2, I2 = flat.search(x, q, k + 1, metric)
     assert np.array_equal(I2[:, :k], I) and np.array_equal(D2[:, :k], D)
+
+
+@pytest.mark.parametrize("metric", [flat.METRIC_IP, flat.METRIC_L2])
+def test_streaming_search_over_blocks_equals_one_scan(metric):
+    """What the full-size GPU tests and bench.py's check rely on: feeding the corpus block by block (ragged blocks,
+    rows regenerated per block) gives the same (D, I) as one sequential scan, ids global, ties lowest id first."""
+    n, d, nq, k = 5_003, 96, 7, 12
+    x = flat.synth(0, n, d, 5)
+    x[4000] = x[17]  # a tie across two blocks
+    q = flat.synth(0, nq, d, 6)
+    q[2] = x[17]
+    st_ = flat.StreamingSearch(q, k, metric)
+    for r0 in range(0, n, 1_111):
+        st_.feed(x[r0:r0 + 1_111], r0)
+    D, I = st_.result()
+    Dr, Ir, _ = flat.search_seq(x, q, k, metric)
+    assert np.array_equal(I, Ir) and np.array_equal(D, Dr)
+    assert I[2, 0] == 17 and I[2, 1] == 4000
+    # fewer rows than k: padded like index.search
+    st2 = flat.StreamingSearch(q, k, metric)
+    st2.feed(x[:5], 0)
+    D2, I2 = st2.result()
+    D2r, I2r, _ = flat.search_seq(x[:5], q, k, metric)
+    assert np.array_equal(I2, I2r) and np.array_equal(D2, D2r)
+    # the in-place bf16 rounding equals the copying one
+    y = x.copy()
+    flat.round_bf16_inplace(y)
+    assert np.array_equal(y, flat.round_bf16(x))
