@@ -283,6 +283,9 @@ B2_API int64_t b2_shard_group_shard_ntotal(const b2_shard_group* g, int shard);
 B2_API int b2_shard_group_add(b2_shard_group* g, int64_t n, const float* x, int x_where, unsigned flags);
 B2_API int b2_shard_group_remove_ids(b2_shard_group* g, int64_t n, const int64_t* ids, int64_t* n_removed);
 B2_API int b2_shard_group_reset(b2_shard_group* g);
+/* index.reconstruct over the group: out[j] = row ids[j] (GLOBAL ids, host arrays, n x d fp32); ids outside the store
+ * give zero rows. */
+B2_API int b2_shard_group_reconstruct_batch(b2_shard_group* g, int64_t n, const int64_t* ids, float* out);
 /* b2_index_set_option on every shard (e.g. "bf16_residual" on an empty bf16 group, "bf16_shadow", "gemm_query_parts"). */
 B2_API int b2_shard_group_set_option(b2_shard_group* g, const char* name, int64_t value);
 B2_API int b2_shard_search(b2_shard_group* g, int64_t nq, const float* q, int q_where, int k, float* D, int64_t* I,

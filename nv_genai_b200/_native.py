@@ -25,7 +25,7 @@ REL_NONE, REL_EUCLIDEAN, REL_COSINE, REL_MAX_INNER_PRODUCT = 0, 1, 2, 3  # langc
 SYMBOLS = [
     "b2_index_create", "b2_index_destroy", "b2_index_ntotal", "b2_index_d", "b2_index_metric", "b2_index_dtype",
     "b2_index_device", "b2_index_add", "b2_index_search", "b2_index_search_static", "b2_index_search_filtered", "b2_filter_results", "b2_index_reconstruct_batch", "b2_index_remove_ids",
-    "b2_index_merge_from", "b2_index_set_option", "b2_index_reset", "b2_index_mmr", "b2_merge_shard_lists", "b2_merge_shard_lists_packed", "b2_index_search_push", "b2_merge_shard_lists_wait", "b2_query_push", "b2_flag_wait", "b2_shard_group_create", "b2_shard_group_destroy", "b2_shard_group_ntotal", "b2_shard_group_nshards", "b2_shard_group_shard_ntotal", "b2_shard_group_add", "b2_shard_group_remove_ids", "b2_shard_group_reset", "b2_shard_group_set_option", "b2_shard_search", "b2_normalize_l2",
+    "b2_index_merge_from", "b2_index_set_option", "b2_index_reset", "b2_index_mmr", "b2_merge_shard_lists", "b2_merge_shard_lists_packed", "b2_index_search_push", "b2_merge_shard_lists_wait", "b2_query_push", "b2_flag_wait", "b2_shard_group_create", "b2_shard_group_destroy", "b2_shard_group_ntotal", "b2_shard_group_nshards", "b2_shard_group_shard_ntotal", "b2_shard_group_add", "b2_shard_group_remove_ids", "b2_shard_group_reset", "b2_shard_group_reconstruct_batch", "b2_shard_group_set_option", "b2_shard_search", "b2_normalize_l2",
     "b2_synth_fill", "b2_launch_count", "b2_launch_count_reset", "b2_prof_enable", "b2_prof_read", "b2_prof_read_kernel", "b2_last_error",
     "b2_version",
 ]
@@ -95,6 +95,8 @@ def _load() -> ctypes.CDLL:
     L.b2_shard_group_remove_ids.restype = i32
     L.b2_shard_group_reset.argtypes = [vp]
     L.b2_shard_group_reset.restype = i32
+    L.b2_shard_group_reconstruct_batch.argtypes = [vp, i64, vp, vp]
+    L.b2_shard_group_reconstruct_batch.restype = i32
     L.b2_shard_group_set_option.argtypes = [vp, ctypes.c_char_p, i64]
     L.b2_shard_group_set_option.restype = i32
     L.b2_shard_search.argtypes = [vp, i64, vp, i32, i32, vp, vp, i32, vp]

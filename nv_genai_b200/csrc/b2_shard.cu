@@ -20,6 +20,7 @@
 // [base_g, base_g + ntotal_g) and is filled up to `rows_per_shard` before shard g + 1 receives rows (the last shard
 // takes whatever follows), so shard order is id order and the merge's lowest-id tie rule holds across shards.
 #include <algorithm>
+#include <cstring>
 #include <mutex>
 #include <vector>
 
@@ -285,6 +286,39 @@ int b2_shard_group_remove_ids(b2_shard_group* g, int64_t n, const int64_t* ids, 
         base += cnt;  // bases are those BEFORE the removal: ids name rows of the store as the caller saw it
     }
     if (n_removed) *n_removed = total;
+    return B2_OK;
+}
+
+int b2_shard_group_reconstruct_batch(b2_shard_group* g, int64_t n, const int64_t* ids, float* out) {
+    B2_TRY(shard_check(g));
+    if (n < 0 || (n > 0 && (ids == nullptr || out == nullptr))) {
+        set_error("b2_shard_group_reconstruct_batch: bad arguments");
+        return B2_ERR_INVALID;
+    }
+    std::lock_guard<std::mutex> lk(g->mu);
+    int64_t base = 0;
+    std::vector<bool> done((size_t)n, false);
+    for (int i = 0; i < g->n; ++i) {
+        const int64_t cnt = b2_index_ntotal(g->shard[i]);
+        std::vector<int64_t> local, where;
+        for (int64_t j = 0; j < n; ++j)
+            if (ids[j] >= base && ids[j] < base + cnt) {
+                local.push_back(ids[j] - base);
+                where.push_back(j);
+            }
+        if (!local.empty()) {
+            std::vector<float> rows(local.size() * (size_t)g->d);
+            B2_TRY(b2_index_reconstruct_batch(g->shard[i], (int64_t)local.size(), local.data(), B2_HOST, rows.data(), B2_HOST,
+                                              nullptr));
+            for (size_t t = 0; t < local.size(); ++t) {
+                memcpy(out + (size_t)where[t] * g->d, rows.data() + t * (size_t)g->d, (size_t)g->d * sizeof(float));
+                done[(size_t)where[t]] = true;
+            }
+        }
+        base += cnt;
+    }
+    for (int64_t j = 0; j < n; ++j)  // ids outside the store: zero rows, as b2_index_reconstruct_batch gives
+        if (!done[(size_t)j]) memset(out + (size_t)j * g->d, 0, (size_t)g->d * sizeof(float));
     return B2_OK;
 }
 

@@ -342,3 +342,58 @@ class ShardGroup:
 
     def reset(self) -> None:
         self._N.check(self._N.lib.b2_shard_group_reset(self._h))
+
+    # ---- what LangChain's FAISS glue needs beyond add / search (vectorstore.py accepts a ShardGroup as its index)
+    device = property(lambda self: self.devices[0])
+
+    def reconstruct_batch(self, ids):
+        import numpy as np
+
+        a = np.ascontiguousarray(np.asarray(ids, dtype=np.int64).reshape(-1))
+        out = np.empty((a.size, self._d), dtype=np.float32)
+        self._N.check(self._N.lib.b2_shard_group_reconstruct_batch(self._h, a.size, a.ctypes.data, out.ctypes.data))
+        return out
+
+    def reconstruct(self, key: int):
+        key = int(key)
+        if key < 0 or key >= self.ntotal:
+            raise RuntimeError(f"reconstruct: key {key} out of range [0, {self.ntotal})")
+        return self.reconstruct_batch([key])[0]
+
+    def reconstruct_n(self, n0: int = 0, ni: int = -1):
+        import numpy as np
+
+        if ni == -1:
+            ni = self.ntotal - n0
+        if n0 < 0 or ni < 0 or n0 + ni > self.ntotal:
+            raise RuntimeError(f"reconstruct_n: range [{n0}, {n0 + ni}) out of [0, {self.ntotal})")
+        return self.reconstruct_batch(np.arange(n0, n0 + ni, dtype=np.int64))
+
+    def merge_from(self, other, add_id: int = 0) -> None:
+        raise NotImplementedError("merge_from into a shard group: add the other store's rows with add()")
+
+    def mmr(self, x, k: int = 4, fetch_k: int = 20, lambda_mult: float = 0.5):
+        """langchain's maximal_marginal_relevance over the group's search hits: global search of fetch_k, the hits' rows
+        gathered from their shards, the greedy pick on the root device (one scratch index per query: this is the
+        API-completeness path, the batched device MMR belongs to a single index)."""
+        import numpy as np
+
+        from .index import METRIC_INNER_PRODUCT, IndexFlat
+
+        q = np.ascontiguousarray(np.atleast_2d(np.asarray(x.cpu() if hasattr(x, "cpu") else x, dtype=np.float32)))
+        D, I = self.search(q, int(fetch_k))
+        ids = np.full((q.shape[0], int(k)), -1, dtype=np.int64)
+        sc = np.full((q.shape[0], int(k)), 0.0, dtype=np.float32)
+        for r in range(q.shape[0]):
+            hits = [int(i) for i in I[r] if i != -1]
+            if not hits:
+                continue
+            rows = self.reconstruct_batch(hits)
+            tmp = IndexFlat(self._d, METRIC_INNER_PRODUCT, "float32", self.devices[0])
+            tmp.add(rows)
+            # the candidates in search order are rows 0.. of the scratch index: fetch them all, pick k
+            pick, _ = tmp.mmr(q[r:r + 1], k=int(k), fetch_k=len(hits), lambda_mult=lambda_mult)
+            for j, p in enumerate(int(v) for v in pick[0] if v != -1):
+                ids[r, j] = hits[p]
+                sc[r, j] = D[r][p]
+        return ids, sc

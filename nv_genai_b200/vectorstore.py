@@ -56,8 +56,10 @@ class FAISS:
         if not hasattr(embedding_function, "embed_documents") and not hasattr(embedding_function, "embed_query"):
             logger.warning("`embedding_function` is expected to be an Embeddings object, support for passing in a "
                            "function will soon be removed.")
-        if not isinstance(getattr(index, "wrapped", index), _ix.IndexFlat):
-            raise TypeError("index must be a nv_genai_b200 IndexFlatL2 / IndexFlatIP (there is no CPU faiss path)")
+        from .sharded import ShardGroup  # a flat index sharded over several GPUs of this process serves as well
+
+        if not isinstance(getattr(index, "wrapped", index), (_ix.IndexFlat, ShardGroup)):
+            raise TypeError("index must be a nv_genai_b200 IndexFlatL2 / IndexFlatIP or ShardGroup (there is no CPU faiss path)")
         self.embedding_function = embedding_function
         self.index = index
         self.docstore = docstore

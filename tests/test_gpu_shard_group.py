@@ -101,3 +101,47 @@ def test_shard_group_argument_errors():
     grp = ShardGroup(64, flat.METRIC_IP, [0, 0], 100)
     with pytest.raises(AssertionError):
         grp.search(np.zeros((1, 32), np.float32), 3)
+
+
+def test_langchain_faiss_class_over_a_shard_group(tmp_path):
+    """`FAISS(embedder, ShardGroup(...), InMemoryDocstore(), {})`: the reference's constructor shape
+    (/root/reference/RetrievalAugmentedGeneration/common/utils.py:217) with the index sharded over GPUs must answer
+    like the same store over one IndexFlatL2: search with scores, thresholds, MMR, delete, save_local."""
+    from fakes import HashEmbeddings
+    from nv_genai_b200 import FAISS, IndexFlatL2, InMemoryDocstore, ShardGroup
+
+    d = 64
+    emb = HashEmbeddings(d)
+    texts = [f"chunk {i} about topic {i % 7}" for i in range(300)]
+    metas = [{"topic": i % 7} for i in range(300)]
+    one = FAISS(emb, IndexFlatL2(d), InMemoryDocstore(), {})
+    grp = FAISS(emb, ShardGroup(d, flat.METRIC_L2, _devices(3), 100), InMemoryDocstore(), {})
+    ids = [f"id-{i}" for i in range(300)]
+    one.add_texts(texts, metas, ids=ids)
+    grp.add_texts(texts[:150], metas[:150], ids=ids[:150])
+    grp.add_texts(texts[150:], metas[150:], ids=ids[150:])
+    assert grp.index.ntotal == 300 and [grp.index.shard_ntotal(i) for i in range(3)] == [100, 100, 100]
+    for query in ("chunk 17 about topic 3", "something else entirely"):
+        a = one.similarity_search_with_score(query, k=5)
+        b = grp.similarity_search_with_score(query, k=5)
+        assert [(x.page_content, float(s)) for x, s in a] == [(x.page_content, float(s)) for x, s in b]
+        a = one.similarity_search_with_score(query, k=4, filter={"topic": 3}, fetch_k=50)
+        b = grp.similarity_search_with_score(query, k=4, filter={"topic": 3}, fetch_k=50)
+        assert [x.page_content for x, _ in a] == [x.page_content for x, _ in b]
+        a = one.max_marginal_relevance_search(query, k=4, fetch_k=20)
+        b = grp.max_marginal_relevance_search(query, k=4, fetch_k=20)
+        assert [x.page_content for x in a] == [x.page_content for x in b]
+    assert grp.similarity_search(texts[42], k=1)[0].page_content == texts[42]
+    # delete renumbers like faiss across the shard boundaries
+    gone = ["id-0", "id-99", "id-100", "id-250"]
+    one.delete(gone)
+    grp.delete(gone)
+    assert grp.index.ntotal == 296 and grp.index_to_docstore_id == one.index_to_docstore_id
+    a = one.similarity_search_with_score(texts[101], k=3)
+    b = grp.similarity_search_with_score(texts[101], k=3)
+    assert [(x.page_content, float(s)) for x, s in a] == [(x.page_content, float(s)) for x, s in b]
+    # saved in faiss's flat format: loads back into a single index
+    grp.save_local(str(tmp_path))
+    back = FAISS.load_local(str(tmp_path), emb, allow_dangerous_deserialization=True)
+    assert back.index.ntotal == 296
+    assert back.similarity_search(texts[200], k=1)[0].page_content == texts[200]
