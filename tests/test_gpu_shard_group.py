@@ -128,6 +128,8 @@ def test_langchain_faiss_class_over_a_shard_group(tmp_path):
         a = one.similarity_search_with_score(query, k=4, filter={"topic": 3}, fetch_k=50)
         b = grp.similarity_search_with_score(query, k=4, filter={"topic": 3}, fetch_k=50)
         assert [x.page_content for x, _ in a] == [x.page_content for x, _ in b]
+    # MMR with queries that are not stored texts (a stored copy makes every later MMR score an exact tie at zero)
+    for query in ("a question about topic 3", "something else entirely"):
         a = one.max_marginal_relevance_search(query, k=4, fetch_k=20)
         b = grp.max_marginal_relevance_search(query, k=4, fetch_k=20)
         assert [x.page_content for x in a] == [x.page_content for x in b]
