@@ -740,6 +740,38 @@ static int search_device(b2_index* h, int64_t nq, const float* q_dev, int k, flo
     return B2_OK;
 }
 
+// Small host inputs / outputs of a search travel through a pinned bounce buffer owned by the calling thread: a copy
+// between pageable memory and the device is staged by the driver and synchronous, two of them (D and I) twice; with the
+// bounce buffer a host-buffer search is ONE async H2D, the kernels, ONE async D2H of the packed (I | D) block and one
+// stream synchronisation.  Grows to what the thread's searches need, up to 1 MiB; larger transfers take the plain path.
+namespace {
+struct HostBounce {
+    char* p = nullptr;
+    size_t cap = 0;
+    ~HostBounce() {
+        if (p) cudaFreeHost(p);
+    }
+    char* get(size_t bytes) {
+        if (bytes > ((size_t)1 << 20)) return nullptr;
+        if (bytes > cap) {
+            if (p) cudaFreeHost(p);
+            p = nullptr;
+            cap = 0;
+            size_t want = 65536;
+            while (want < bytes) want <<= 1;
+            if (cudaHostAlloc(reinterpret_cast<void**>(&p), want, cudaHostAllocPortable) != cudaSuccess) {
+                cudaGetLastError();
+                p = nullptr;
+                return nullptr;
+            }
+            cap = want;
+        }
+        return p;
+    }
+};
+thread_local HostBounce t_bounce;
+}  // namespace
+
 int b2_index_search(b2_index* h, int64_t nq, const float* q, int q_where, int k, float* D, int64_t* I, int out_where,
                     void* stream_) {
     B2_TRY(check_handle(h));
@@ -766,9 +798,21 @@ int b2_index_search(b2_index* h, int64_t nq, const float* q, int q_where, int k,
     void* out_tmp = nullptr;
     const size_t nres = (size_t)nq * k;
     int rc = B2_OK;
+    // one bounce buffer for both directions: [queries | packed results]
+    const size_t q_bytes = q_where == B2_HOST ? (size_t)nq * h->d * sizeof(float) : 0;
+    const size_t r_bytes = out_where == B2_HOST ? nres * 12 : 0;
+    const size_t q_pad = (q_bytes + 255) & ~(size_t)255;
+    // only when the call ends with a stream synchronisation (host outputs): the copies out of / into the buffer are
+    // then complete before this thread can reuse it
+    char* bounce = out_where == B2_HOST ? t_bounce.get(q_pad + r_bytes) : nullptr;
     if (q_where == B2_HOST) {
         B2_CUDA_TRY(cudaMallocAsync(&q_tmp, (size_t)nq * h->d * sizeof(float), stream));
-        cudaError_t e = cudaMemcpyAsync(q_tmp, q, (size_t)nq * h->d * sizeof(float), cudaMemcpyHostToDevice, stream);
+        const void* src = q;
+        if (bounce != nullptr) {
+            memcpy(bounce, q, q_bytes);
+            src = bounce;
+        }
+        cudaError_t e = cudaMemcpyAsync(q_tmp, src, (size_t)nq * h->d * sizeof(float), cudaMemcpyHostToDevice, stream);
         if (e != cudaSuccess) {
             set_error("b2_index_search: query copy failed: %s", cudaGetErrorString(e));
             rc = B2_ERR_CUDA;
@@ -787,8 +831,13 @@ int b2_index_search(b2_index* h, int64_t nq, const float* q, int q_where, int k,
     }
     if (rc == B2_OK) rc = search_device(h, nq, q_dev, k, D_dev, I_dev, stream);
     if (rc == B2_OK && out_where == B2_HOST) {
-        cudaError_t e = cudaMemcpyAsync(I, I_dev, nres * 8, cudaMemcpyDeviceToHost, stream);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(D, D_dev, nres * 4, cudaMemcpyDeviceToHost, stream);
+        cudaError_t e;
+        if (bounce != nullptr) {
+            e = cudaMemcpyAsync(bounce + q_pad, I_dev, nres * 12, cudaMemcpyDeviceToHost, stream);  // (I | D) are contiguous
+        } else {
+            e = cudaMemcpyAsync(I, I_dev, nres * 8, cudaMemcpyDeviceToHost, stream);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(D, D_dev, nres * 4, cudaMemcpyDeviceToHost, stream);
+        }
         if (e != cudaSuccess) {
             set_error("b2_index_search: result copy failed: %s", cudaGetErrorString(e));
             rc = B2_ERR_CUDA;
@@ -801,6 +850,9 @@ int b2_index_search(b2_index* h, int64_t nq, const float* q, int q_where, int k,
         if (e != cudaSuccess) {
             set_error("b2_index_search: %s", cudaGetErrorString(e));
             rc = B2_ERR_CUDA;
+        } else if (bounce != nullptr) {
+            memcpy(I, bounce + q_pad, nres * 8);
+            memcpy(D, bounce + q_pad + nres * 8, nres * 4);
         }
     }
     return rc;
